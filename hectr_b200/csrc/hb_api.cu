@@ -1,0 +1,826 @@
+// C ABI of the engine (include/hectr_b200.h): context, containers, launch orchestration.
+#include <cstdio>
+#include <cstdarg>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <map>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+#include "../../include/hectr_b200.h"
+#include "hb_tables.hpp"
+#include "hb_kernels.cuh"
+
+extern "C" {
+struct hb_ring;
+hb_ring *hb_ring_create(unsigned logn);
+void hb_ring_destroy(hb_ring *r);
+void hb_ring_encode(const hb_ring *r, unsigned slots, const double *m, double Delta, uint64_t *words, unsigned W);
+void hb_ring_decode(const hb_ring *r, unsigned slots, const uint64_t *words, unsigned W, double Delta, double *m);
+}
+
+using hbdev::Tables;
+
+// ---------------------------------------------------------------------------------------------------------
+// error handling: the reference prints a red "error:" line and aborts (precomp.c:344-350)
+// ---------------------------------------------------------------------------------------------------------
+[[noreturn]] static void hb_die(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  fprintf(stderr, "\033[1m\033[31merror:\033[0m \033[1mhectr_b200\033[0m. ");
+  vfprintf(stderr, fmt, ap);
+  fprintf(stderr, "\n");
+  va_end(ap);
+  abort();
+}
+#define CUDA_OK(expr)                                                                          \
+  do {                                                                                         \
+    cudaError_t e_ = (expr);                                                                   \
+    if (e_ != cudaSuccess) hb_die("CUDA failure %s at %s:%d (%s)", cudaGetErrorString(e_), __FILE__, __LINE__, #expr); \
+  } while (0)
+
+struct GemvPlan {
+  std::vector<double> A;     // the matrix the plan was built from
+  unsigned l = 0, D = 0;
+  uint64_t *pthat = nullptr; // device [slots][D][N]: ntt of the encoded, pre-rotated diagonals
+};
+
+struct hb_ctx {
+  hb::HostTables ht;
+  Tables dt;
+  std::vector<void *> table_allocs;
+  int device = 0, sm_count = 0;
+  cudaStream_t stream = nullptr, own_stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  uint64_t launches = 0;
+  // workspaces (grow only)
+  uint64_t *wsA = nullptr, *wsB = nullptr;
+  size_t wsA_bytes = 0, wsB_bytes = 0;
+  // pool of ciphertext buffers keyed by capacity in bytes
+  std::multimap<size_t, uint64_t *> pool;
+  std::map<uint64_t *, size_t> live;
+  hb_ring *ring = nullptr;
+  std::vector<GemvPlan> plans;
+  std::vector<uint64_t> enc_host;   // [WC][N] scratch for hb_he_ecd / gemv plans
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// launch helpers
+// ---------------------------------------------------------------------------------------------------------
+template <class... KArgs, class... Args>
+static void launch(hb_ctx *ctx, void (*kernel)(KArgs...), unsigned grid, unsigned threads, size_t smem, int cluster,
+                   Args... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof cfg);
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(threads, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = ctx->stream;
+  cudaLaunchAttribute at[1];
+  if (cluster > 1) {
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cluster;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+  }
+  CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...));
+  ctx->launches++;
+}
+
+template <class K>
+static void want_smem(K kernel, size_t bytes) {
+  static std::map<void *, size_t> done;
+  void *key = (void *)kernel;
+  auto it = done.find(key);
+  if (it != done.end() && it->second >= bytes) return;
+  CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  done[key] = bytes;
+}
+
+#define HB_LOGN_CASES(X) X(7) X(10) X(11) X(12) X(13) X(14) X(15) X(16)
+
+template <int LOGN>
+struct Launch {
+  typedef hbdev::Cfg<LOGN> G;
+  static void ntt_fwd(hb_ctx *c, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D, bool strict) {
+    if (strict) {
+      want_smem(hbdev::k_ntt_fwd<LOGN, true>, G::SMEM_BYTES);
+      launch(c, hbdev::k_ntt_fwd<LOGN, true>, (unsigned)(nlimbs * G::C), G::THREADS, G::SMEM_BYTES, G::C, in, out, c->dt, d0, D);
+    } else {
+      want_smem(hbdev::k_ntt_fwd<LOGN, false>, G::SMEM_BYTES);
+      launch(c, hbdev::k_ntt_fwd<LOGN, false>, (unsigned)(nlimbs * G::C), G::THREADS, G::SMEM_BYTES, G::C, in, out, c->dt, d0, D);
+    }
+  }
+  static void ntt_inv(hb_ctx *c, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D) {
+    want_smem(hbdev::k_ntt_inv<LOGN>, G::SMEM_BYTES);
+    launch(c, hbdev::k_ntt_inv<LOGN>, (unsigned)(nlimbs * G::C), G::THREADS, G::SMEM_BYTES, G::C, in, out, c->dt, d0, D);
+  }
+  static void poly_ntt(hb_ctx *c, const uint64_t *src, size_t stride, int W, uint64_t *out, unsigned D, size_t npoly) {
+    want_smem(hbdev::k_poly_ntt<LOGN>, G::SMEM_BYTES);
+    launch(c, hbdev::k_poly_ntt<LOGN>, (unsigned)(npoly * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, src, stride, W, out, c->dt, D);
+  }
+  static void ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, unsigned ginv, const uint64_t *evk,
+                      uint64_t *chat, unsigned D, unsigned batch) {
+    want_smem(hbdev::k_ks_limb<LOGN>, 2 * G::SMEM_BYTES);
+    launch(c, hbdev::k_ks_limb<LOGN>, (unsigned)((size_t)batch * D * G::C), G::THREADS, 2 * G::SMEM_BYTES, G::C, src, bstride, W,
+           ginv, evk, c->ht.dimevk, chat, c->dt, D);
+  }
+  static void mulpt_limb(hb_ctx *c, const uint64_t *ct, int W, const uint64_t *pthat, uint64_t *chat, unsigned D, unsigned batch) {
+    want_smem(hbdev::k_mulpt_limb<LOGN>, G::SMEM_BYTES);
+    launch(c, hbdev::k_mulpt_limb<LOGN>, (unsigned)((size_t)batch * 2 * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, ct, W, pthat,
+           chat, c->dt, D);
+  }
+  static void tensor_intt(hb_ctx *c, const uint64_t *hatA, const uint64_t *hatB, uint64_t *dhat, unsigned D, unsigned batch) {
+    want_smem(hbdev::k_tensor_intt<LOGN>, G::SMEM_BYTES);
+    launch(c, hbdev::k_tensor_intt<LOGN>, (unsigned)((size_t)batch * 3 * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, hatA, hatB, dhat, c->dt, D);
+  }
+};
+
+static void do_ntt_fwd(hb_ctx *c, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D, bool strict) {
+#define X(L) case L: Launch<L>::ntt_fwd(c, in, out, nlimbs, d0, D, strict); break;
+  switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
+#undef X
+}
+static void do_ntt_inv(hb_ctx *c, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D) {
+#define X(L) case L: Launch<L>::ntt_inv(c, in, out, nlimbs, d0, D); break;
+  switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
+#undef X
+}
+static void do_poly_ntt(hb_ctx *c, const uint64_t *src, size_t stride, int W, uint64_t *out, unsigned D, size_t npoly) {
+#define X(L) case L: Launch<L>::poly_ntt(c, src, stride, W, out, D, npoly); break;
+  switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
+#undef X
+}
+static void do_ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, unsigned ginv, const uint64_t *evk,
+                       uint64_t *chat, unsigned D, unsigned batch) {
+#define X(L) case L: Launch<L>::ks_limb(c, src, bstride, W, ginv, evk, chat, D, batch); break;
+  switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
+#undef X
+}
+static void do_mulpt_limb(hb_ctx *c, const uint64_t *ct, int W, const uint64_t *pthat, uint64_t *chat, unsigned D, unsigned batch) {
+#define X(L) case L: Launch<L>::mulpt_limb(c, ct, W, pthat, chat, D, batch); break;
+  switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
+#undef X
+}
+static void do_tensor_intt(hb_ctx *c, const uint64_t *hatA, const uint64_t *hatB, uint64_t *dhat, unsigned D, unsigned batch) {
+#define X(L) case L: Launch<L>::tensor_intt(c, hatA, hatB, dhat, D, batch); break;
+  switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
+#undef X
+}
+
+static int wk_class(unsigned wk) { return wk <= 1 ? 1 : wk <= 2 ? 2 : wk <= 4 ? 4 : wk <= 8 ? 8 : 16; }
+static int wp_class(unsigned wp) { return wp <= 4 ? 4 : wp <= 8 ? 8 : wp <= 12 ? 12 : 20; }
+
+static void do_recon_smod(hb_ctx *c, const uint64_t *chat, unsigned D, uint64_t *out, int Wout, int k, size_t npoly) {
+  const unsigned threads = 128;
+  const size_t total = npoly * c->ht.N;
+  const unsigned grid = (unsigned)((total + threads - 1) / threads);
+  const unsigned wk = (k + 63) / 64;
+  switch (wk_class(wk)) {
+#define X(WKC) case WKC: launch(c, hbdev::k_recon_smod<WKC>, grid, threads, 0, 1, chat, D, out, Wout, k, c->dt, (unsigned)npoly); break;
+    X(1) X(2) X(4) X(8) X(16)
+#undef X
+  }
+}
+
+template <int WKC>
+static void ks_finish_wp(hb_ctx *c, unsigned grid, unsigned threads, const uint64_t *chat, unsigned D, const uint64_t *add0,
+                         const uint64_t *add1, size_t add_bstride, int Wadd, unsigned ginv, uint64_t *out, int Wout, int k,
+                         unsigned batch) {
+  switch (wp_class(c->ht.WP)) {
+#define X(WPC) case WPC: launch(c, hbdev::k_ks_finish<WKC, WPC>, grid, threads, 0, 1, chat, D, add0, add1, add_bstride, Wadd, ginv, out, Wout, k, c->dt, batch); break;
+    X(4) X(8) X(12) X(20)
+#undef X
+  }
+}
+
+static void do_ks_finish(hb_ctx *c, const uint64_t *chat, unsigned D, const uint64_t *add0, const uint64_t *add1,
+                         size_t add_bstride, int Wadd, unsigned ginv, uint64_t *out, int Wout, int k, unsigned batch) {
+  const unsigned threads = 128;
+  const size_t total = (size_t)batch * 2 * c->ht.N;
+  const unsigned grid = (unsigned)((total + threads - 1) / threads);
+  const unsigned wk = (k + 63) / 64;
+  switch (wk_class(wk)) {
+#define X(WKC) case WKC: ks_finish_wp<WKC>(c, grid, threads, chat, D, add0, add1, add_bstride, Wadd, ginv, out, Wout, k, batch); break;
+    X(1) X(2) X(4) X(8) X(16)
+#undef X
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------------------------------------
+template <class T>
+static T *upload_vec(hb_ctx *ctx, const std::vector<T> &v) {
+  void *d = nullptr;
+  size_t bytes = v.size() * sizeof(T);
+  CUDA_OK(cudaMalloc(&d, bytes ? bytes : 8));
+  if (bytes) CUDA_OK(cudaMemcpy(d, v.data(), bytes, cudaMemcpyHostToDevice));
+  ctx->table_allocs.push_back(d);
+  return (T *)d;
+}
+
+extern "C" hb_ctx *hb_ctx_create(unsigned logn, unsigned logq, unsigned slots, unsigned logDelta, int device) {
+  hb_ctx *ctx = new hb_ctx();
+  std::string err = hb::build_tables(ctx->ht, logn, logq, slots, logDelta);
+  if (!err.empty()) hb_die("Invalid argument. %s", err.c_str());
+  if (ctx->ht.WC > 16) hb_die("log2(q)=%u needs more than 16 words per coefficient", logq);
+  if (ctx->ht.WP > 20) hb_die("special modulus P of %u bits is too wide for this build", ctx->ht.nbitsP);
+  {
+    bool ok = false;
+#define X(L) if (logn == L) ok = true;
+    HB_LOGN_CASES(X)
+#undef X
+    if (!ok) hb_die("logn=%u is not built into this library", logn);
+  }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    hb_die("no CUDA device: this engine has no CPU fallback (%s)", e == cudaSuccess ? "0 devices" : cudaGetErrorString(e));
+  if (device < 0 || device >= ndev) hb_die("device %d out of range (have %d)", device, ndev);
+  ctx->device = device;
+  CUDA_OK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CUDA_OK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) hb_die("device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+  ctx->sm_count = prop.multiProcessorCount;
+  CUDA_OK(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+  ctx->stream = ctx->own_stream;
+  CUDA_OK(cudaEventCreate(&ctx->ev0));
+  CUDA_OK(cudaEventCreate(&ctx->ev1));
+  const hb::HostTables &h = ctx->ht;
+  static_assert(sizeof(hb::PrimeConsts) == sizeof(hbdev::PrimeConsts), "PrimeConsts layout");
+  Tables &t = ctx->dt;
+  t.primes = (const hbdev::PrimeConsts *)upload_vec(ctx, h.primes);
+  t.tw = (const ulonglong2 *)upload_vec(ctx, h.tw);
+  t.itw = (const ulonglong2 *)upload_vec(ctx, h.itw);
+  t.pow64 = upload_vec(ctx, h.pow64);
+  t.crt_inv = upload_vec(ctx, h.crt_inv);
+  t.crt_inv_q = upload_vec(ctx, h.crt_inv_q);
+  t.crt_phat = upload_vec(ctx, h.crt_phat);
+  t.crt_P = upload_vec(ctx, h.crt_P);
+  t.ks_inv = upload_vec(ctx, h.ks_inv);
+  t.ks_inv_q = upload_vec(ctx, h.ks_inv_q);
+  t.ks_phat = upload_vec(ctx, h.ks_phat);
+  t.ks_P = upload_vec(ctx, h.ks_P);
+  t.ks_Ph = upload_vec(ctx, h.ks_Ph);
+  t.ks_Pinv = upload_vec(ctx, h.ks_Pinv);
+  t.N = h.N; t.logn = h.logn; t.dimub = h.dimub; t.WC = h.WC; t.WP = h.WP; t.dim = h.dim;
+  ctx->ring = hb_ring_create(logn);
+  ctx->enc_host.assign((size_t)h.WC * h.N, 0);
+  return ctx;
+}
+
+extern "C" void hb_ctx_destroy(hb_ctx *ctx) {
+  if (!ctx) return;
+  CUDA_OK(cudaSetDevice(ctx->device));
+  cudaStreamSynchronize(ctx->stream);
+  for (void *p : ctx->table_allocs) cudaFree(p);
+  for (auto &kv : ctx->pool) cudaFree(kv.second);
+  for (auto &kv : ctx->live) cudaFree(kv.first);
+  for (auto &pl : ctx->plans) cudaFree(pl.pthat);
+  cudaFree(ctx->wsA);
+  cudaFree(ctx->wsB);
+  cudaEventDestroy(ctx->ev0);
+  cudaEventDestroy(ctx->ev1);
+  cudaStreamDestroy(ctx->own_stream);
+  hb_ring_destroy(ctx->ring);
+  delete ctx;
+}
+
+static void fill_info(const hb::HostTables &h, hb_info *o);
+extern "C" void hb_ctx_info(const hb_ctx *ctx, hb_info *o) {
+  fill_info(ctx->ht, o);
+  o->device = ctx->device; o->sm_count = ctx->sm_count;
+}
+static void check_level(const hb_ctx *ctx, unsigned l) {
+  if (l > ctx->ht.L) hb_die("level %u out of range (L=%u)", l, ctx->ht.L);
+}
+extern "C" unsigned hb_ctx_words(const hb_ctx *ctx, unsigned l) { check_level(ctx, l); return hb::words_of_level(ctx->ht, l); }
+extern "C" unsigned hb_ctx_logq(const hb_ctx *ctx, unsigned l) { check_level(ctx, l); return ctx->ht.logq_l[l]; }
+extern "C" void hb_ctx_primes(const hb_ctx *ctx, uint64_t *out) {
+  for (unsigned d = 0; d < ctx->ht.dimub; d++) out[d] = ctx->ht.primes[d].p;
+}
+extern "C" void hb_ctx_twiddles(const hb_ctx *ctx, unsigned d, int inverse, uint64_t *out) {
+  if (d >= ctx->ht.dimub) hb_die("prime index %u out of range", d);
+  const std::vector<uint64_t> &src = inverse ? ctx->ht.itw : ctx->ht.tw;
+  for (unsigned i = 0; i < ctx->ht.N; i++) out[i] = src[((size_t)d * ctx->ht.N + i) * 2];
+}
+extern "C" unsigned hb_dim_keyswitch(const hb_ctx *ctx, unsigned l) { check_level(ctx, l); return hb::dim_keyswitch(ctx->ht, l); }
+extern "C" unsigned hb_dim_mul(const hb_ctx *ctx, unsigned l) { check_level(ctx, l); return hb::dim_mul(ctx->ht, l); }
+extern "C" unsigned hb_dim_mulpt(const hb_ctx *ctx, unsigned l, double nu) { check_level(ctx, l); return hb::dim_mulpt(ctx->ht, l, nu); }
+extern "C" void hb_ctx_set_stream(hb_ctx *ctx, void *s) { ctx->stream = s ? (cudaStream_t)s : ctx->own_stream; }
+extern "C" void hb_sync(hb_ctx *ctx) { CUDA_OK(cudaStreamSynchronize(ctx->stream)); }
+extern "C" void hb_timer_start(hb_ctx *ctx) { CUDA_OK(cudaEventRecord(ctx->ev0, ctx->stream)); }
+extern "C" float hb_timer_stop_ms(hb_ctx *ctx) {
+  CUDA_OK(cudaEventRecord(ctx->ev1, ctx->stream));
+  CUDA_OK(cudaEventSynchronize(ctx->ev1));
+  float ms = 0;
+  CUDA_OK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+  return ms;
+}
+extern "C" uint64_t hb_launch_count(const hb_ctx *ctx) { return ctx->launches; }
+
+// ---------------------------------------------------------------------------------------------------------
+// host-only tables view
+// ---------------------------------------------------------------------------------------------------------
+struct hb_tables {
+  hb::HostTables ht;
+  hb_ring *ring = nullptr;
+};
+extern "C" hb_tables *hb_tables_create(unsigned logn, unsigned logq, unsigned slots, unsigned logDelta) {
+  hb_tables *t = new hb_tables();
+  std::string err = hb::build_tables(t->ht, logn, logq, slots, logDelta);
+  if (!err.empty()) {
+    fprintf(stderr, "\033[1m\033[31merror:\033[0m \033[1mhectr_b200\033[0m. Invalid argument. %s\n", err.c_str());
+    delete t;
+    return nullptr;
+  }
+  t->ring = hb_ring_create(logn);
+  return t;
+}
+extern "C" void hb_tables_destroy(hb_tables *t) { if (t) { hb_ring_destroy(t->ring); delete t; } }
+static void fill_info(const hb::HostTables &h, hb_info *o) {
+  o->logn = h.logn; o->n = h.N; o->logq = h.logq; o->logDelta = h.logDelta; o->slots = h.slots;
+  o->L = h.L; o->dim = h.dim; o->dimevk = h.dimevk; o->dimub = h.dimub; o->words_top = h.WC;
+  o->nbitsP = h.nbitsP; o->nbitsPqL = h.nbitsPqL; o->device = -1; o->sm_count = 0;
+}
+extern "C" void hb_tables_info(const hb_tables *t, hb_info *o) { fill_info(t->ht, o); }
+extern "C" void hb_tables_primes(const hb_tables *t, uint64_t *out) {
+  for (unsigned d = 0; d < t->ht.dimub; d++) out[d] = t->ht.primes[d].p;
+}
+extern "C" void hb_tables_twiddles(const hb_tables *t, unsigned d, int inverse, uint64_t *out) {
+  if (d >= t->ht.dimub) hb_die("prime index %u out of range", d);
+  const std::vector<uint64_t> &src = inverse ? t->ht.itw : t->ht.tw;
+  for (unsigned i = 0; i < t->ht.N; i++) out[i] = src[((size_t)d * t->ht.N + i) * 2];
+}
+extern "C" void hb_tables_crt(const hb_tables *t, unsigned D, uint64_t *inv, uint64_t *phat_low, uint64_t *P_low) {
+  const hb::HostTables &h = t->ht;
+  if (D == 0 || D > h.dimub) hb_die("limb count %u outside the prime chain (%u)", D, h.dimub);
+  for (unsigned d = 0; d < D; d++) {
+    inv[d] = h.crt_inv[(size_t)D * h.dimub + d];
+    for (unsigned w = 0; w < h.WC; w++) phat_low[(size_t)d * h.WC + w] = h.crt_phat[((size_t)D * h.dimub + d) * h.WC + w];
+  }
+  for (unsigned w = 0; w < h.WC; w++) P_low[w] = h.crt_P[(size_t)D * h.WC + w];
+}
+extern "C" unsigned hb_tables_dim(const hb_tables *t, int which, unsigned l, double nu) {
+  if (l > t->ht.L) hb_die("level %u out of range (L=%u)", l, t->ht.L);
+  return which == 0 ? hb::dim_keyswitch(t->ht, l) : which == 1 ? hb::dim_mul(t->ht, l) : hb::dim_mulpt(t->ht, l, nu);
+}
+extern "C" void hb_tables_encode(const hb_tables *t, const double *m, double Delta, uint64_t *words) {
+  hb_ring_encode(t->ring, t->ht.slots, m, Delta, words, t->ht.WC);
+}
+extern "C" void hb_tables_decode(const hb_tables *t, const uint64_t *words, unsigned W, double Delta, double *m) {
+  hb_ring_decode(t->ring, t->ht.slots, words, W, Delta, m);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// raw memory
+// ---------------------------------------------------------------------------------------------------------
+extern "C" void *hb_dev_alloc(hb_ctx *ctx, size_t bytes) {
+  CUDA_OK(cudaSetDevice(ctx->device));
+  void *p = nullptr;
+  CUDA_OK(cudaMalloc(&p, bytes ? bytes : 8));
+  return p;
+}
+extern "C" void hb_dev_free(hb_ctx *ctx, void *p) {
+  if (!p) return;
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  CUDA_OK(cudaFree(p));
+}
+extern "C" void *hb_host_alloc(hb_ctx *ctx, size_t bytes) {
+  (void)ctx;
+  void *p = nullptr;
+  CUDA_OK(cudaMallocHost(&p, bytes ? bytes : 8));
+  return p;
+}
+extern "C" void hb_host_free(hb_ctx *ctx, void *p) { (void)ctx; if (p) CUDA_OK(cudaFreeHost(p)); }
+extern "C" void hb_h2d(hb_ctx *ctx, void *dst, const void *src, size_t bytes) {
+  CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+}
+extern "C" void hb_d2h(hb_ctx *ctx, void *dst, const void *src, size_t bytes) {
+  CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+}
+extern "C" void hb_dev_fill(hb_ctx *ctx, void *dst, int byte, size_t bytes) {
+  CUDA_OK(cudaMemsetAsync(dst, byte, bytes, ctx->stream));
+}
+
+static uint64_t *pool_get(hb_ctx *ctx, size_t bytes) {
+  auto it = ctx->pool.find(bytes);
+  uint64_t *p;
+  if (it != ctx->pool.end()) { p = it->second; ctx->pool.erase(it); }
+  else { void *q = nullptr; CUDA_OK(cudaMalloc(&q, bytes)); p = (uint64_t *)q; }
+  ctx->live[p] = bytes;
+  return p;
+}
+static void pool_put(hb_ctx *ctx, uint64_t *p) {
+  if (!p) return;
+  auto it = ctx->live.find(p);
+  if (it == ctx->live.end()) hb_die("freeing a ciphertext buffer this context does not own");
+  ctx->pool.insert({it->second, p});
+  ctx->live.erase(it);
+}
+static uint64_t *ws_get(hb_ctx *ctx, uint64_t *&ws, size_t &cur, size_t bytes) {
+  if (bytes > cur) {
+    if (ws) { CUDA_OK(cudaStreamSynchronize(ctx->stream)); CUDA_OK(cudaFree(ws)); }
+    void *q = nullptr;
+    CUDA_OK(cudaMalloc(&q, bytes));
+    ws = (uint64_t *)q;
+    cur = bytes;
+  }
+  return ws;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// containers
+// ---------------------------------------------------------------------------------------------------------
+static size_t ct_capacity(const hb_ctx *ctx, unsigned batch) { return (size_t)batch * 2 * ctx->ht.WC * ctx->ht.N * 8; }
+static size_t ct_words(const hb_ctx *ctx, const hb_ct *ct) { return (size_t)ct->batch * 2 * hb::words_of_level(ctx->ht, ct->l) * ctx->ht.N; }
+
+extern "C" void hb_ct_alloc(hb_ctx *ctx, hb_ct *ct, unsigned batch) {
+  if (batch == 0) hb_die("a ciphertext handle must hold at least one instance");
+  CUDA_OK(cudaSetDevice(ctx->device));
+  ct->l = ctx->ht.L; ct->nu = 0; ct->B = 0; ct->batch = batch;
+  ct->words = pool_get(ctx, ct_capacity(ctx, batch));
+  CUDA_OK(cudaMemsetAsync(ct->words, 0, ct_capacity(ctx, batch), ctx->stream));   // gcry_mpi_new(0) == 0
+}
+extern "C" void hb_ct_free(hb_ctx *ctx, hb_ct *ct) {
+  pool_put(ctx, ct->words);
+  ct->words = nullptr; ct->batch = 0;
+}
+static void need_ct(const hb_ct *ct, const char *what) {
+  if (!ct || !ct->words) hb_die("%s: ciphertext handle is not allocated", what);
+}
+extern "C" void hb_ct_copy(hb_ctx *ctx, hb_ct *dst, const hb_ct *src) {
+  need_ct(dst, "hb_ct_copy"); need_ct(src, "hb_ct_copy");
+  if (dst->batch != src->batch) hb_die("hb_ct_copy: batch mismatch (%u vs %u)", dst->batch, src->batch);
+  dst->l = src->l; dst->nu = src->nu; dst->B = src->B;
+  if (dst->words != src->words)
+    CUDA_OK(cudaMemcpyAsync(dst->words, src->words, ct_words(ctx, src) * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+}
+extern "C" void hb_ct_upload(hb_ctx *ctx, hb_ct *ct, const uint64_t *host, unsigned l, double nu, double B) {
+  need_ct(ct, "hb_ct_upload"); check_level(ctx, l);
+  ct->l = l; ct->nu = nu; ct->B = B;
+  CUDA_OK(cudaMemcpyAsync(ct->words, host, ct_words(ctx, ct) * 8, cudaMemcpyHostToDevice, ctx->stream));
+}
+extern "C" void hb_ct_download(hb_ctx *ctx, const hb_ct *ct, uint64_t *host) {
+  need_ct(ct, "hb_ct_download");
+  CUDA_OK(cudaMemcpyAsync(host, ct->words, ct_words(ctx, ct) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+}
+extern "C" void hb_pt_alloc(hb_ctx *ctx, hb_pt *pt) {
+  pt->nu = 0;
+  pt->words = (uint64_t *)hb_dev_alloc(ctx, (size_t)ctx->ht.WC * ctx->ht.N * 8);
+  CUDA_OK(cudaMemsetAsync(pt->words, 0, (size_t)ctx->ht.WC * ctx->ht.N * 8, ctx->stream));
+}
+extern "C" void hb_pt_free(hb_ctx *ctx, hb_pt *pt) { hb_dev_free(ctx, pt->words); pt->words = nullptr; }
+extern "C" void hb_pt_upload(hb_ctx *ctx, hb_pt *pt, const uint64_t *host, double nu) {
+  if (!pt->words) hb_die("hb_pt_upload: plaintext handle is not allocated");
+  pt->nu = nu;
+  CUDA_OK(cudaMemcpyAsync(pt->words, host, (size_t)ctx->ht.WC * ctx->ht.N * 8, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+}
+extern "C" void hb_evk_upload(hb_ctx *ctx, hb_evk *evk, const uint64_t *p0, const uint64_t *p1) {
+  const size_t half = (size_t)ctx->ht.dimevk * ctx->ht.N;
+  evk->p = (uint64_t *)hb_dev_alloc(ctx, 2 * half * 8);
+  CUDA_OK(cudaMemcpyAsync(evk->p, p0, half * 8, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_OK(cudaMemcpyAsync(evk->p + half, p1, half * 8, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+}
+extern "C" void hb_evk_free(hb_ctx *ctx, hb_evk *evk) { hb_dev_free(ctx, evk->p); evk->p = nullptr; }
+
+// ---------------------------------------------------------------------------------------------------------
+// encode / decode
+// ---------------------------------------------------------------------------------------------------------
+extern "C" void hb_encode(const hb_ctx *ctx, const double *m, double Delta, uint64_t *words) {
+  hb_ring_encode(ctx->ring, ctx->ht.slots, m, Delta, words, ctx->ht.WC);
+}
+extern "C" void hb_decode(const hb_ctx *ctx, const uint64_t *words, unsigned W, double Delta, double *m) {
+  hb_ring_decode(ctx->ring, ctx->ht.slots, words, W, Delta, m);
+}
+extern "C" void hb_he_ecd(hb_ctx *ctx, hb_pt *pt, const double *m) {
+  if (!pt->words) hb_die("hb_he_ecd: plaintext handle is not allocated");
+  // he_ecd writes 2*slots coefficients and keeps the rest (he-encode.c:58-63): read-modify-write
+  const size_t bytes = (size_t)ctx->ht.WC * ctx->ht.N * 8;
+  CUDA_OK(cudaMemcpyAsync(ctx->enc_host.data(), pt->words, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  const double Delta = std::ldexp(1.0, (int)ctx->ht.logDelta);
+  hb_ring_encode(ctx->ring, ctx->ht.slots, m, Delta, ctx->enc_host.data(), ctx->ht.WC);
+  hb_pt_upload(ctx, pt, ctx->enc_host.data(), Delta);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// evaluation
+// ---------------------------------------------------------------------------------------------------------
+static void same_shape(const hb_ct *a, const hb_ct *b, const char *what) {
+  need_ct(a, what); need_ct(b, what);
+  if (a->batch != b->batch) hb_die("%s: batch mismatch (%u vs %u)", what, a->batch, b->batch);
+}
+
+static void addsub(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b, int op, const char *what) {
+  same_shape(a, b, what); same_shape(ct, a, what);
+  if (a->l != b->l) hb_die("%s: operands are at different levels (%u vs %u)", what, a->l, b->l);   // assert, he-add.c:35
+  ct->l = a->l;
+  ct->nu = (a->nu >= b->nu) ? a->nu : b->nu;
+  ct->B = a->B + b->B;
+  const int W = hb::words_of_level(ctx->ht, ct->l), k = ctx->ht.logq_l[ct->l];
+  const size_t npoly = (size_t)ct->batch * 2, total = npoly * ctx->ht.N;
+  launch(ctx, hbdev::k_ct_addsub, (unsigned)((total + 255) / 256), 256, 0, 1, a->words, b->words, ct->words, W, k, op, ctx->ht.N, npoly);
+}
+extern "C" void hb_he_add(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b) { addsub(ctx, ct, a, b, 0, "hb_he_add"); }
+extern "C" void hb_he_sub(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b) { addsub(ctx, ct, a, b, 1, "hb_he_sub"); }
+extern "C" void hb_he_neg(hb_ctx *ctx, hb_ct *ct) {
+  need_ct(ct, "hb_he_neg");
+  const int W = hb::words_of_level(ctx->ht, ct->l), k = ctx->ht.logq_l[ct->l];
+  const size_t npoly = (size_t)ct->batch * 2, total = npoly * ctx->ht.N;
+  launch(ctx, hbdev::k_ct_addsub, (unsigned)((total + 255) / 256), 256, 0, 1, ct->words, (const uint64_t *)nullptr, ct->words, W, k, 2,
+         ctx->ht.N, npoly);
+}
+
+static void rescale_like(hb_ctx *ctx, hb_ct *ct, int shift, const char *what) {
+  need_ct(ct, what);
+  if (ct->l == 0) hb_die("%s: ciphertext is already at level 0", what);
+  const int Win = hb::words_of_level(ctx->ht, ct->l);
+  ct->l -= 1;
+  const int Wout = hb::words_of_level(ctx->ht, ct->l), kout = ctx->ht.logq_l[ct->l];
+  uint64_t *out = pool_get(ctx, ct_capacity(ctx, ct->batch));
+  const size_t npoly = (size_t)ct->batch * 2, total = npoly * ctx->ht.N;
+  launch(ctx, hbdev::k_ct_rescale, (unsigned)((total + 255) / 256), 256, 0, 1, ct->words, out, Win, Wout, shift, kout, ctx->ht.N, npoly);
+  pool_put(ctx, ct->words);
+  ct->words = out;
+}
+extern "C" void hb_he_rs(hb_ctx *ctx, hb_ct *ct) {
+  need_ct(ct, "hb_he_rs");
+  const double Delta = std::ldexp(1.0, (int)ctx->ht.logDelta);
+  const double n = ctx->ht.N, Brs = std::sqrt(n / 3.) * (3 + 8 * std::sqrt(64.0));   // precomp.c:417
+  ct->nu /= Delta;
+  ct->B = ct->B / Delta + Brs;
+  rescale_like(ctx, ct, (int)ctx->ht.logDelta, "hb_he_rs");
+}
+extern "C" void hb_he_moddown(hb_ctx *ctx, hb_ct *ct) { rescale_like(ctx, ct, 0, "hb_he_moddown"); }
+
+// pthat[D][N] -> chat -> dst   (shared by hb_he_mulpt and the gemv plan)
+static void mulpt_with_hat(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const uint64_t *pthat, unsigned D, double ptnu) {
+  const int W = hb::words_of_level(ctx->ht, src->l), k = ctx->ht.logq_l[src->l];
+  uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, (size_t)src->batch * 2 * D * ctx->ht.N * 8);
+  do_mulpt_limb(ctx, src->words, W, pthat, chat, D, src->batch);
+  dst->l = src->l;
+  const double nu = src->nu, B = src->B;
+  dst->nu = nu * ptnu;
+  dst->B = B * ptnu;
+  do_recon_smod(ctx, chat, D, dst->words, W, k, (size_t)src->batch * 2);
+}
+
+extern "C" void hb_he_mulpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt) {
+  same_shape(dst, src, "hb_he_mulpt");
+  if (!pt || !pt->words) hb_die("hb_he_mulpt: plaintext handle is not allocated");
+  const unsigned D = hb::dim_mulpt(ctx->ht, src->l, pt->nu);
+  if (D == 0 || D > ctx->ht.dimub) hb_die("hb_he_mulpt: limb count %u outside the prime chain (%u)", D, ctx->ht.dimub);
+  uint64_t *pthat = ws_get(ctx, ctx->wsB, ctx->wsB_bytes, (size_t)D * ctx->ht.N * 8);
+  do_poly_ntt(ctx, pt->words, (size_t)ctx->ht.WC * ctx->ht.N, ctx->ht.WC, pthat, D, 1);
+  mulpt_with_hat(ctx, dst, src, pthat, D, pt->nu);
+}
+
+static unsigned pow5_inv_mod_2n(const hb_ctx *ctx, unsigned rot) {
+  const unsigned m = 2 * ctx->ht.N;
+  unsigned g = 1;
+  for (unsigned j = 0; j < rot; j++) g = (unsigned)(((uint64_t)g * 5u) % m);   // poly.c:265-268
+  // inverse of an odd number modulo a power of two (Newton)
+  unsigned x = g;
+  for (int i = 0; i < 5; i++) x *= 2 - g * x;
+  return x & (m - 1);
+}
+
+// he_swk with the automorphism ginv; add1 = true adds sigma(c1) too (he_relin's d1), he_swk does not.
+static void keyswitch_inplace(hb_ctx *ctx, hb_ct *ct, unsigned ginv, const hb_evk *key, const char *what) {
+  need_ct(ct, what);
+  if (!key || !key->p) hb_die("%s: evaluation key is not loaded", what);
+  const hb::HostTables &h = ctx->ht;
+  const unsigned D = hb::dim_keyswitch(h, ct->l);
+  if (D > h.dimevk) hb_die("%s: needs %u limbs but keys hold %u", what, D, h.dimevk);
+  const int W = hb::words_of_level(h, ct->l), k = h.logq_l[ct->l];
+  const size_t bstride = (size_t)2 * W * h.N;
+  uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, (size_t)ct->batch * 2 * D * h.N * 8);
+  do_ks_limb(ctx, ct->words + (size_t)W * h.N, bstride, W, ginv, key->p, chat, D, ct->batch);
+  uint64_t *out = pool_get(ctx, ct_capacity(ctx, ct->batch));
+  do_ks_finish(ctx, chat, D, ct->words, nullptr, bstride, W, ginv, out, W, k, ct->batch);
+  pool_put(ctx, ct->words);
+  ct->words = out;
+}
+
+extern "C" void hb_he_rot(hb_ctx *ctx, hb_ct *ct, int rot, const hb_evk *rk) {
+  if (rot < 0 || (unsigned)rot >= ctx->ht.slots) hb_die("hb_he_rot: rotation %d outside [0,%u)", rot, ctx->ht.slots);
+  keyswitch_inplace(ctx, ct, pow5_inv_mod_2n(ctx, (unsigned)rot), &rk[rot], "hb_he_rot");
+}
+extern "C" void hb_he_conj(hb_ctx *ctx, hb_ct *ct, const hb_evk *ck) {
+  keyswitch_inplace(ctx, ct, 2 * ctx->ht.N - 1, ck, "hb_he_conj");
+}
+
+extern "C" void hb_he_mul(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b, const hb_evk *rlk) {
+  same_shape(a, b, "hb_he_mul"); same_shape(ct, a, "hb_he_mul");
+  if (a->l != b->l) hb_die("hb_he_mul: operands are at different levels (%u vs %u)", a->l, b->l);   // assert, he-mult.c:90
+  if (!rlk || !rlk->p) hb_die("hb_he_mul: relinearisation key is not loaded");
+  const hb::HostTables &h = ctx->ht;
+  const unsigned l = a->l, batch = a->batch;
+  const unsigned Dm = hb::dim_mul(h, l), Dk = hb::dim_keyswitch(h, l);
+  if (Dm > h.dimub || Dk > h.dimevk) hb_die("hb_he_mul: limb count outside the prime chain");
+  const int W = hb::words_of_level(h, l), k = h.logq_l[l];
+  const size_t N = h.N, polyw = (size_t)W * N;
+  // workspace A: hat[b][4][Dm][N] then (reused) key-switch chat[b][2][Dk][N]; B: dhat[b][3][Dm][N] + d[b][3][W][N]
+  const size_t hat_words = (size_t)batch * 4 * Dm * N, chat_words = (size_t)batch * 2 * Dk * N;
+  uint64_t *wsA = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, (hat_words > chat_words ? hat_words : chat_words) * 8);
+  const size_t dhat_words = (size_t)batch * 3 * Dm * N, d_words = (size_t)batch * 3 * polyw;
+  uint64_t *wsB = ws_get(ctx, ctx->wsB, ctx->wsB_bytes, (dhat_words + d_words) * 8);
+  uint64_t *hat = wsA, *dhat = wsB, *dpoly = wsB + dhat_words;
+  // 4 forward transforms per limb: hatA[b][0..1] from a, hatB[b][0..1] from b
+  uint64_t *hatA = hat, *hatB = hat + hat_words / 2;
+  do_poly_ntt(ctx, a->words, polyw, W, hatA, Dm, (size_t)batch * 2);
+  do_poly_ntt(ctx, b->words, polyw, W, hatB, Dm, (size_t)batch * 2);
+  do_tensor_intt(ctx, hatA, hatB, dhat, Dm, batch);
+  do_recon_smod(ctx, dhat, Dm, dpoly, W, k, (size_t)batch * 3);      // d0,d1,d2 mod q_l  (he-mult.c:140-142)
+  // relinearise d2 with rlk, add d0 and d1 (he-mult.c:40-85)
+  uint64_t *chat = wsA;
+  do_ks_limb(ctx, dpoly + 2 * polyw, 3 * polyw, W, 1u, rlk->p, chat, Dk, batch);
+  const double nu1 = a->nu, nu2 = b->nu, B1 = a->B, B2 = b->B;
+  ct->l = l;
+  ct->nu = nu1 * nu2;
+  {
+    // bnd.Bmult[l] = Pinv*q_l*Bks + Brs (precomp.c:411-429) -- metadata only
+    long double Pinv = 1;
+    for (unsigned d = 0; d < h.dimub; d++) Pinv *= 1. / h.primes[d].p;
+    const double sigma = 3.1915382432114616, n = h.N;
+    const double Bks = 8 * sigma * n / std::sqrt(3.0), Brs = std::sqrt(n / 3.) * (3 + 8 * std::sqrt(64.0));
+    long double Pinvql = Pinv * (long double)std::ldexp(1.0, (int)h.logq_l[0]);
+    for (unsigned j = 1; j <= l; j++) Pinvql = Pinvql * std::ldexp(1.0, (int)h.logDelta);
+    ct->B = nu1 * B2 + nu2 * B1 + B1 * B2 + (double)(Pinvql * Bks + Brs);
+  }
+  do_ks_finish(ctx, chat, Dk, dpoly, dpoly + polyw, 3 * polyw, W, 1u, ct->words, W, k, batch);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// he_gemv (he-algo.c:47-93)
+// ---------------------------------------------------------------------------------------------------------
+static const GemvPlan &gemv_plan(hb_ctx *ctx, const double *A, unsigned l) {
+  const hb::HostTables &h = ctx->ht;
+  const unsigned S = h.slots;
+  const size_t nA = (size_t)S * S * 2;
+  for (const GemvPlan &p : ctx->plans)
+    if (p.l == l && memcmp(p.A.data(), A, nA * sizeof(double)) == 0) return p;
+  if (ctx->plans.size() >= 8) {   // small LRU: drop the oldest
+    CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    cudaFree(ctx->plans.front().pthat);
+    ctx->plans.erase(ctx->plans.begin());
+  }
+  GemvPlan plan;
+  plan.A.assign(A, A + nA);
+  plan.l = l;
+  const double Delta = std::ldexp(1.0, (int)h.logDelta);
+  plan.D = hb::dim_mulpt(h, l, Delta);
+  if (plan.D == 0 || plan.D > h.dimub) hb_die("hb_he_gemv: limb count %u outside the prime chain", plan.D);
+  unsigned n1 = (unsigned)std::sqrt((double)S);
+  if (S != n1 * n1) n1 = (unsigned)std::sqrt((double)(2 * S));
+  const unsigned n2 = S / n1;
+  // encode all diagonals on the host in the reference's order; the single he_pt_t it reuses keeps stale
+  // coefficients only at indices every encode overwrites (SURVEY hazard 11), so a zeroed buffer is equivalent.
+  const size_t ptw = (size_t)h.WC * h.N;
+  std::vector<uint64_t> host((size_t)S * ptw, 0);
+  std::vector<double> diag(2 * S), rd(2 * S);
+  for (unsigned i = 0; i < n2; i++) {
+    const int shift = (int)(i * n1);
+    for (unsigned j = 0; j < n1; j++) {
+      const unsigned idx = shift + j;
+      for (unsigned r = 0; r < S; r++) {             // zrotdiag, he-algo.c:29-43
+        const size_t src = ((size_t)(r % S) * S + (idx + r) % S) * 2;
+        diag[2 * r] = A[src]; diag[2 * r + 1] = A[src + 1];
+      }
+      for (unsigned r = 0; r < S; r++) {
+        int ri = ((int)r - shift) % (int)S;
+        if (ri < 0) ri += S;
+        rd[2 * r] = diag[2 * ri]; rd[2 * r + 1] = diag[2 * ri + 1];
+      }
+      hb_ring_encode(ctx->ring, S, rd.data(), Delta, host.data() + (size_t)idx * ptw, h.WC);
+    }
+  }
+  uint64_t *dpt = (uint64_t *)hb_dev_alloc(ctx, host.size() * 8);
+  CUDA_OK(cudaMemcpyAsync(dpt, host.data(), host.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+  plan.pthat = (uint64_t *)hb_dev_alloc(ctx, (size_t)S * plan.D * h.N * 8);
+  do_poly_ntt(ctx, dpt, ptw, h.WC, plan.pthat, plan.D, S);
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  CUDA_OK(cudaFree(dpt));
+  ctx->plans.push_back(std::move(plan));
+  return ctx->plans.back();
+}
+
+extern "C" void hb_he_gemv(hb_ctx *ctx, hb_ct *dst, const double *A, const hb_ct *ct, const hb_evk *rk) {
+  same_shape(dst, ct, "hb_he_gemv");
+  const hb::HostTables &h = ctx->ht;
+  const unsigned S = h.slots;
+  const GemvPlan &plan = gemv_plan(ctx, A, ct->l);
+  unsigned n1 = (unsigned)std::sqrt((double)S);
+  if (S != n1 * n1) n1 = (unsigned)std::sqrt((double)(2 * S));
+  const unsigned n2 = S / n1;
+  const double Delta = std::ldexp(1.0, (int)h.logDelta);
+  hb_ct inner, outer, rot;
+  hb_ct_alloc(ctx, &inner, ct->batch);
+  hb_ct_alloc(ctx, &outer, ct->batch);
+  hb_ct_alloc(ctx, &rot, ct->batch);
+  for (unsigned i = 0; i < n2; i++) {
+    const unsigned shift = i * n1;
+    for (unsigned j = 0; j < n1; j++) {
+      hb_ct_copy(ctx, &rot, ct);
+      hb_he_rot(ctx, &rot, (int)j, rk);                          // key-switches even for j == 0 (he-algo.c:68)
+      mulpt_with_hat(ctx, &rot, &rot, plan.pthat + (size_t)(shift + j) * plan.D * h.N, plan.D, Delta);
+      if (!j) hb_ct_copy(ctx, &inner, &rot);
+      else hb_he_add(ctx, &inner, &inner, &rot);
+    }
+    hb_he_rot(ctx, &inner, (int)shift, rk);
+    if (!i) hb_ct_copy(ctx, &outer, &inner);
+    else hb_he_add(ctx, &outer, &outer, &inner);
+  }
+  hb_ct_copy(ctx, dst, &outer);
+  hb_he_rs(ctx, dst);
+  hb_ct_free(ctx, &inner);
+  hb_ct_free(ctx, &outer);
+  hb_ct_free(ctx, &rot);
+}
+
+extern "C" void hb_ctr_hempc_eval(hb_ctx *ctx, hb_ct *up, const double *Ka, const double *Kb, const hb_ct *xhat,
+                                  const hb_ct *xr, const hb_ct *uhat, const hb_ct *ur, const hb_evk *rk) {
+  same_shape(xhat, xr, "hb_ctr_hempc_eval"); same_shape(uhat, ur, "hb_ctr_hempc_eval");
+  same_shape(xhat, uhat, "hb_ctr_hempc_eval"); same_shape(up, xhat, "hb_ctr_hempc_eval");
+  const unsigned batch = xhat->batch;
+  hb_ct xdiff, udiff, KaX, KbU, du, ucopy;
+  hb_ct_alloc(ctx, &xdiff, batch); hb_ct_alloc(ctx, &udiff, batch); hb_ct_alloc(ctx, &KaX, batch);
+  hb_ct_alloc(ctx, &KbU, batch); hb_ct_alloc(ctx, &du, batch); hb_ct_alloc(ctx, &ucopy, batch);
+  hb_he_sub(ctx, &xdiff, xhat, xr);              // hempc.c:253
+  hb_he_sub(ctx, &udiff, uhat, ur);              // hempc.c:255
+  hb_he_gemv(ctx, &KaX, Ka, &xdiff, rk);         // hempc.c:257
+  hb_he_gemv(ctx, &KbU, Kb, &udiff, rk);         // hempc.c:259
+  hb_he_add(ctx, &du, &KaX, &KbU);               // hempc.c:261
+  hb_he_neg(ctx, &du);                           // hempc.c:262
+  hb_ct_copy(ctx, &ucopy, uhat);                 // hempc.c:264
+  hb_he_moddown(ctx, &ucopy);                    // hempc.c:265
+  hb_he_add(ctx, up, &ucopy, &du);               // hempc.c:266
+  hb_ct_free(ctx, &xdiff); hb_ct_free(ctx, &udiff); hb_ct_free(ctx, &KaX);
+  hb_ct_free(ctx, &KbU); hb_ct_free(ctx, &du); hb_ct_free(ctx, &ucopy);
+}
+
+extern "C" void hb_ctr_hempc_eval_host(hb_ctx *ctx, unsigned batch, unsigned l, const double *Ka, const double *Kb,
+                                       const uint64_t *in_xhat, const uint64_t *in_xr, const uint64_t *in_uhat,
+                                       const uint64_t *in_ur, const hb_evk *rk, uint64_t *out_up) {
+  check_level(ctx, l);
+  if (l == 0) hb_die("hb_ctr_hempc_eval_host: inputs must be above level 0");
+  hb_ct xhat, xr, uhat, ur, up;
+  hb_ct_alloc(ctx, &xhat, batch); hb_ct_alloc(ctx, &xr, batch); hb_ct_alloc(ctx, &uhat, batch);
+  hb_ct_alloc(ctx, &ur, batch); hb_ct_alloc(ctx, &up, batch);
+  const double Delta = std::ldexp(1.0, (int)ctx->ht.logDelta);
+  hb_ct_upload(ctx, &xhat, in_xhat, l, Delta, 1.0);
+  hb_ct_upload(ctx, &xr, in_xr, l, Delta, 1.0);
+  hb_ct_upload(ctx, &uhat, in_uhat, l, Delta, 1.0);
+  hb_ct_upload(ctx, &ur, in_ur, l, Delta, 1.0);
+  hb_ctr_hempc_eval(ctx, &up, Ka, Kb, &xhat, &xr, &uhat, &ur, rk);
+  hb_ct_download(ctx, &up, out_up);
+  hb_ct_free(ctx, &xhat); hb_ct_free(ctx, &xr); hb_ct_free(ctx, &uhat); hb_ct_free(ctx, &ur); hb_ct_free(ctx, &up);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// limb-level entry points
+// ---------------------------------------------------------------------------------------------------------
+static void check_primes(const hb_ctx *ctx, unsigned d0, unsigned D, const char *what) {
+  if (D == 0 || d0 + D > ctx->ht.dimub) hb_die("%s: primes [%u,%u) outside the chain of %u", what, d0, d0 + D, ctx->ht.dimub);
+}
+extern "C" void hb_ntt_forward(hb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D, int strict) {
+  check_primes(ctx, d0, D, "hb_ntt_forward");
+  if (nlimbs) do_ntt_fwd(ctx, in, out, nlimbs, d0, D, strict != 0);
+}
+extern "C" void hb_ntt_inverse(hb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D) {
+  check_primes(ctx, d0, D, "hb_ntt_inverse");
+  if (nlimbs) do_ntt_inv(ctx, in, out, nlimbs, d0, D);
+}
+extern "C" void hb_ntt_forward_host(hb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D, int strict) {
+  check_primes(ctx, d0, D, "hb_ntt_forward_host");
+  const size_t bytes = nlimbs * ctx->ht.N * 8;
+  uint64_t *buf = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, bytes);
+  CUDA_OK(cudaMemcpyAsync(buf, in, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  if (nlimbs) do_ntt_fwd(ctx, buf, buf, nlimbs, d0, D, strict != 0);
+  CUDA_OK(cudaMemcpyAsync(out, buf, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+}
+extern "C" void hb_poly_ntt(hb_ctx *ctx, const uint64_t *polys, unsigned W, size_t npoly, unsigned D, uint64_t *out) {
+  check_primes(ctx, 0, D, "hb_poly_ntt");
+  if (W == 0 || W > ctx->ht.WC) hb_die("hb_poly_ntt: %u words per coefficient outside [1,%u]", W, ctx->ht.WC);
+  if (npoly) do_poly_ntt(ctx, polys, (size_t)W * ctx->ht.N, (int)W, out, D, npoly);
+}
+extern "C" void hb_rns2words(hb_ctx *ctx, const uint64_t *limbs, size_t npoly, unsigned D, unsigned k, unsigned Wout, uint64_t *out) {
+  check_primes(ctx, 0, D, "hb_rns2words");
+  if (k == 0 || k > 64 * ctx->ht.WC) hb_die("hb_rns2words: modulus 2^%u outside (0, 2^%u]", k, 64 * ctx->ht.WC);
+  if (npoly) do_recon_smod(ctx, limbs, D, out, (int)Wout, (int)k, npoly);
+}
+extern "C" void hb_poly_rot(hb_ctx *ctx, const uint64_t *polys, unsigned W, size_t npoly, int rot, uint64_t *out) {
+  const unsigned ginv = rot < 0 ? 2 * ctx->ht.N - 1 : pow5_inv_mod_2n(ctx, (unsigned)rot);
+  const size_t total = npoly * ctx->ht.N;
+  if (total) launch(ctx, hbdev::k_poly_automorph, (unsigned)((total + 255) / 256), 256, 0, 1, polys, out, (int)W, ginv, ctx->ht.N, npoly);
+}

@@ -1,0 +1,507 @@
+// sm_100a kernels of the CKKS evaluation path.  Every kernel cites the reference routine that defines its
+// results.  Ciphertext polynomials are planar little-endian two's-complement words  poly[w*N + i]
+// (w = 0 least significant), RNS limbs are u64[limb][N].
+#pragma once
+#include "hb_dev.cuh"
+
+namespace hbdev {
+
+// =========================================================================================================
+// K2 / K3: stand-alone batched transforms (config B microbench; building blocks of he_mul)
+// =========================================================================================================
+// Results = ntt() of GPQHE/src/ntt.c:37-52.  STRICT reproduces the reference's [0,p] representation bit for
+// bit; the default returns the same residues canonicalised to [0,p) (p -> 0).
+template <int LOGN, bool STRICT>
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS)
+k_ntt_fwd(const uint64_t *__restrict__ in, uint64_t *__restrict__ out, Tables T, unsigned d0, unsigned D) {
+  typedef Cfg<LOGN> G;
+  extern __shared__ __align__(16) uint64_t smem[];
+  const unsigned limb = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
+  const unsigned d = d0 + limb % D;
+  const uint64_t p = T.primes[d].p;
+  const ulonglong2 *tw = T.tw + (size_t)d * G::N;
+  const uint64_t *src = in + (size_t)limb * G::N;
+  ntt_forward<LOGN, STRICT>(smem, [&](int gi) { return src[gi]; }, tw, p);
+  uint64_t *dst = out + (size_t)limb * G::N + (size_t)chunk * G::M;
+  for (int i = threadIdx.x; i < G::M; i += G::THREADS) {
+    uint64_t v = smem[pidx(i)];
+    dst[i] = STRICT ? v : canon4(v, p);
+  }
+}
+
+// Results = invntt() of GPQHE/src/ntt.c:54-73 (canonical [0,p)).  Inputs may be any value <= p.
+template <int LOGN>
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS)
+k_ntt_inv(const uint64_t *__restrict__ in, uint64_t *__restrict__ out, Tables T, unsigned d0, unsigned D) {
+  typedef Cfg<LOGN> G;
+  extern __shared__ __align__(16) uint64_t smem[];
+  const unsigned limb = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
+  const unsigned d = d0 + limb % D;
+  const PrimeConsts pc = T.primes[d];
+  const uint64_t *src = in + (size_t)limb * G::N + (size_t)chunk * G::M;
+  for (int i = threadIdx.x; i < G::M; i += G::THREADS) smem[pidx(i)] = src[i];
+  __syncthreads();
+  uint64_t *dst = out + (size_t)limb * G::N;
+  ntt_inverse<LOGN>(smem, [&](int gi, uint64_t v) { dst[gi] = v; }, T.itw + (size_t)d * G::N, pc);
+}
+
+// =========================================================================================================
+// K1 + K2: signed multiword polynomial -> NTT limbs  (rns_decompose rns.c:37-48, then ntt)
+// =========================================================================================================
+// src: npoly polynomials, polynomial q at src + q*poly_stride, W words each.  out[q][d][N], canonical.
+template <int LOGN>
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS)
+k_poly_ntt(const uint64_t *__restrict__ src, size_t poly_stride, int W, uint64_t *__restrict__ out, Tables T,
+           unsigned D) {
+  typedef Cfg<LOGN> G;
+  extern __shared__ __align__(16) uint64_t smem[];
+  const unsigned idx = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
+  const unsigned q = idx / D, d = idx % D;
+  const PrimeConsts pc = T.primes[d];
+  const uint64_t pw = T.pow64[(size_t)d * (T.WC + 1) + W];
+  const uint64_t *poly = src + (size_t)q * poly_stride;
+  ntt_forward<LOGN, false>(smem, [&](int gi) { return decompose_words(poly + gi, G::N, W, pc, pw); },
+                           T.tw + (size_t)d * G::N, pc.p);
+  uint64_t *dst = out + ((size_t)q * D + d) * G::N + (size_t)chunk * G::M;
+  for (int i = threadIdx.x; i < G::M; i += G::THREADS) dst[i] = canon4(smem[pidx(i)], pc.p);
+}
+
+// =========================================================================================================
+// key switch, per-limb half:  he_swk  GPQHE/src/he-automorphism.c:59-67  (== he_relin he-mult.c:58-66)
+//   chat[b][h][d] = invntt( ntt( decompose( sigma(src_b) ) mod p_d ) o evk.p_h[d] ),  h = 0,1
+// sigma is the automorphism X -> X^g fused into the load (poly_rot / poly_conj, poly.c:263-283), given as
+// ginv = g^-1 mod 2N:  sigma(a)[k] = +a[k*ginv mod 2N]  if that index is < N, else  -a[(k*ginv mod 2N) - N].
+// =========================================================================================================
+template <int LOGN>
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS)
+k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, unsigned ginv,
+          const uint64_t *__restrict__ evk, unsigned dimevk, uint64_t *__restrict__ chat, Tables T, unsigned D) {
+  typedef Cfg<LOGN> G;
+  extern __shared__ __align__(16) uint64_t smem[];
+  uint64_t *smA = smem, *smB = smem + G::SMEM_WORDS;
+  const unsigned idx = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
+  const unsigned b = idx / D, d = idx % D;
+  const PrimeConsts pc = T.primes[d];
+  const uint64_t p = pc.p;
+  const uint64_t pw = T.pow64[(size_t)d * (T.WC + 1) + W];
+  const uint64_t *poly = src + (size_t)b * src_bstride;
+  ntt_forward<LOGN, false>(
+      smA,
+      [&](int gi) {
+        unsigned ip = ((unsigned)gi * ginv) & (2 * G::N - 1);
+        uint64_t v = decompose_words(poly + (ip & (G::N - 1)), G::N, W, pc, pw);
+        return (ip >= (unsigned)G::N && v) ? p - v : v;
+      },
+      T.tw + (size_t)d * G::N, p);
+#pragma unroll 1
+  for (int h = 0; h < 2; h++) {
+    const uint64_t *key = evk + ((size_t)h * dimevk + d) * G::N + (size_t)chunk * G::M;
+    for (int i = threadIdx.x; i < G::M; i += G::THREADS)
+      smB[pidx(i)] = mulmod_barrett(canon4(smA[pidx(i)], p), key[i], p, pc.mu);
+    __syncthreads();
+    uint64_t *dst = chat + (((size_t)b * 2 + h) * D + d) * G::N;
+    ntt_inverse<LOGN>(smB, [&](int gi, uint64_t v) { dst[gi] = v; }, T.itw + (size_t)d * G::N, pc);
+  }
+}
+
+// =========================================================================================================
+// ct x pt, per-limb:  he_mulpt  GPQHE/src/he-mult.c:176-188
+//   chat[b][h][d] = invntt( ntt(decompose(c_h)) o pthat[d] )
+// =========================================================================================================
+template <int LOGN>
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS)
+k_mulpt_limb(const uint64_t *__restrict__ ct, int W, const uint64_t *__restrict__ pthat,
+             uint64_t *__restrict__ chat, Tables T, unsigned D) {
+  typedef Cfg<LOGN> G;
+  extern __shared__ __align__(16) uint64_t smem[];
+  const unsigned idx = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
+  const unsigned q = idx / D, d = idx % D;          // q = b*2 + h
+  const PrimeConsts pc = T.primes[d];
+  const uint64_t p = pc.p;
+  const uint64_t pw = T.pow64[(size_t)d * (T.WC + 1) + W];
+  const uint64_t *poly = ct + (size_t)q * W * G::N;
+  ntt_forward<LOGN, false>(smem, [&](int gi) { return decompose_words(poly + gi, G::N, W, pc, pw); },
+                           T.tw + (size_t)d * G::N, p);
+  const uint64_t *pt = pthat + (size_t)d * G::N + (size_t)chunk * G::M;
+  for (int i = threadIdx.x; i < G::M; i += G::THREADS)
+    smem[pidx(i)] = mulmod_barrett(canon4(smem[pidx(i)], p), pt[i], p, pc.mu);
+  __syncthreads();
+  uint64_t *dst = chat + ((size_t)q * D + d) * G::N;
+  ntt_inverse<LOGN>(smem, [&](int gi, uint64_t v) { dst[gi] = v; }, T.itw + (size_t)d * G::N, pc);
+}
+
+// =========================================================================================================
+// ct x ct tensor, per-limb:  he_mul  GPQHE/src/he-mult.c:116-138
+//   in  hatA[b][2][D][N], hatB[b][2][D][N] = ntt of (a.c0, a.c1), (b.c0, b.c1)      (k_poly_ntt)
+//   out dhat[b][3][D][N] = invntt of (a0 b0, a0 b1 + a1 b0, a1 b1)
+// The reference inverts a0 b1 and a1 b0 separately and adds mod p afterwards; the inverse transform is linear
+// mod p, so adding first gives the same canonical residues.
+// =========================================================================================================
+template <int LOGN>
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS)
+k_tensor_intt(const uint64_t *__restrict__ hatA, const uint64_t *__restrict__ hatB, uint64_t *__restrict__ dhat, Tables T,
+              unsigned D) {
+  typedef Cfg<LOGN> G;
+  extern __shared__ __align__(16) uint64_t smem[];
+  const unsigned idx = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
+  const unsigned d = idx % D, which = (idx / D) % 3, b = idx / (3 * D);
+  const PrimeConsts pc = T.primes[d];
+  const uint64_t p = pc.p;
+  const size_t off = (size_t)d * G::N + (size_t)chunk * G::M;
+  const uint64_t *a0 = hatA + ((size_t)b * 2 + 0) * D * G::N + off, *a1 = hatA + ((size_t)b * 2 + 1) * D * G::N + off;
+  const uint64_t *b0 = hatB + ((size_t)b * 2 + 0) * D * G::N + off, *b1 = hatB + ((size_t)b * 2 + 1) * D * G::N + off;
+  for (int i = threadIdx.x; i < G::M; i += G::THREADS) {
+    uint64_t v;
+    if (which == 0) v = mulmod_barrett(a0[i], b0[i], p, pc.mu);
+    else if (which == 2) v = mulmod_barrett(a1[i], b1[i], p, pc.mu);
+    else v = addmod(mulmod_barrett(a0[i], b1[i], p, pc.mu), mulmod_barrett(a1[i], b0[i], p, pc.mu), p);
+    smem[pidx(i)] = v;
+  }
+  __syncthreads();
+  uint64_t *dst = dhat + (((size_t)b * 3 + which) * D + d) * G::N;
+  ntt_inverse<LOGN>(smem, [&](int gi, uint64_t v) { dst[gi] = v; }, T.itw + (size_t)d * G::N, pc);
+}
+
+// =========================================================================================================
+// K5: exact CRT reconstruction, low words only.
+//   rns_reconstruct rns.c:60-75 + centring mod P_D (poly.c:116):  x = sum_d y_d (P_D/p_d) - v P_D,
+//   y_d = a_d (P_D/p_d)^-1 mod p_d,  v = round(sum_d y_d / p_d)  (120-bit fixed point, error < D 2^-60).
+//   Only x mod 2^(64 WK) is formed: every consumer reduces modulo a power of two afterwards.
+// =========================================================================================================
+template <int WK, class Get>
+__device__ __forceinline__ void crt_low(Get a, unsigned D, const Tables &T, uint64_t (&acc)[WK]) {
+#pragma unroll
+  for (int w = 0; w < WK; w++) acc[w] = 0;
+  uint64_t Flo = 0, Fhi = 0;
+  const uint64_t *inv = T.crt_inv + (size_t)D * T.dimub, *invq = T.crt_inv_q + (size_t)D * T.dimub;
+  const uint64_t *phat = T.crt_phat + (size_t)D * T.dimub * T.WC;
+  for (unsigned d = 0; d < D; d++) {
+    const uint64_t p = T.primes[d].p, mu = T.primes[d].mu;
+    const uint64_t y = shoup(a(d), inv[d], invq[d], p);
+    uint64_t lo = y * mu, hi = __umul64hi(y, mu);
+    Flo += lo;
+    Fhi += hi + (Flo < lo);
+    uint64_t carry = 0;
+#pragma unroll
+    for (int w = 0; w < WK; w++) {
+      const uint64_t pw = (w < (int)T.WC) ? phat[(size_t)d * T.WC + w] : 0;
+      uint64_t l = y * pw, h = __umul64hi(y, pw);
+      uint64_t s = acc[w] + l;
+      h += (s < l);
+      uint64_t s2 = s + carry;
+      h += (s2 < carry);
+      acc[w] = s2;
+      carry = h;
+    }
+  }
+  const uint64_t v = (Fhi + (1ULL << 55)) >> 56;
+  const uint64_t *P = T.crt_P + (size_t)D * T.WC;
+  uint64_t borrow = 0;
+#pragma unroll
+  for (int w = 0; w < WK; w++) {
+    const uint64_t pw = (w < (int)T.WC) ? P[w] : 0;
+    uint64_t l = v * pw, h = __umul64hi(v, pw);
+    uint64_t sub = l + borrow;
+    h += (sub < l);
+    h += (acc[w] < sub);
+    acc[w] -= sub;
+    borrow = h;
+  }
+}
+
+// out polynomial q (of npoly) = smod(reconstruct(chat[q][0..D)), 2^k)   -- poly_rns2mpi, poly.c:109-120
+template <int WK>
+__global__ void k_recon_smod(const uint64_t *__restrict__ chat, unsigned D, uint64_t *__restrict__ out, int Wout,
+                             int k, Tables T, unsigned npoly) {
+  const unsigned N = T.N;
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)npoly * N) return;
+  const unsigned q = gid / N, i = gid % N;
+  const uint64_t *limbs = chat + (size_t)q * D * N + i;
+  uint64_t acc[WK];
+  crt_low<WK>([&](unsigned d) { return limbs[(size_t)d * N]; }, D, T, acc);
+  sext_bits<WK>(acc, k);
+  uint64_t *o = out + (size_t)q * Wout * N + i;
+#pragma unroll
+  for (int w = 0; w < WK; w++)
+    if (w < Wout) o[(size_t)w * N] = acc[w];
+}
+
+// =========================================================================================================
+// K5 + K6: key-switch tail.  he_swk he-automorphism.c:68-76 / he_relin he-mult.c:68-77:
+//   c_h = smod( rdiv( smod(reconstruct(chat_h), P q_l), P ) + add_h , q_l )
+// With q_l = 2^k and P odd this equals  ((x - R) P^-1 + [R > floor(P/2)] + add_h) mod 2^k, sign-extended, where
+// x is the centred reconstruction (only its low words are needed) and R = x mod P is rebuilt EXACTLY from the
+// first `dim` limbs (P = p_0...p_{dim-1}); see DESIGN.md "key-switch tail" for the proof.
+// add0/add1: optional polynomials (batch stride given) with the automorphism ginv applied on the fly.
+// =========================================================================================================
+template <int WK, int WPK>
+__global__ void k_ks_finish(const uint64_t *__restrict__ chat, unsigned D, const uint64_t *__restrict__ add0,
+                            const uint64_t *__restrict__ add1, size_t add_bstride, int Wadd, unsigned ginv,
+                            uint64_t *__restrict__ out, int Wout, int k, Tables T, unsigned batch) {
+  const unsigned N = T.N;
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)batch * 2 * N) return;
+  const unsigned i = gid % N, h = (gid / N) & 1, b = gid / (2 * (size_t)N);
+  const uint64_t *limbs = chat + ((size_t)b * 2 + h) * D * N + i;
+  uint64_t acc[WK];
+  crt_low<WK>([&](unsigned d) { return limbs[(size_t)d * N]; }, D, T, acc);
+  // ---- R = x mod P, exact ----
+  uint64_t R[WPK];
+#pragma unroll
+  for (int w = 0; w < WPK; w++) R[w] = 0;
+  uint64_t Flo = 0, Fhi = 0;
+  const int WP = T.WP;
+  for (unsigned d = 0; d < T.dim; d++) {
+    const uint64_t p = T.primes[d].p, mu = T.primes[d].mu;
+    const uint64_t z = shoup(limbs[(size_t)d * N], T.ks_inv[d], T.ks_inv_q[d], p);
+    uint64_t lo = z * mu, hi = __umul64hi(z, mu);
+    Flo += lo;
+    Fhi += hi + (Flo < lo);
+    uint64_t carry = 0;
+#pragma unroll
+    for (int w = 0; w < WPK; w++) {
+      if (w < WP) {
+        const uint64_t pw = T.ks_phat[(size_t)d * WP + w];
+        uint64_t l = z * pw, hh = __umul64hi(z, pw);
+        uint64_t s = R[w] + l;
+        hh += (s < l);
+        uint64_t s2 = s + carry;
+        hh += (s2 < carry);
+        R[w] = s2;
+        carry = hh;
+      }
+    }
+  }
+  {
+    const uint64_t v = Fhi >> 56;     // floor estimate: true floor is v or v+1
+    uint64_t borrow = 0;
+#pragma unroll
+    for (int w = 0; w < WPK; w++) {
+      if (w < WP) {
+        const uint64_t pw = T.ks_P[w];
+        uint64_t l = v * pw, hh = __umul64hi(v, pw);
+        uint64_t sub = l + borrow;
+        hh += (sub < l);
+        hh += (R[w] < sub);
+        R[w] -= sub;
+        borrow = hh;
+      }
+    }
+    // if R >= P: R -= P
+    bool ge = true;  // compare from the top word down
+    {
+      bool decided = false;
+#pragma unroll
+      for (int w = WPK - 1; w >= 0; w--) {
+        if (w < WP && !decided) {
+          const uint64_t pw = T.ks_P[w];
+          if (R[w] != pw) { ge = R[w] > pw; decided = true; }
+        }
+      }
+    }
+    if (ge) {
+      uint64_t bw = 0;
+#pragma unroll
+      for (int w = 0; w < WPK; w++) {
+        if (w < WP) {
+          const uint64_t pw = T.ks_P[w];
+          uint64_t sub = pw + bw;
+          uint64_t nb = (sub < pw) | (R[w] < sub);
+          R[w] -= sub;
+          bw = nb;
+        }
+      }
+    }
+  }
+  bool roundup = false;  // R > floor(P/2)   (mpi_rdiv, types.c:115-128)
+  {
+    bool decided = false;
+#pragma unroll
+    for (int w = WPK - 1; w >= 0; w--) {
+      if (w < WP && !decided) {
+        const uint64_t hw = T.ks_Ph[w];
+        if (R[w] != hw) { roundup = R[w] > hw; decided = true; }
+      }
+    }
+  }
+  // ---- t = (x - R) * P^-1 mod 2^(64 WK) ----
+  uint64_t diff[WK];
+  {
+    uint64_t bw = 0;
+#pragma unroll
+    for (int w = 0; w < WK; w++) {
+      const uint64_t rw = (w < WPK && w < WP) ? R[w < WPK ? w : 0] : 0;
+      uint64_t sub = rw + bw;
+      uint64_t nb = (sub < rw) | (acc[w] < sub);
+      diff[w] = acc[w] - sub;
+      bw = nb;
+    }
+  }
+  uint64_t t[WK];
+#pragma unroll
+  for (int w = 0; w < WK; w++) t[w] = 0;
+#pragma unroll
+  for (int a = 0; a < WK; a++) {
+    uint64_t carry = 0;
+#pragma unroll
+    for (int c = 0; c + a < WK; c++) {
+      const uint64_t pw = (c < (int)T.WC) ? T.ks_Pinv[c] : 0;
+      uint64_t l = diff[a] * pw, hh = __umul64hi(diff[a], pw);
+      uint64_t s = t[a + c] + l;
+      hh += (s < l);
+      uint64_t s2 = s + carry;
+      hh += (s2 < carry);
+      t[a + c] = s2;
+      carry = hh;
+    }
+  }
+  // ---- + roundup + sigma(add_h)[i] ----
+  uint64_t addw[WK];
+#pragma unroll
+  for (int w = 0; w < WK; w++) addw[w] = 0;
+  const uint64_t *add = h ? add1 : add0;
+  bool negate = false;
+  if (add) {
+    unsigned ip = (i * ginv) & (2 * N - 1);
+    negate = ip >= N;
+    const uint64_t *ap = add + (size_t)b * add_bstride + (ip & (N - 1));
+    uint64_t fill = 0;
+#pragma unroll
+    for (int w = 0; w < WK; w++) {
+      if (w < Wadd) { addw[w] = ap[(size_t)w * N]; fill = (uint64_t)((int64_t)addw[w] >> 63); }
+      else addw[w] = fill;
+    }
+  }
+  {
+    // t += roundup + (negate ? -addw : addw)  ==  t + roundup + (addw ^ m) + (negate ? 1 : 0)
+    const uint64_t m = negate ? ~0ULL : 0ULL;
+    uint64_t carry = (roundup ? 1u : 0u);
+    uint64_t carry2 = negate ? 1u : 0u;
+#pragma unroll
+    for (int w = 0; w < WK; w++) {
+      uint64_t a = addw[w] ^ m;
+      uint64_t s = t[w] + a;
+      uint64_t c1 = (s < a);
+      uint64_t s2 = s + carry;
+      uint64_t c2 = (s2 < carry);
+      uint64_t s3 = s2 + carry2;
+      uint64_t c3 = (s3 < carry2);
+      t[w] = s3;
+      carry = c1 + c2;   // at most 1 in total with c3 handled separately
+      carry2 = c3;
+    }
+  }
+  sext_bits<WK>(t, k);
+  uint64_t *o = out + ((size_t)b * 2 + h) * Wout * N + i;
+#pragma unroll
+  for (int w = 0; w < WK; w++)
+    if (w < Wout) o[(size_t)w * N] = t[w];
+}
+
+// =========================================================================================================
+// K7: coefficient-wise ciphertext arithmetic (he-add.c:32-142, he-rescale.c:33-70), q_l = 2^k.
+//   op 0: a + b   op 1: a - b   op 2: -a      then smod(., 2^k) = sign-extension from bit k-1.
+// One thread per (polynomial, coefficient); W words each.
+// =========================================================================================================
+__global__ void k_ct_addsub(const uint64_t *__restrict__ a, const uint64_t *__restrict__ b, uint64_t *__restrict__ out,
+                            int W, int k, int op, unsigned N, size_t npoly) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= npoly * N) return;
+  const size_t q = gid / N, i = gid % N;
+  const uint64_t *pa = a + q * W * N + i;
+  const uint64_t *pb = b ? b + q * W * N + i : nullptr;
+  uint64_t *po = out + q * W * N + i;
+  uint64_t carry = (op == 0) ? 0 : 1;      // two's complement: x - y = x + ~y + 1 ; -x = ~x + 1
+  uint64_t fill = 0;
+  bool done = false;
+  for (int w = 0; w < W; w++) {
+    uint64_t r;
+    if (done) r = fill;
+    else {
+      uint64_t x = pa[(size_t)w * N], y = pb ? pb[(size_t)w * N] : 0;
+      uint64_t lhs = (op == 2) ? 0 : x;
+      uint64_t rhs = (op == 0) ? y : (op == 1 ? ~y : ~x);
+      uint64_t s = lhs + rhs;
+      uint64_t c1 = s < rhs;
+      uint64_t s2 = s + carry;
+      uint64_t c2 = s2 < carry;
+      carry = c1 | c2;
+      r = s2;
+      int kk = k - 64 * w;
+      if (kk <= 64) {
+        if (kk < 64) r = (uint64_t)(((int64_t)(r << (64 - kk))) >> (64 - kk));
+        fill = (uint64_t)((int64_t)r >> 63);
+        done = true;
+      }
+    }
+    po[(size_t)w * N] = r;
+  }
+}
+
+// he_rs (shift = log2 Delta: rounded division, ties toward -inf on the remainder test r > Delta/2, types.c:115-128)
+// and he_moddown (shift = 0), both followed by smod(., 2^kout).  Win words in, Wout words out (out of place).
+__global__ void k_ct_rescale(const uint64_t *__restrict__ a, uint64_t *__restrict__ out, int Win, int Wout, int shift,
+                             int kout, unsigned N, size_t npoly) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= npoly * N) return;
+  const size_t q = gid / N, i = gid % N;
+  const uint64_t *pa = a + q * Win * N + i;
+  uint64_t *po = out + q * Wout * N + i;
+  const uint64_t sign = (uint64_t)((int64_t)pa[(size_t)(Win - 1) * N] >> 63);
+  auto word = [&](int w) -> uint64_t { return w < Win ? pa[(size_t)w * N] : sign; };
+  // round up iff (a mod 2^shift) > 2^(shift-1)
+  uint64_t roundup = 0;
+  if (shift > 0) {
+    const int hb = shift - 1;                   // bit index of the half
+    const int hw = hb / 64, hbit = hb % 64;
+    const uint64_t wv = word(hw);
+    if ((wv >> hbit) & 1) {
+      bool lower = (hbit > 0) && ((wv & ((1ULL << hbit) - 1)) != 0);
+      for (int w = 0; w < hw && !lower; w++) lower = word(w) != 0;
+      roundup = lower ? 1 : 0;
+    }
+  }
+  const int ws = shift / 64, bs = shift % 64;
+  uint64_t carry = roundup, fill = 0;
+  bool done = false;
+  for (int w = 0; w < Wout; w++) {
+    uint64_t r;
+    if (done) r = fill;
+    else {
+      uint64_t lo = word(w + ws), hi = word(w + ws + 1);
+      uint64_t v = bs ? ((lo >> bs) | (hi << (64 - bs))) : lo;
+      uint64_t s = v + carry;
+      carry = (s < carry);
+      r = s;
+      int kk = kout - 64 * w;
+      if (kk <= 64) {
+        if (kk < 64) r = (uint64_t)(((int64_t)(r << (64 - kk))) >> (64 - kk));
+        fill = (uint64_t)((int64_t)r >> 63);
+        done = true;
+      }
+    }
+    po[(size_t)w * N] = r;
+  }
+}
+
+// poly_rot / poly_conj as a stand-alone permutation (poly.c:263-283) -- used by tests and he_rot's add path.
+__global__ void k_poly_automorph(const uint64_t *__restrict__ a, uint64_t *__restrict__ out, int W, unsigned ginv,
+                                 unsigned N, size_t npoly) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= npoly * N) return;
+  const size_t q = gid / N;
+  const unsigned i = gid % N;
+  const unsigned ip = (i * ginv) & (2 * N - 1);
+  const bool neg = ip >= N;
+  const uint64_t *pa = a + q * W * N + (ip & (N - 1));
+  uint64_t *po = out + q * W * N + i;
+  uint64_t carry = neg ? 1 : 0;
+  for (int w = 0; w < W; w++) {
+    uint64_t x = pa[(size_t)w * N];
+    if (neg) { x = ~x; uint64_t s = x + carry; carry = s < carry; x = s; }
+    po[(size_t)w * N] = x;
+  }
+}
+
+}  // namespace hbdev

@@ -1,0 +1,160 @@
+/* hectr_b200 -- C ABI of the B200 (sm_100a) CKKS evaluation engine.
+ *
+ * Drop-in boundary for the evaluation half of the GPQHE C API that HECTR's encrypted MPC
+ * (src/hempc.c:216-274) drives.  Every entry point names the reference function it stands in
+ * for (paths relative to the OChicken/HECTR tree).  The reference computes on libgcrypt MPIs
+ * in host memory; here a ciphertext lives in GPU memory as fixed-width integers and a handle
+ * may hold a BATCH of independent ciphertexts that every operation processes in one launch.
+ *
+ * Data formats (all little-endian, host or device as stated):
+ *   ciphertext  uint64 words[batch][2][W_l][N]   two's-complement coefficient, word w of
+ *               coefficient i of polynomial c_h of instance b at ((b*2+h)*W_l + w)*N + i,
+ *               W_l = hb_ctx_words(ctx, l) = ceil((log2 q_l + 1)/64).  Same integers as
+ *               he_ct_t.c0/c1.coeffs[i] (GPQHE/src/gpqhe.h:84-91), centred in [-q_l/2, q_l/2).
+ *   plaintext   uint64 words[WC][N], WC = hb_ctx_words(ctx, L)        (he_pt_t.m, gpqhe.h:93-97)
+ *   eval. key   uint64 p0[dimevk][N], p1[dimevk][N] exactly as he_genswk stores them
+ *               (NTT/RNS form, GPQHE/src/he-kem.c:103-110; he_evk_t gpqhe.h:78-82)
+ *   RNS limbs   uint64 limbs[nlimbs][N]
+ *
+ * Restrictions, checked at hb_ctx_create: q = 2^logq and Delta = 2^logDelta (every reference call
+ * site uses powers of two: src/ctr.c:514-518, GPQHE/tests/gpqhe.c:1349-1353).
+ *
+ * Error behaviour follows the reference (GPQHE/src/precomp.c:344-350, he-add.c:35): misuse prints
+ * "error: ..." on stderr and abort()s; so does any CUDA failure.  There is no CPU fallback.
+ * One context is used by one host thread at a time (the reference has one global context).
+ */
+#ifndef HECTR_B200_H
+#define HECTR_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct hb_ctx hb_ctx;
+
+typedef struct hb_info {           /* what hectx_init derives (precomp.c:386-409) */
+  unsigned logn, n, logq, logDelta, slots;
+  unsigned L, dim, dimevk, dimub;
+  unsigned words_top;              /* W_L */
+  unsigned nbitsP, nbitsPqL;
+  int device, sm_count;
+} hb_info;
+
+typedef struct hb_ct {             /* he_ct_t (gpqhe.h:84-91) with a device payload */
+  unsigned l;
+  double nu, B;
+  unsigned batch;
+  uint64_t *words;                 /* DEVICE pointer, owned by the library */
+} hb_ct;
+
+typedef struct hb_pt {             /* he_pt_t (gpqhe.h:93-97) */
+  double nu;
+  uint64_t *words;                 /* DEVICE pointer [WC][N] */
+} hb_pt;
+
+typedef struct hb_evk {            /* he_evk_t (gpqhe.h:78-82) */
+  uint64_t *p;                     /* DEVICE pointer [2][dimevk][N] */
+} hb_evk;
+
+/* ---- context: hectx_init / hectx_exit (precomp.c:431-453,465-) --------------------------------- */
+hb_ctx *hb_ctx_create(unsigned logn, unsigned logq, unsigned slots, unsigned logDelta, int device);
+void hb_ctx_destroy(hb_ctx *ctx);
+void hb_ctx_info(const hb_ctx *ctx, hb_info *out);
+unsigned hb_ctx_words(const hb_ctx *ctx, unsigned l);          /* W_l */
+unsigned hb_ctx_logq(const hb_ctx *ctx, unsigned l);           /* log2 q_l */
+void hb_ctx_primes(const hb_ctx *ctx, uint64_t *out);          /* [dimub]       rns_ctx.p */
+void hb_ctx_twiddles(const hb_ctx *ctx, unsigned d, int inverse, uint64_t *out); /* [N] plain zeta^brv(i) */
+unsigned hb_dim_keyswitch(const hb_ctx *ctx, unsigned l);      /* he-automorphism.c:52 */
+unsigned hb_dim_mul(const hb_ctx *ctx, unsigned l);            /* he-mult.c:99 */
+unsigned hb_dim_mulpt(const hb_ctx *ctx, unsigned l, double nu); /* he-mult.c:168 */
+void hb_ctx_set_stream(hb_ctx *ctx, void *cuda_stream);        /* default: the context's own stream */
+void hb_sync(hb_ctx *ctx);
+/* CUDA-event stopwatch on the context's stream (bench.py, roofline timing) */
+void hb_timer_start(hb_ctx *ctx);
+float hb_timer_stop_ms(hb_ctx *ctx);
+/* kernels launched by this context since creation (bench.py "gpu_launches") */
+uint64_t hb_launch_count(const hb_ctx *ctx);
+
+/* ---- host-only view of the same tables (no GPU needed: CPU tests of the host logic) -------------------- */
+typedef struct hb_tables hb_tables;
+hb_tables *hb_tables_create(unsigned logn, unsigned logq, unsigned slots, unsigned logDelta);  /* NULL + message if rejected */
+void hb_tables_destroy(hb_tables *t);
+void hb_tables_info(const hb_tables *t, hb_info *out);
+void hb_tables_primes(const hb_tables *t, uint64_t *out);
+void hb_tables_twiddles(const hb_tables *t, unsigned d, int inverse, uint64_t *out);
+/* CRT constants for D limbs: inv[D] = (P_D/p_d)^-1 mod p_d, phat_low[D][W_L], P_low[W_L]   (precomp.c:266-293) */
+void hb_tables_crt(const hb_tables *t, unsigned D, uint64_t *inv, uint64_t *phat_low, uint64_t *P_low);
+unsigned hb_tables_dim(const hb_tables *t, int which, unsigned l, double nu);   /* 0 keyswitch, 1 mul, 2 mulpt */
+void hb_tables_encode(const hb_tables *t, const double *m, double Delta, uint64_t *words);
+void hb_tables_decode(const hb_tables *t, const uint64_t *words, unsigned W, double Delta, double *m);
+
+/* ---- raw memory helpers ------------------------------------------------------------------------- */
+void *hb_dev_alloc(hb_ctx *ctx, size_t bytes);
+void hb_dev_free(hb_ctx *ctx, void *p);
+void *hb_host_alloc(hb_ctx *ctx, size_t bytes);                /* pinned */
+void hb_host_free(hb_ctx *ctx, void *p);
+void hb_h2d(hb_ctx *ctx, void *dst, const void *src, size_t bytes);   /* async on the ctx stream */
+void hb_d2h(hb_ctx *ctx, void *dst, const void *src, size_t bytes);   /* async on the ctx stream */
+void hb_dev_fill(hb_ctx *ctx, void *dst, int byte, size_t bytes);
+
+/* ---- containers: he-mem.c:31-97 ---------------------------------------------------------------- */
+void hb_ct_alloc(hb_ctx *ctx, hb_ct *ct, unsigned batch);      /* he_alloc_ct */
+void hb_ct_free(hb_ctx *ctx, hb_ct *ct);                       /* he_free_ct  */
+void hb_ct_copy(hb_ctx *ctx, hb_ct *dst, const hb_ct *src);    /* he_copy_ct  */
+void hb_ct_upload(hb_ctx *ctx, hb_ct *ct, const uint64_t *host_words, unsigned l, double nu, double B);
+void hb_ct_download(hb_ctx *ctx, const hb_ct *ct, uint64_t *host_words);   /* synchronises */
+void hb_pt_alloc(hb_ctx *ctx, hb_pt *pt);                      /* he_alloc_pt */
+void hb_pt_free(hb_ctx *ctx, hb_pt *pt);
+void hb_pt_upload(hb_ctx *ctx, hb_pt *pt, const uint64_t *host_words, double nu);
+void hb_evk_upload(hb_ctx *ctx, hb_evk *evk, const uint64_t *p0, const uint64_t *p1);  /* he_alloc_evk + copy */
+void hb_evk_free(hb_ctx *ctx, hb_evk *evk);
+
+/* ---- encode / decode on the host: he-encode.c:53-125, canemb.c:43-81 -------------------------------- */
+/* m: slots complex doubles (re,im interleaved).  words: host [WC][N]; only indices j*gap and j*gap+N/2 are
+ * written, exactly like encode() (hazard: other coefficients are left as they are). */
+void hb_encode(const hb_ctx *ctx, const double *m, double Delta, uint64_t *words);
+void hb_decode(const hb_ctx *ctx, const uint64_t *words, unsigned W, double Delta, double *m);
+void hb_he_ecd(hb_ctx *ctx, hb_pt *pt, const double *m);       /* he_ecd: encode at Delta and upload */
+
+/* ---- evaluation ------------------------------------------------------------------------------------ */
+void hb_he_add(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b);        /* he_add   he-add.c:32-54 */
+void hb_he_sub(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b);        /* he_sub   he-add.c:57-79 */
+void hb_he_neg(hb_ctx *ctx, hb_ct *ct);                                        /* he_neg   he-add.c:124-142 */
+void hb_he_rs(hb_ctx *ctx, hb_ct *ct);                                         /* he_rs    he-rescale.c:33-54 */
+void hb_he_moddown(hb_ctx *ctx, hb_ct *ct);                                    /* he_moddown he-rescale.c:56-70 */
+void hb_he_mulpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt);  /* he_mulpt he-mult.c:159-196 */
+void hb_he_mul(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b, const hb_evk *rlk); /* he_mul he-mult.c:88-156 */
+void hb_he_rot(hb_ctx *ctx, hb_ct *ct, int rot, const hb_evk *rk);             /* he_rot   he-automorphism.c:102-115; rk[rot] */
+void hb_he_conj(hb_ctx *ctx, hb_ct *ct, const hb_evk *ck);                     /* he_conj  he-automorphism.c:87-100 */
+/* he_gemv he-algo.c:47-93.  A: slots x slots complex doubles, row-major, shared by the whole batch. */
+void hb_he_gemv(hb_ctx *ctx, hb_ct *dst, const double *A, const hb_ct *ct, const hb_evk *rk);
+/* The ciphertext half of ctr_hempc (src/hempc.c:253-266):
+ *   up = uhat|moddown - ( Ka (xhat - xr) + Kb (uhat - ur) )      all at level l, result at l-1 */
+void hb_ctr_hempc_eval(hb_ctx *ctx, hb_ct *up, const double *Ka, const double *Kb, const hb_ct *xhat,
+                       const hb_ct *xr, const hb_ct *uhat, const hb_ct *ur, const hb_evk *rk);
+/* Same, end to end from HOST buffers (pinned or pageable): uploads the four input batches, evaluates,
+ * downloads the result batch (level l-1) and synchronises.  in_*: [batch][2][W_l][N]. */
+void hb_ctr_hempc_eval_host(hb_ctx *ctx, unsigned batch, unsigned l, const double *Ka, const double *Kb,
+                            const uint64_t *in_xhat, const uint64_t *in_xr, const uint64_t *in_uhat,
+                            const uint64_t *in_ur, const hb_evk *rk, uint64_t *out_up);
+
+/* ---- limb-level entry points (parity tests, NTT microbench) ---------------------------------------- */
+/* ntt / invntt (GPQHE/src/ntt.c:37-73) over nlimbs limbs in DEVICE memory; limb j uses prime d0 + j % D.
+ * strict != 0 reproduces the reference's [0,p] forward representation bit for bit; strict == 0 returns
+ * the same residues canonicalised to [0,p). */
+void hb_ntt_forward(hb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D, int strict);
+void hb_ntt_inverse(hb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D);
+/* host-buffer variant: H2D, transform, D2H, synchronise */
+void hb_ntt_forward_host(hb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D, int strict);
+/* rns_decompose + ntt (rns.c:37-48): npoly DEVICE polynomials of W words -> out[npoly][D][N] */
+void hb_poly_ntt(hb_ctx *ctx, const uint64_t *polys, unsigned W, size_t npoly, unsigned D, uint64_t *out);
+/* poly_rns2mpi (poly.c:109-120) with modulus 2^k: limbs[npoly][D][N] -> words[npoly][Wout][N], DEVICE */
+void hb_rns2words(hb_ctx *ctx, const uint64_t *limbs, size_t npoly, unsigned D, unsigned k, unsigned Wout, uint64_t *out);
+/* poly_rot / poly_conj (poly.c:263-283) on DEVICE polynomials; rot < 0 means conjugation */
+void hb_poly_rot(hb_ctx *ctx, const uint64_t *polys, unsigned W, size_t npoly, int rot, uint64_t *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

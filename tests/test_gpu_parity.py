@@ -1,0 +1,218 @@
+"""GPU parity: the CUDA path (through the C ABI) against the compiled, unmodified reference
+(oracle/_ref/libgpqhe.so) on the same seeded inputs.  Integer work: bit-exact."""
+import numpy as np
+import pytest
+
+from conftest import random_ct_words
+
+pytestmark = pytest.mark.gpu
+
+A_PARAMS = (12, 109, 16, 50)      # config A: cstr-hempc (src/ctr.c:510-518)
+
+
+@pytest.fixture(scope="module")
+def cfgA(ref_available):
+    from oracle.ref import Ref
+    from hectr_b200 import Engine
+    ref = Ref.get(*A_PARAMS)
+    eng = Engine(*A_PARAMS)
+    pk, sk = ref.keypair()
+    rk = ref.genrk(sk)
+    rk_arr = np.stack([ref.evk_to_array(rk[i]) for i in range(ref.slots)])
+    keys = eng.keys(rk_arr)
+    yield dict(ref=ref, eng=eng, pk=pk, sk=sk, rk=rk, keys=keys)
+    keys.free()
+    eng.close()
+
+
+def _ref_ct(ref, words, l):
+    return ref.ct_from_words(words, l)
+
+
+def test_context_matches_reference(cfgA):
+    ref, eng = cfgA["ref"], cfgA["eng"]
+    i = eng.info
+    assert (i.L, i.dim, i.dimevk, i.dimub) == (ref.L, ref.dim, ref.dimevk, ref.dimub)
+    assert list(map(int, eng.primes())) == ref.primes()
+    for l in range(ref.L + 1):
+        assert 1 << eng.logq(l) == ref.q_level(l)
+
+
+@pytest.mark.parametrize("logn", [7, 12, 13, 14, 16])
+def test_ntt_bit_exact(ref_available, logn):
+    from oracle.ref import Ref
+    from hectr_b200 import Engine
+    logq = {7: 61, 12: 109, 13: 109, 14: 109, 16: 109}[logn]
+    slots, logD = (16, 50)
+    ref = Ref.get(logn, logq, slots, logD)
+    eng = Engine(logn, logq, slots, logD)
+    try:
+        n = 1 << logn
+        rng = np.random.default_rng(1234 + logn)
+        primes = ref.primes()
+        D = min(3, len(primes))
+        limbs = np.stack([rng.integers(0, primes[d], size=n, dtype=np.uint64) for d in range(D)] * 2)   # 2*D limbs
+        # adversarial limbs: zeros, all p-1, and p itself as an input
+        adv = np.zeros((3, n), dtype=np.uint64)
+        adv[1, :] = primes[0] - 1
+        adv[2, ::2] = primes[0]
+        want = np.stack([ref.ntt(limbs[j], j % D) for j in range(limbs.shape[0])])
+        got_strict = eng.ntt(limbs, 0, D, strict=True)
+        assert np.array_equal(got_strict, want), "strict forward NTT differs from ntt.c"
+        got = eng.ntt(limbs, 0, D, strict=False)
+        canon = np.stack([want[j] % np.uint64(primes[j % D]) for j in range(limbs.shape[0])])
+        assert np.array_equal(got, canon), "lazy forward NTT differs from canonicalised ntt.c"
+        want_adv = np.stack([ref.ntt(adv[j], 0) for j in range(3)])
+        assert np.array_equal(eng.ntt(adv, 0, 1, strict=True), want_adv)
+        assert np.array_equal(eng.ntt(adv, 0, 1, strict=False), want_adv % np.uint64(primes[0]))
+        # inverse: inputs as the reference would feed them (forward outputs, in [0,p])
+        want_inv = np.stack([ref.ntt(want[j], j % D, inverse=True) for j in range(limbs.shape[0])])
+        assert np.array_equal(eng.ntt(want, 0, D, inverse=True), want_inv)
+        assert np.array_equal(want_inv, limbs)     # round trip (size-independent property)
+        assert np.array_equal(eng.ntt(want_adv, 0, 1, inverse=True), np.stack([ref.ntt(want_adv[j], 0, inverse=True) for j in range(3)]))
+    finally:
+        eng.close()
+
+
+def test_decompose_ntt(cfgA):
+    ref, eng = cfgA["ref"], cfgA["eng"]
+    rng = np.random.default_rng(7)
+    for l, D in ((2, 7), (1, 3)):
+        W, k = eng.words(l), eng.logq(l)
+        words = random_ct_words(rng, 1, W, eng.n, k)[0]          # [2][W][N]
+        got = eng.poly_ntt(words, D)
+        for q in range(2):
+            poly = ref.alloc_poly()
+            ref.words_to_poly(poly, words[q])
+            for d in range(D):
+                want = ref.ntt(ref.rns_decompose(poly, d), d) % np.uint64(ref.primes()[d])
+                assert np.array_equal(got[q, d], want), (l, q, d)
+
+
+@pytest.mark.parametrize("D,k,W", [(2, 59, 1), (3, 109, 2), (7, 109, 2), (7, 59, 1), (4, 109, 2)])
+def test_reconstruct(cfgA, D, k, W):
+    ref, eng = cfgA["ref"], cfgA["eng"]
+    rng = np.random.default_rng(100 + D + k)
+    primes = ref.primes()
+    # valid products keep |x| < P_D/4; emulate by CRT-ing a bounded integer instead of random residues
+    bits = sum(p.bit_length() for p in primes[:D]) - D - 3
+    n = eng.n
+    vals = [int.from_bytes(rng.bytes((bits + 7) // 8), "little") % (1 << bits) * (1 if i % 2 else -1) for i in range(n)]
+    vals[0], vals[1], vals[2] = 0, 1, -1
+    limbs = np.array([[v % p for v in vals] for p in primes[:D]], dtype=np.uint64)
+    want = ref.rns2mpi(limbs, k, W)
+    got = eng.rns2words(limbs[None], k, W)[0]
+    assert np.array_equal(got, want)
+
+
+def test_add_sub_neg_rs_moddown(cfgA):
+    ref, eng = cfgA["ref"], cfgA["eng"]
+    rng = np.random.default_rng(11)
+    l = 2
+    W, k = eng.words(l), eng.logq(l)
+    a = random_ct_words(rng, 2, W, eng.n, k)
+    b = random_ct_words(rng, 2, W, eng.n, k)
+    # edge coefficients: extremes of the centred range and rounding ties for he_rs
+    a[0, 0, :, 0] = [0, 1 << 44]; b[0, 0, :, 0] = [0, 1 << 44]          # +q/4 + q/4 wraps to -q/2
+    a[0, 0, :, 1] = [0, (1 << 64) - (1 << 44)]                            # -q/2
+    a[0, 0, :, 2] = [1 << 49, 0]                                          # exact tie: rounds down
+    a[0, 0, :, 3] = [(1 << 49) + 1, 0]                                    # just above the tie
+    a[0, 0, :, 4] = [(1 << 64) - (1 << 49), (1 << 64) - 1]                # -2^49: tie on a negative
+    ea, eb = eng.ct(a, l), eng.ct(b, l)
+    for bi in range(2):
+        ra, rb = _ref_ct(ref, a[bi], l), _ref_ct(ref, b[bi], l)
+        assert np.array_equal(eng.he_add(ea, eb).download()[bi], ref.ct_to_words(ref.add(ra, rb)))
+        assert np.array_equal(eng.he_sub(ea, eb).download()[bi], ref.ct_to_words(ref.sub(ra, rb)))
+        n1 = eng.he_neg(eng.he_copy_ct(ea)).download()[bi]
+        assert np.array_equal(n1, ref.ct_to_words(ref.neg(ref.copy_ct(ra))))
+        r1 = eng.he_rs(eng.he_copy_ct(ea))
+        rr = ref.rs(ref.copy_ct(ra))
+        assert r1.l == rr.l == 1 and np.array_equal(r1.download()[bi], ref.ct_to_words(rr))
+        assert r1.nu == rr.nu and r1.B == rr.B
+        m1 = eng.he_moddown(eng.he_copy_ct(ea))
+        mr = ref.moddown(ref.copy_ct(ra))
+        assert np.array_equal(m1.download()[bi], ref.ct_to_words(mr))
+
+
+@pytest.mark.parametrize("l", [2, 1])
+def test_rot_all_rotations(cfgA, l):
+    ref, eng, keys = cfgA["ref"], cfgA["eng"], cfgA["keys"]
+    rng = np.random.default_rng(21 + l)
+    W, k = eng.words(l), eng.logq(l)
+    a = random_ct_words(rng, 2, W, eng.n, k)
+    a[0, :, :, 5] = [[0, (1 << 64) - (1 << 44)]] * 2 if W == 2 else [[(1 << 64) - (1 << 58)]] * 2   # -q/2 (negation edge)
+    for r in range(ref.slots):
+        got = eng.he_rot(eng.ct(a, l), r, keys).download()
+        for bi in range(2):
+            want = ref.ct_to_words(ref.rot(_ref_ct(ref, a[bi], l), r, cfgA["rk"]))
+            assert np.array_equal(got[bi], want), (l, r, bi)
+
+
+def test_mulpt(cfgA):
+    ref, eng = cfgA["ref"], cfgA["eng"]
+    rng = np.random.default_rng(31)
+    m = rng.standard_normal(16) + 1j * rng.standard_normal(16)
+    pt_ref = ref.encode(m)
+    pt_words = ref.poly_to_words(pt_ref.m, eng.info.words_top)
+    assert np.array_equal(eng.encode(m), pt_words), "host encoder differs from he_ecd"
+    pt = eng.pt(pt_words, pt_ref.nu)
+    for l in (2, 1):
+        a = random_ct_words(rng, 2, eng.words(l), eng.n, eng.logq(l))
+        got = eng.he_mulpt(eng.ct(a, l, nu=2.0 ** 50), pt)
+        for bi in range(2):
+            ra = _ref_ct(ref, a[bi], l)
+            ra.nu = 2.0 ** 50
+            want = ref.mulpt(ra, pt_ref)
+            assert np.array_equal(got.download()[bi], ref.ct_to_words(want)), (l, bi)
+            assert got.nu == want.nu and got.B == want.B
+
+
+def test_gemv_and_hempc(cfgA):
+    ref, eng, keys, pk, sk = cfgA["ref"], cfgA["eng"], cfgA["keys"], cfgA["pk"], cfgA["sk"]
+    rng = np.random.default_rng(41)
+    S = 16
+    Ka = np.zeros((S, S), dtype=np.complex128)
+    Kb = np.zeros((S, S), dtype=np.complex128)
+    Ka[:8, :3] = rng.standard_normal((8, 3))
+    Kb[:8, :2] = rng.standard_normal((8, 2))
+    cts = {}
+    vals = {}
+    for name in ("xhat", "xr", "uhat", "ur"):
+        v = np.zeros(S, dtype=np.complex128)
+        v[:3] = rng.standard_normal(3)
+        vals[name] = v
+        cts[name] = ref.enc_pk(ref.encode(v), pk)
+    w = {n: ref.ct_to_words(c)[None] for n, c in cts.items()}
+    e = {n: eng.ct(w[n], 2, nu=cts[n].nu, B=cts[n].B) for n in w}
+    # gemv alone
+    got = eng.he_gemv(Ka, e["xhat"], keys)
+    want = ref.gemv(Ka, cts["xhat"], cfgA["rk"])
+    assert got.l == want.l == 1
+    assert np.array_equal(got.download()[0], ref.ct_to_words(want)), "he_gemv ciphertext differs"
+    # the ciphertext half of ctr_hempc (src/hempc.c:253-266)
+    xd, ud = ref.sub(cts["xhat"], cts["xr"]), ref.sub(cts["uhat"], cts["ur"])
+    du = ref.neg(ref.add(ref.gemv(Ka, xd, cfgA["rk"]), ref.gemv(Kb, ud, cfgA["rk"])))
+    up_ref = ref.add(ref.moddown(ref.copy_ct(cts["uhat"])), du)
+    up = eng.ctr_hempc_eval(Ka, Kb, e["xhat"], e["xr"], e["uhat"], e["ur"], keys)
+    assert np.array_equal(up.download()[0], ref.ct_to_words(up_ref)), "ctr_hempc ciphertext differs"
+    out = eng.ctr_hempc_eval_host(Ka, Kb, w["xhat"], w["xr"], w["uhat"], w["ur"], keys, 2)
+    assert np.array_equal(out[0], ref.ct_to_words(up_ref))
+    # decrypted control action vs the plaintext computation (CKKS error; tolerance 1e-7 on O(1) values)
+    dec = ref.decode(ref.dec(up_ref, sk))
+    plain = vals["uhat"] - (Ka @ (vals["xhat"] - vals["xr"]) + Kb @ (vals["uhat"] - vals["ur"]))
+    assert np.abs(dec - plain).max() < 1e-7
+
+
+def test_mul_relin(cfgA):
+    ref, eng, pk, sk = cfgA["ref"], cfgA["eng"], cfgA["pk"], cfgA["sk"]
+    rlk = ref.genrlk(sk)
+    ekeys = eng.keys(ref.evk_to_array(rlk))
+    rng = np.random.default_rng(51)
+    for l in (2, 1):
+        a = random_ct_words(rng, 2, eng.words(l), eng.n, eng.logq(l))
+        b = random_ct_words(rng, 2, eng.words(l), eng.n, eng.logq(l))
+        got = eng.he_mul(eng.ct(a, l), eng.ct(b, l), ekeys).download()
+        for bi in range(2):
+            want = ref.mul(_ref_ct(ref, a[bi], l), _ref_ct(ref, b[bi], l), rlk)
+            assert np.array_equal(got[bi], ref.ct_to_words(want)), (l, bi)
+    ekeys.free()
