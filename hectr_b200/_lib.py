@@ -42,8 +42,8 @@ PROTOTYPES = {
     "hb_ctx_info": (None, [ctx_p, C.POINTER(HbInfo)]),
     "hb_ctx_words": (C.c_uint, [ctx_p, C.c_uint]),
     "hb_ctx_logq": (C.c_uint, [ctx_p, C.c_uint]),
-    "hb_ctx_primes": (None, [ctx_p, u64p]),
-    "hb_ctx_twiddles": (None, [ctx_p, C.c_uint, C.c_int, u64p]),
+    "hb_ctx_primes": (None, [ctx_p, vp]),
+    "hb_ctx_twiddles": (None, [ctx_p, C.c_uint, C.c_int, vp]),
     "hb_dim_keyswitch": (C.c_uint, [ctx_p, C.c_uint]),
     "hb_dim_mul": (C.c_uint, [ctx_p, C.c_uint]),
     "hb_dim_mulpt": (C.c_uint, [ctx_p, C.c_uint, C.c_double]),
@@ -55,9 +55,9 @@ PROTOTYPES = {
     "hb_tables_create": (vp, [C.c_uint, C.c_uint, C.c_uint, C.c_uint]),
     "hb_tables_destroy": (None, [vp]),
     "hb_tables_info": (None, [vp, C.POINTER(HbInfo)]),
-    "hb_tables_primes": (None, [vp, u64p]),
-    "hb_tables_twiddles": (None, [vp, C.c_uint, C.c_int, u64p]),
-    "hb_tables_crt": (None, [vp, C.c_uint, u64p, u64p, u64p]),
+    "hb_tables_primes": (None, [vp, vp]),
+    "hb_tables_twiddles": (None, [vp, C.c_uint, C.c_int, vp]),
+    "hb_tables_crt": (None, [vp, C.c_uint, vp, vp, vp]),
     "hb_tables_dim": (C.c_uint, [vp, C.c_int, C.c_uint, C.c_double]),
     "hb_tables_encode": (None, [vp, vp, C.c_double, vp]),
     "hb_tables_decode": (None, [vp, vp, C.c_uint, C.c_double, vp]),

@@ -600,7 +600,7 @@ static void keyswitch_inplace(hb_ctx *ctx, hb_ct *ct, unsigned ginv, const hb_ev
   if (!key || !key->p) hb_die("%s: evaluation key is not loaded", what);
   const hb::HostTables &h = ctx->ht;
   const unsigned D = hb::dim_keyswitch(h, ct->l);
-  if (D > h.dimevk) hb_die("%s: needs %u limbs but keys hold %u", what, D, h.dimevk);
+  if (D > h.dimevk || D > h.dimub) hb_die("%s: needs %u limbs but keys hold %u and the prime chain %u", what, D, h.dimevk, h.dimub);
   const int W = hb::words_of_level(h, ct->l), k = h.logq_l[ct->l];
   const size_t bstride = (size_t)2 * W * h.N;
   uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, (size_t)ct->batch * 2 * D * h.N * 8);

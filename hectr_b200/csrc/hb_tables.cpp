@@ -172,7 +172,8 @@ std::string build_tables(HostTables &t, unsigned logn, unsigned logq, unsigned s
   t.nbitsP = P.bits();
   t.nbitsPqL = t.nbitsP + logq;
   t.dimevk = (logq + 1 + t.nbitsPqL + logn) / LOGP + 1;         // precomp.c:407
-  if (t.dimevk > DU) return "internal: dimevk exceeds the prime chain";
+  // NB: for small rings dimevk can exceed dimub (e.g. logn=11, logq=54); the reference's hectx_init accepts
+  // that too and only its key generation walks off the prime list.  Key-switch entry points check D <= dimub.
   t.WP = (t.nbitsP + 63) / 64 + 1;
   t.ks_inv.assign(t.dim, 0); t.ks_inv_q.assign(t.dim, 0);
   t.ks_phat.assign((size_t)t.dim * t.WP, 0);

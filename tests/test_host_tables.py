@@ -36,14 +36,14 @@ def test_tables_match_reference(ref_available, params):
         assert info.nbitsP == ref.mpi_int(ref.hectx.P).bit_length()
         assert info.nbitsPqL == ref.mpi_int(ref.hectx.PqL).bit_length()
         primes = np.zeros(info.dimub, dtype=np.uint64)
-        lib.hb_tables_primes(t, primes.ctypes.data_as(_lib.u64p))
+        lib.hb_tables_primes(t, primes.ctypes.data_as(C.c_void_p))
         assert list(map(int, primes)) == ref.primes()
         n = info.n
         tw = np.zeros(n, dtype=np.uint64)
         for d in sorted({0, 1, info.dimub - 1}):
             p = int(primes[d])
             for inv in (0, 1):
-                lib.hb_tables_twiddles(t, d, inv, tw.ctypes.data_as(_lib.u64p))
+                lib.hb_tables_twiddles(t, d, inv, tw.ctypes.data_as(C.c_void_p))
                 mont = ref.zetas(d, inv=bool(inv))          # zeta * 2^64 mod p  (precomp.c:258-259)
                 idx = np.random.default_rng(d).integers(0, n, size=64)
                 for i in list(idx) + [0, 1, n - 1]:
@@ -54,7 +54,7 @@ def test_tables_match_reference(ref_available, params):
             inv = np.zeros(D, dtype=np.uint64)
             phat = np.zeros((D, WC), dtype=np.uint64)
             Plow = np.zeros(WC, dtype=np.uint64)
-            lib.hb_tables_crt(t, D, inv.ctypes.data_as(_lib.u64p), phat.ctypes.data_as(_lib.u64p), Plow.ctypes.data_as(_lib.u64p))
+            lib.hb_tables_crt(t, D, inv.ctypes.data_as(C.c_void_p), phat.ctypes.data_as(C.c_void_p), Plow.ctypes.data_as(C.c_void_p))
             node = ref.node(D - 1)
             P = ref.mpi_int(node.P)
             mask = (1 << (64 * WC)) - 1
