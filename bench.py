@@ -1,0 +1,490 @@
+#!/usr/bin/env python
+"""bench.py -- encrypted CSTR MPC iterations/s (BASELINE.json metric) on N B200s of one node.
+
+One *step* = one pass of the ciphertext half of ctr_hempc (src/hempc.c:253-266: 2 he_sub, 2 he_gemv, he_add,
+he_neg, he_copy_ct, he_moddown, he_add) over a batch of independent controller instances (config E: 4096
+instances of the `cstr-hempc` parameter set N=4096, q=2^109, Delta=2^50, slots=16; shared keys and gain
+matrices).  Instances are sharded contiguously across ranks (strong scaling, no data-path collective); with
+N>1 the result ciphertexts are gathered with one NCCL all_gather per step.
+
+    python bench.py [--gpus N --steps K --warmup W]          # our arm
+    python bench.py --impl reference [...]                     # the reference's own CPU path (oracle/_ref), all host cores
+
+Prints ONE JSON line (rank 0).  Inputs are synthetic: uniform random ciphertext words in the centred range of
+q_l (what an RLWE ciphertext looks like), uniform random key limbs, random gain matrices with the hempc block
+structure.  The arithmetic is identical for any input values (no data-dependent control flow in the kernels).
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+PARAMS = dict(logn=12, logq=109, slots=16, logDelta=50)     # src/ctr.c:510-518
+METRIC = "encrypted CSTR MPC iterations/s"
+UNIT = "iterations/s"
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            d = json.load(open(path))
+            return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------------
+# clocks sampler
+# ------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+
+    def __init__(self, index: int):
+        self.index = index
+        self.samples = []
+        self.proc = None
+        self.thread = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index), "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+            return
+        def run():
+            for line in self.proc.stdout:
+                self.samples.append(line.strip())
+        self.thread = threading.Thread(target=run, daemon=True)
+        self.thread.start()
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], None, set()
+        for s in self.samples:
+            f = [x.strip() for x in s.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                smax = float(f[1])
+            except ValueError:
+                continue
+            for name, v in zip(self.NAMES, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------------
+# synthetic workload
+# ------------------------------------------------------------------------------------------------------
+def synth_ct_into(buf: np.ndarray, rng, k: int):
+    """Fill uint64[B][2][W][N] with uniform two's-complement coefficients in [-2^(k-1), 2^(k-1))."""
+    B, _, W, n = buf.shape
+    chunk = max(1, (1 << 24) // (2 * W * n))
+    for s in range(0, B, chunk):
+        e = min(B, s + chunk)
+        buf[s:e] = rng.integers(0, 1 << 64, size=(e - s, 2, W, n), dtype=np.uint64)
+    top = k - 64 * (W - 1)
+    if top < 64:
+        t = buf[:, :, W - 1, :].view(np.int64)
+        t <<= np.int64(64 - top)
+        t >>= np.int64(64 - top)
+
+
+def synth_keys(eng, rng):
+    primes = eng.primes()
+    i = eng.info
+    keys = np.empty((eng.slots, 2, i.dimevk, eng.n), dtype=np.uint64)
+    for d in range(i.dimevk):
+        keys[:, :, d, :] = rng.integers(0, int(primes[d]), size=(eng.slots, 2, eng.n), dtype=np.uint64)
+    return keys
+
+
+def synth_gains(rng, slots, nx=3, nu=2, horizon=4):
+    """Ka (mN x n) and Kb (mN x m) zero-padded to slots x slots, as ctr_hempc builds them (src/hempc.c:232-238)."""
+    Ka = np.zeros((slots, slots), dtype=np.complex128)
+    Kb = np.zeros((slots, slots), dtype=np.complex128)
+    Ka[: nu * horizon, :nx] = rng.standard_normal((nu * horizon, nx))
+    Kb[: nu * horizon, :nu] = rng.standard_normal((nu * horizon, nu))
+    return Ka, Kb
+
+
+def pinned_array(eng, shape):
+    nbytes = int(np.prod(shape)) * 8
+    p = eng.lib.hb_host_alloc(eng.ctx, nbytes)
+    arr = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint64)), shape=(int(np.prod(shape)),)).reshape(shape)
+    return arr, p
+
+
+# algorithmic bytes per launch, config A, batch B instances per launch
+def algorithmic_bytes(kernel: str, B: int, n: int, W: int, D_ks: int, D_pt: int):
+    ct_poly = n * W * 8
+    table = {
+        # one key switch: read d0,d1 + write c0,c1 + keys shared over the batch (2*D*N*8 / B per unit)
+        "k_ks_limb": B * (2 * ct_poly + 2 * ct_poly) + 2 * D_ks * n * 8,
+        "k_ks_finish": B * (2 * ct_poly + 2 * ct_poly) + 2 * D_ks * n * 8,
+        # one ct x pt: ct in + ct out + plaintext (shared)
+        "k_mulpt_limb": B * (2 * ct_poly + 2 * ct_poly) + D_pt * n * 8,
+        "k_recon_smod": B * (2 * ct_poly + 2 * ct_poly) + D_pt * n * 8,
+        "k_ct_addsub": B * 3 * 2 * ct_poly,
+        "k_ct_rescale": B * 2 * 2 * ct_poly,
+    }
+    return table.get(kernel)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from hectr_b200 import Engine
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    total = args.instances
+    per = total // world
+    assert per * world == total, "instances must divide by the number of GPUs"
+
+    eng = Engine(PARAMS["logn"], PARAMS["logq"], PARAMS["slots"], PARAMS["logDelta"], device=local)
+    lib, ctx = eng.lib, eng.ctx
+    stream = torch.cuda.current_stream()
+    lib.hb_ctx_set_stream(ctx, C.c_void_p(stream.cuda_stream))
+    l = eng.L
+    W, k, n = eng.words(l), eng.logq(l), eng.n
+    Wout = eng.words(l - 1)
+    rng = np.random.default_rng(0x48454354 + rank)
+    keys = eng.keys(synth_keys(eng, np.random.default_rng(7)))
+    Ka, Kb = synth_gains(np.random.default_rng(9), eng.slots)
+
+    names = ("xhat", "xr", "uhat", "ur")
+    host, hptr = {}, {}
+    for nm in names:
+        host[nm], hptr[nm] = pinned_array(eng, (per, 2, W, n))
+        synth_ct_into(host[nm], rng, k)
+    out_host, out_ptr = pinned_array(eng, (per, 2, Wout, n))
+    dev = {nm: eng.ct(batch=per) for nm in names}
+    Delta = 2.0 ** PARAMS["logDelta"]
+    for nm in names:
+        lib.hb_ct_upload(ctx, C.byref(dev[nm].h), host[nm].ctypes.data_as(C.c_void_p), l, Delta, 1.0)
+    up = eng.ct(batch=per)
+    gather_in = torch.empty(per * 2 * Wout * n, dtype=torch.int64, device="cuda")
+    gather_out = torch.empty(world * per * 2 * Wout * n, dtype=torch.int64, device="cuda") if world > 1 else None
+
+    def step():
+        eng.ctr_hempc_eval(Ka, Kb, dev["xhat"], dev["xr"], dev["uhat"], dev["ur"], keys, out=up)
+        if world > 1:      # the only collective: gather the result ciphertexts (north_star)
+            lib.hb_ct_export(ctx, C.byref(up.h), C.c_void_p(gather_in.data_ptr()))
+            dist.all_gather_into_tensor(gather_out, gather_in)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    lib.hb_prof_reset(ctx)
+    lib.hb_prof_enable(ctx, 1)
+    launches0 = eng.launches()
+    lib.hb_timer_start(ctx)
+    for _ in range(args.steps):
+        step()
+    ms = float(lib.hb_timer_stop_ms(ctx))
+    barrier()
+    launches = eng.launches() - launches0
+    lib.hb_prof_enable(ctx, 0)
+    need = lib.hb_prof_report(ctx, None, 0)
+    buf = C.create_string_buffer(need + 1)
+    lib.hb_prof_report(ctx, buf, need + 1)
+    prof = json.loads(buf.value.decode())
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = total * args.steps / (ms / 1e3)
+
+    # ---- end to end through the C ABI with host buffers: H2D of the 4 input batches + evaluate + D2H of the result ----
+    def e2e_step():
+        lib.hb_ctr_hempc_eval_host(ctx, per, l, Ka.ctypes.data_as(C.c_void_p), Kb.ctypes.data_as(C.c_void_p),
+                                   C.c_void_p(hptr["xhat"]), C.c_void_p(hptr["xr"]), C.c_void_p(hptr["uhat"]),
+                                   C.c_void_p(hptr["ur"]), keys.arr, C.c_void_p(out_ptr))
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_value = total * args.steps / e2e_s
+    h2d = 4 * per * 2 * W * n * 8
+    d2h = per * 2 * Wout * n * 8
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel, timed live with CUDA events in the region above ----
+    peak, peak_src = load_peaks()
+    D_ks = lib.hb_dim_keyswitch(ctx, l)
+    D_pt = lib.hb_dim_mulpt(ctx, l, Delta)
+    tot_ms = sum(v["ms"] for v in prof.values()) or 1.0
+    dom = max(prof, key=lambda kname: prof[kname]["ms"])
+    avg_ms = prof[dom]["ms"] / prof[dom]["launches"]
+    abytes = algorithmic_bytes(dom, per, n, W, D_ks, D_pt)
+    achieved = abytes / (avg_ms / 1e3) / 1e9 if abytes else None
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get(dom, {}).get(str(per))
+        except Exception:
+            traffic = None
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": abytes, "avg_launch_ms": avg_ms,
+                "share_of_step": prof[dom]["ms"] / tot_ms,
+                "kernels": {kname: {"launches": v["launches"], "ms": round(v["ms"], 3), "share": round(v["ms"] / tot_ms, 4)}
+                            for kname, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])},
+                "note": "integer-pipe bound path (59-bit modular butterflies); HBM fraction is reported as the contract asks"}
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline_single(n_eval=args.cpu_evals)
+    ntt = None
+    if not args.no_ntt:
+        try:
+            ntt = ntt_microbench(local, peak)
+        except Exception as ex:  # pragma: no cover
+            ntt = {"error": str(ex)}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "u64", "data": "synthetic (uniform random ciphertext words and key limbs, random 8x3 / 8x2 gain blocks)",
+        "config": {"workload": f"{total} independent cstr-hempc controller instances (BASELINE configs[4] on configs[0] parameters)",
+                   "logn": PARAMS["logn"], "logq": PARAMS["logq"], "logDelta": PARAMS["logDelta"], "slots": PARAMS["slots"],
+                   "instances": total, "instances_per_gpu": per, "parallelism": f"instances sharded x{world}, keys replicated",
+                   "l2": f"inputs larger than L2 ({4 * per * 2 * W * n * 8 >> 20} MiB of ciphertext per GPU per step)"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "api": "hb_ctr_hempc_eval_host (pinned host buffers in, pinned host buffer out)"},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": roofline,
+        "cpu_baseline": cpu,
+        "ntt": ntt,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------------
+# secondary metric: N=2^16 batched forward NTT limbs/s (BASELINE configs[1])
+# ------------------------------------------------------------------------------------------------------
+def ntt_microbench(device: int, peak: float, logn: int = 16, nlimbs: int = 1024, D: int = 8, reps: int = 5):
+    from hectr_b200 import Engine
+    eng = Engine(logn, 109, 16, 50, device=device)
+    lib, ctx = eng.lib, eng.ctx
+    n = eng.n
+    primes = eng.primes()
+    rng = np.random.default_rng(3)
+    host = np.empty((nlimbs, n), dtype=np.uint64)
+    for j in range(nlimbs):
+        host[j] = rng.integers(0, int(primes[j % D]), size=n, dtype=np.uint64)
+    d_in = eng.to_device(host)
+    d_out = eng.dev_alloc(host.nbytes)
+    res = {}
+    for name, fn in (("forward", lambda: lib.hb_ntt_forward(ctx, d_in, d_out, nlimbs, 0, D, 0)),
+                     ("inverse", lambda: lib.hb_ntt_inverse(ctx, d_in, d_out, nlimbs, 0, D))):
+        for _ in range(3):
+            fn()
+        eng.sync()
+        lib.hb_timer_start(ctx)
+        for _ in range(reps):
+            fn()
+        ms = float(lib.hb_timer_stop_ms(ctx)) / reps
+        gbs = 16.0 * n * nlimbs / (ms / 1e3) / 1e9
+        res[name] = {"limbs_per_s": nlimbs / (ms / 1e3), "ms_per_launch": ms, "achieved_gbs": gbs, "frac_of_hbm": gbs / peak}
+    eng.dev_free(d_in)
+    eng.dev_free(d_out)
+    eng.close()
+    return {"metric": "N=2^16 NTT limbs/s", "logn": logn, "limbs_per_launch": nlimbs, "primes": D,
+            "algorithmic_bytes_per_limb": 16 * n, "l2": f"{host.nbytes >> 20} MiB in + out per launch (> L2)", **res}
+
+
+# ------------------------------------------------------------------------------------------------------
+# CPU baseline: the reference's own code (oracle/_ref), timed on this box's host cores
+# ------------------------------------------------------------------------------------------------------
+def _ref_setup(opt="Og"):
+    from oracle.ref import Ref
+    ref = Ref.get(PARAMS["logn"], PARAMS["logq"], PARAMS["slots"], PARAMS["logDelta"], opt=opt)
+    pk, sk = ref.keypair()
+    rk = ref.genrk(sk)
+    rng = np.random.default_rng(9)
+    Ka, Kb = synth_gains(rng, PARAMS["slots"])
+    cts = {}
+    for nm in ("xhat", "xr", "uhat", "ur"):
+        v = np.zeros(PARAMS["slots"], dtype=np.complex128)
+        v[:3] = rng.standard_normal(3)
+        cts[nm] = ref.enc_pk(ref.encode(v), pk)
+    return ref, rk, Ka, Kb, cts
+
+
+def _ref_eval(ref, rk, Ka, Kb, cts):
+    """The ciphertext half of ctr_hempc through the reference's API, in the reference's order (hempc.c:253-266)."""
+    xd, ud = ref.sub(cts["xhat"], cts["xr"]), ref.sub(cts["uhat"], cts["ur"])
+    a, b = ref.gemv(Ka, xd, rk), ref.gemv(Kb, ud, rk)
+    du = ref.neg(ref.add(a, b))
+    uc = ref.moddown(ref.copy_ct(cts["uhat"]))
+    up = ref.add(uc, du)
+    for c in (xd, ud, a, b, du, uc, up):
+        ref.free_ct(c)
+
+
+def cpu_baseline_single(n_eval=3):
+    from oracle import ref as R
+    if not R.available():
+        return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+    ref, rk, Ka, Kb, cts = _ref_setup()
+    _ref_eval(ref, rk, Ka, Kb, cts)   # warm
+    t0 = time.perf_counter()
+    for _ in range(n_eval):
+        _ref_eval(ref, rk, Ka, Kb, cts)
+    dt = time.perf_counter() - t0
+    return {"value": n_eval / dt, "unit": UNIT, "cores": 1, "kind": "reference",
+            "sample": f"{n_eval} single-instance ctr_hempc ciphertext evaluations through oracle/_ref/libgpqhe.so "
+                      f"(unmodified reference, -Og as its Makefile builds it), {dt:.1f} s",
+            "flags": "-Og -fomit-frame-pointer -DSUPERCOP"}
+
+
+def _ref_worker(q_in, q_out, opt):
+    ref, rk, Ka, Kb, cts = _ref_setup(opt)
+    q_out.put("ready")
+    while True:
+        n = q_in.get()
+        if n is None:
+            break
+        t0 = time.perf_counter()
+        for _ in range(n):
+            _ref_eval(ref, rk, Ka, Kb, cts)
+        q_out.put(time.perf_counter() - t0)
+
+
+def run_reference(args):
+    """--impl reference: the unmodified reference on all host cores.  It is single-threaded with process-global state
+    (SURVEY F9), so 'all cores' = one process per core, each evaluating its own instance."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import ref as R
+    if not R.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref is not built on this box"}))
+        return
+    import multiprocessing as mp
+    mpctx = mp.get_context("spawn")
+    P = args.cpu_procs or os.cpu_count() or 1
+    per_step = 1                                    # evaluations per process per step
+    qs = [(mpctx.Queue(), mpctx.Queue()) for _ in range(P)]
+    procs = [mpctx.Process(target=_ref_worker, args=(qi, qo, args.ref_opt), daemon=True) for qi, qo in qs]
+    for p in procs:
+        p.start()
+    for _, qo in qs:
+        qo.get()
+
+    def step():
+        t0 = time.perf_counter()
+        for qi, _ in qs:
+            qi.put(per_step)
+        for _, qo in qs:
+            qo.get()
+        return time.perf_counter() - t0
+
+    for _ in range(args.warmup):
+        step()
+    t = sum(step() for _ in range(args.steps))
+    for qi, _ in qs:
+        qi.put(None)
+    for p in procs:
+        p.join(timeout=10)
+    value = P * per_step * args.steps / t
+    total = args.instances
+    flags = "-Og -fomit-frame-pointer -DSUPERCOP" if args.ref_opt == "Og" else "-O2 -fomit-frame-pointer -DSUPERCOP"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "u64", "data": "synthetic (reference-encrypted random states, random gain blocks)",
+        "config": {"workload": f"{total} independent cstr-hempc controller instances (BASELINE configs[4] on configs[0] parameters)",
+                   "logn": PARAMS["logn"], "logq": PARAMS["logq"], "logDelta": PARAMS["logDelta"], "slots": PARAMS["slots"],
+                   "instances": total},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": P, "kind": "reference", "flags": flags,
+                         "sample": f"each step = {P} processes x {per_step} ctr_hempc ciphertext evaluation(s) of the {total}-instance "
+                                   f"workload (bounded sample; the reference is single-threaded, one process per core)"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--instances", type=int, default=4096, help="controller instances in the whole job")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ntt", action="store_true")
+    ap.add_argument("--cpu-evals", type=int, default=3)
+    ap.add_argument("--cpu-procs", type=int, default=0)
+    ap.add_argument("--ref-opt", default="Og", choices=["Og", "O2"])
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -52,6 +52,11 @@ PROTOTYPES = {
     "hb_timer_start": (None, [ctx_p]),
     "hb_timer_stop_ms": (C.c_float, [ctx_p]),
     "hb_launch_count": (C.c_uint64, [ctx_p]),
+    "hb_prof_enable": (None, [ctx_p, C.c_int]),
+    "hb_prof_reset": (None, [ctx_p]),
+    "hb_prof_report": (C.c_size_t, [ctx_p, C.c_char_p, C.c_size_t]),
+    "hb_ct_export": (None, [ctx_p, ct_p, vp]),
+    "hb_ct_import": (None, [ctx_p, ct_p, vp, C.c_uint, C.c_double, C.c_double]),
     "hb_tables_create": (vp, [C.c_uint, C.c_uint, C.c_uint, C.c_uint]),
     "hb_tables_destroy": (None, [vp]),
     "hb_tables_info": (None, [vp, C.POINTER(HbInfo)]),

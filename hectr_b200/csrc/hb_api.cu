@@ -54,6 +54,11 @@ struct hb_ctx {
   cudaStream_t stream = nullptr, own_stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   uint64_t launches = 0;
+  // optional per-kernel CUDA-event timing (bench.py roofline): name -> (launches, event pairs)
+  bool prof = false;
+  struct ProfRec { uint64_t n = 0; double ms = 0; std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending; };
+  std::map<std::string, ProfRec> prof_recs;
+  std::vector<cudaEvent_t> prof_free;
   // workspaces (grow only)
   uint64_t *wsA = nullptr, *wsB = nullptr;
   size_t wsA_bytes = 0, wsB_bytes = 0;
@@ -65,12 +70,23 @@ struct hb_ctx {
   std::vector<uint64_t> enc_host;   // [WC][N] scratch for hb_he_ecd / gemv plans
 };
 
+static void need_ct(const hb_ct *ct, const char *what);
+static size_t ct_words(const hb_ctx *ctx, const hb_ct *ct);
+static void check_level(const hb_ctx *ctx, unsigned l);
+
 // ---------------------------------------------------------------------------------------------------------
 // launch helpers
 // ---------------------------------------------------------------------------------------------------------
+static cudaEvent_t prof_event(hb_ctx *ctx) {
+  if (!ctx->prof_free.empty()) { cudaEvent_t e = ctx->prof_free.back(); ctx->prof_free.pop_back(); return e; }
+  cudaEvent_t e;
+  CUDA_OK(cudaEventCreate(&e));
+  return e;
+}
+
 template <class... KArgs, class... Args>
-static void launch(hb_ctx *ctx, void (*kernel)(KArgs...), unsigned grid, unsigned threads, size_t smem, int cluster,
-                   Args... args) {
+static void launch(hb_ctx *ctx, const char *name, void (*kernel)(KArgs...), unsigned grid, unsigned threads, size_t smem,
+                   int cluster, Args... args) {
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof cfg);
   cfg.gridDim = dim3(grid, 1, 1);
@@ -86,7 +102,15 @@ static void launch(hb_ctx *ctx, void (*kernel)(KArgs...), unsigned grid, unsigne
     cfg.attrs = at;
     cfg.numAttrs = 1;
   }
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (ctx->prof) { e0 = prof_event(ctx); e1 = prof_event(ctx); CUDA_OK(cudaEventRecord(e0, ctx->stream)); }
   CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...));
+  if (ctx->prof) {
+    CUDA_OK(cudaEventRecord(e1, ctx->stream));
+    hb_ctx::ProfRec &r = ctx->prof_recs[name];
+    r.n++;
+    r.pending.push_back({e0, e1});
+  }
   ctx->launches++;
 }
 
@@ -108,34 +132,34 @@ struct Launch {
   static void ntt_fwd(hb_ctx *c, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D, bool strict) {
     if (strict) {
       want_smem(hbdev::k_ntt_fwd<LOGN, true>, G::SMEM_BYTES);
-      launch(c, hbdev::k_ntt_fwd<LOGN, true>, (unsigned)(nlimbs * G::C), G::THREADS, G::SMEM_BYTES, G::C, in, out, c->dt, d0, D);
+      launch(c, "k_ntt_fwd_strict", hbdev::k_ntt_fwd<LOGN, true>, (unsigned)(nlimbs * G::C), G::THREADS, G::SMEM_BYTES, G::C, in, out, c->dt, d0, D);
     } else {
       want_smem(hbdev::k_ntt_fwd<LOGN, false>, G::SMEM_BYTES);
-      launch(c, hbdev::k_ntt_fwd<LOGN, false>, (unsigned)(nlimbs * G::C), G::THREADS, G::SMEM_BYTES, G::C, in, out, c->dt, d0, D);
+      launch(c, "k_ntt_fwd", hbdev::k_ntt_fwd<LOGN, false>, (unsigned)(nlimbs * G::C), G::THREADS, G::SMEM_BYTES, G::C, in, out, c->dt, d0, D);
     }
   }
   static void ntt_inv(hb_ctx *c, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D) {
     want_smem(hbdev::k_ntt_inv<LOGN>, G::SMEM_BYTES);
-    launch(c, hbdev::k_ntt_inv<LOGN>, (unsigned)(nlimbs * G::C), G::THREADS, G::SMEM_BYTES, G::C, in, out, c->dt, d0, D);
+    launch(c, "k_ntt_inv", hbdev::k_ntt_inv<LOGN>, (unsigned)(nlimbs * G::C), G::THREADS, G::SMEM_BYTES, G::C, in, out, c->dt, d0, D);
   }
   static void poly_ntt(hb_ctx *c, const uint64_t *src, size_t stride, int W, uint64_t *out, unsigned D, size_t npoly) {
     want_smem(hbdev::k_poly_ntt<LOGN>, G::SMEM_BYTES);
-    launch(c, hbdev::k_poly_ntt<LOGN>, (unsigned)(npoly * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, src, stride, W, out, c->dt, D);
+    launch(c, "k_poly_ntt", hbdev::k_poly_ntt<LOGN>, (unsigned)(npoly * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, src, stride, W, out, c->dt, D);
   }
   static void ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, unsigned ginv, const uint64_t *evk,
                       uint64_t *chat, unsigned D, unsigned batch) {
     want_smem(hbdev::k_ks_limb<LOGN>, 2 * G::SMEM_BYTES);
-    launch(c, hbdev::k_ks_limb<LOGN>, (unsigned)((size_t)batch * D * G::C), G::THREADS, 2 * G::SMEM_BYTES, G::C, src, bstride, W,
+    launch(c, "k_ks_limb", hbdev::k_ks_limb<LOGN>, (unsigned)((size_t)batch * D * G::C), G::THREADS, 2 * G::SMEM_BYTES, G::C, src, bstride, W,
            ginv, evk, c->ht.dimevk, chat, c->dt, D);
   }
   static void mulpt_limb(hb_ctx *c, const uint64_t *ct, int W, const uint64_t *pthat, uint64_t *chat, unsigned D, unsigned batch) {
     want_smem(hbdev::k_mulpt_limb<LOGN>, G::SMEM_BYTES);
-    launch(c, hbdev::k_mulpt_limb<LOGN>, (unsigned)((size_t)batch * 2 * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, ct, W, pthat,
+    launch(c, "k_mulpt_limb", hbdev::k_mulpt_limb<LOGN>, (unsigned)((size_t)batch * 2 * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, ct, W, pthat,
            chat, c->dt, D);
   }
   static void tensor_intt(hb_ctx *c, const uint64_t *hatA, const uint64_t *hatB, uint64_t *dhat, unsigned D, unsigned batch) {
     want_smem(hbdev::k_tensor_intt<LOGN>, G::SMEM_BYTES);
-    launch(c, hbdev::k_tensor_intt<LOGN>, (unsigned)((size_t)batch * 3 * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, hatA, hatB, dhat, c->dt, D);
+    launch(c, "k_tensor_intt", hbdev::k_tensor_intt<LOGN>, (unsigned)((size_t)batch * 3 * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, hatA, hatB, dhat, c->dt, D);
   }
 };
 
@@ -180,7 +204,7 @@ static void do_recon_smod(hb_ctx *c, const uint64_t *chat, unsigned D, uint64_t 
   const unsigned grid = (unsigned)((total + threads - 1) / threads);
   const unsigned wk = (k + 63) / 64;
   switch (wk_class(wk)) {
-#define X(WKC) case WKC: launch(c, hbdev::k_recon_smod<WKC>, grid, threads, 0, 1, chat, D, out, Wout, k, c->dt, (unsigned)npoly); break;
+#define X(WKC) case WKC: launch(c, "k_recon_smod", hbdev::k_recon_smod<WKC>, grid, threads, 0, 1, chat, D, out, Wout, k, c->dt, (unsigned)npoly); break;
     X(1) X(2) X(4) X(8) X(16)
 #undef X
   }
@@ -191,7 +215,7 @@ static void ks_finish_wp(hb_ctx *c, unsigned grid, unsigned threads, const uint6
                          const uint64_t *add1, size_t add_bstride, int Wadd, unsigned ginv, uint64_t *out, int Wout, int k,
                          unsigned batch) {
   switch (wp_class(c->ht.WP)) {
-#define X(WPC) case WPC: launch(c, hbdev::k_ks_finish<WKC, WPC>, grid, threads, 0, 1, chat, D, add0, add1, add_bstride, Wadd, ginv, out, Wout, k, c->dt, batch); break;
+#define X(WPC) case WPC: launch(c, "k_ks_finish", hbdev::k_ks_finish<WKC, WPC>, grid, threads, 0, 1, chat, D, add0, add1, add_bstride, Wadd, ginv, out, Wout, k, c->dt, batch); break;
     X(4) X(8) X(12) X(20)
 #undef X
   }
@@ -282,6 +306,9 @@ extern "C" void hb_ctx_destroy(hb_ctx *ctx) {
   for (auto &kv : ctx->pool) cudaFree(kv.second);
   for (auto &kv : ctx->live) cudaFree(kv.first);
   for (auto &pl : ctx->plans) cudaFree(pl.pthat);
+  for (auto &kv : ctx->prof_recs)
+    for (auto &pr : kv.second.pending) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+  for (cudaEvent_t e : ctx->prof_free) cudaEventDestroy(e);
   cudaFree(ctx->wsA);
   cudaFree(ctx->wsB);
   cudaEventDestroy(ctx->ev0);
@@ -323,6 +350,44 @@ extern "C" float hb_timer_stop_ms(hb_ctx *ctx) {
   return ms;
 }
 extern "C" uint64_t hb_launch_count(const hb_ctx *ctx) { return ctx->launches; }
+extern "C" void hb_prof_enable(hb_ctx *ctx, int on) { ctx->prof = on != 0; }
+extern "C" void hb_prof_reset(hb_ctx *ctx) {
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  for (auto &kv : ctx->prof_recs)
+    for (auto &pr : kv.second.pending) { ctx->prof_free.push_back(pr.first); ctx->prof_free.push_back(pr.second); }
+  ctx->prof_recs.clear();
+}
+extern "C" size_t hb_prof_report(hb_ctx *ctx, char *buf, size_t cap) {
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  std::string out = "{";
+  bool first = true;
+  for (auto &kv : ctx->prof_recs) {
+    for (auto &pr : kv.second.pending) {
+      float ms = 0;
+      CUDA_OK(cudaEventElapsedTime(&ms, pr.first, pr.second));
+      kv.second.ms += ms;
+      ctx->prof_free.push_back(pr.first); ctx->prof_free.push_back(pr.second);
+    }
+    kv.second.pending.clear();
+    char line[256];
+    snprintf(line, sizeof line, "%s\"%s\": {\"launches\": %llu, \"ms\": %.6f}", first ? "" : ", ", kv.first.c_str(),
+             (unsigned long long)kv.second.n, kv.second.ms);
+    out += line;
+    first = false;
+  }
+  out += "}";
+  if (buf && cap) { size_t n = out.size() < cap - 1 ? out.size() : cap - 1; memcpy(buf, out.data(), n); buf[n] = 0; }
+  return out.size();
+}
+extern "C" void hb_ct_export(hb_ctx *ctx, const hb_ct *ct, void *dst_device) {
+  need_ct(ct, "hb_ct_export");
+  CUDA_OK(cudaMemcpyAsync(dst_device, ct->words, ct_words(ctx, ct) * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+}
+extern "C" void hb_ct_import(hb_ctx *ctx, hb_ct *ct, const void *src_device, unsigned l, double nu, double B) {
+  need_ct(ct, "hb_ct_import"); check_level(ctx, l);
+  ct->l = l; ct->nu = nu; ct->B = B;
+  CUDA_OK(cudaMemcpyAsync(ct->words, src_device, ct_words(ctx, ct) * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+}
 
 // ---------------------------------------------------------------------------------------------------------
 // host-only tables view
@@ -528,7 +593,7 @@ static void addsub(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b, int o
   ct->B = a->B + b->B;
   const int W = hb::words_of_level(ctx->ht, ct->l), k = ctx->ht.logq_l[ct->l];
   const size_t npoly = (size_t)ct->batch * 2, total = npoly * ctx->ht.N;
-  launch(ctx, hbdev::k_ct_addsub, (unsigned)((total + 255) / 256), 256, 0, 1, a->words, b->words, ct->words, W, k, op, ctx->ht.N, npoly);
+  launch(ctx, "k_ct_addsub", hbdev::k_ct_addsub, (unsigned)((total + 255) / 256), 256, 0, 1, a->words, b->words, ct->words, W, k, op, ctx->ht.N, npoly);
 }
 extern "C" void hb_he_add(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b) { addsub(ctx, ct, a, b, 0, "hb_he_add"); }
 extern "C" void hb_he_sub(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b) { addsub(ctx, ct, a, b, 1, "hb_he_sub"); }
@@ -536,7 +601,7 @@ extern "C" void hb_he_neg(hb_ctx *ctx, hb_ct *ct) {
   need_ct(ct, "hb_he_neg");
   const int W = hb::words_of_level(ctx->ht, ct->l), k = ctx->ht.logq_l[ct->l];
   const size_t npoly = (size_t)ct->batch * 2, total = npoly * ctx->ht.N;
-  launch(ctx, hbdev::k_ct_addsub, (unsigned)((total + 255) / 256), 256, 0, 1, ct->words, (const uint64_t *)nullptr, ct->words, W, k, 2,
+  launch(ctx, "k_ct_addsub", hbdev::k_ct_addsub, (unsigned)((total + 255) / 256), 256, 0, 1, ct->words, (const uint64_t *)nullptr, ct->words, W, k, 2,
          ctx->ht.N, npoly);
 }
 
@@ -548,7 +613,7 @@ static void rescale_like(hb_ctx *ctx, hb_ct *ct, int shift, const char *what) {
   const int Wout = hb::words_of_level(ctx->ht, ct->l), kout = ctx->ht.logq_l[ct->l];
   uint64_t *out = pool_get(ctx, ct_capacity(ctx, ct->batch));
   const size_t npoly = (size_t)ct->batch * 2, total = npoly * ctx->ht.N;
-  launch(ctx, hbdev::k_ct_rescale, (unsigned)((total + 255) / 256), 256, 0, 1, ct->words, out, Win, Wout, shift, kout, ctx->ht.N, npoly);
+  launch(ctx, "k_ct_rescale", hbdev::k_ct_rescale, (unsigned)((total + 255) / 256), 256, 0, 1, ct->words, out, Win, Wout, shift, kout, ctx->ht.N, npoly);
   pool_put(ctx, ct->words);
   ct->words = out;
 }
@@ -822,5 +887,5 @@ extern "C" void hb_rns2words(hb_ctx *ctx, const uint64_t *limbs, size_t npoly, u
 extern "C" void hb_poly_rot(hb_ctx *ctx, const uint64_t *polys, unsigned W, size_t npoly, int rot, uint64_t *out) {
   const unsigned ginv = rot < 0 ? 2 * ctx->ht.N - 1 : pow5_inv_mod_2n(ctx, (unsigned)rot);
   const size_t total = npoly * ctx->ht.N;
-  if (total) launch(ctx, hbdev::k_poly_automorph, (unsigned)((total + 255) / 256), 256, 0, 1, polys, out, (int)W, ginv, ctx->ht.N, npoly);
+  if (total) launch(ctx, "k_poly_automorph", hbdev::k_poly_automorph, (unsigned)((total + 255) / 256), 256, 0, 1, polys, out, (int)W, ginv, ctx->ht.N, npoly);
 }

@@ -75,6 +75,11 @@ void hb_timer_start(hb_ctx *ctx);
 float hb_timer_stop_ms(hb_ctx *ctx);
 /* kernels launched by this context since creation (bench.py "gpu_launches") */
 uint64_t hb_launch_count(const hb_ctx *ctx);
+/* per-kernel CUDA-event timing on the context's stream: enable, run, then read {"kernel": {"launches","ms"}} as JSON
+ * (returns the length the full report needs) */
+void hb_prof_enable(hb_ctx *ctx, int on);
+void hb_prof_reset(hb_ctx *ctx);
+size_t hb_prof_report(hb_ctx *ctx, char *buf, size_t cap);
 
 /* ---- host-only view of the same tables (no GPU needed: CPU tests of the host logic) -------------------- */
 typedef struct hb_tables hb_tables;
@@ -104,6 +109,9 @@ void hb_ct_free(hb_ctx *ctx, hb_ct *ct);                       /* he_free_ct  */
 void hb_ct_copy(hb_ctx *ctx, hb_ct *dst, const hb_ct *src);    /* he_copy_ct  */
 void hb_ct_upload(hb_ctx *ctx, hb_ct *ct, const uint64_t *host_words, unsigned l, double nu, double B);
 void hb_ct_download(hb_ctx *ctx, const hb_ct *ct, uint64_t *host_words);   /* synchronises */
+/* device-to-device exchange with buffers the caller owns (e.g. a torch tensor used for the NCCL result gather) */
+void hb_ct_export(hb_ctx *ctx, const hb_ct *ct, void *dst_device);
+void hb_ct_import(hb_ctx *ctx, hb_ct *ct, const void *src_device, unsigned l, double nu, double B);
 void hb_pt_alloc(hb_ctx *ctx, hb_pt *pt);                      /* he_alloc_pt */
 void hb_pt_free(hb_ctx *ctx, hb_pt *pt);
 void hb_pt_upload(hb_ctx *ctx, hb_pt *pt, const uint64_t *host_words, double nu);
