@@ -6,7 +6,7 @@ import os
 import re
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libhectr_b200.so")
+LIB_PATH = os.environ.get("HB_LIB") or os.path.join(HERE, "libhectr_b200.so")   # HB_LIB: development variants
 HEADER_PATH = os.path.join(HERE, os.pardir, "include", "hectr_b200.h")
 
 u64p = C.POINTER(C.c_uint64)

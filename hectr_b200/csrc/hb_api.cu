@@ -43,7 +43,8 @@ using hbdev::Tables;
 struct GemvPlan {
   std::vector<double> A;     // the matrix the plan was built from
   unsigned l = 0, D = 0;
-  uint64_t *pthat = nullptr; // device [slots][D][N]: ntt of the encoded, pre-rotated diagonals
+  bool fused = false;        // the n1 products of one giant step may be summed before the CRT (bound check below)
+  ulonglong2 *pthat = nullptr; // device [slots][D][N] Shoup pairs: ntt of the encoded, pre-rotated diagonals
 };
 
 struct hb_ctx {
@@ -60,8 +61,9 @@ struct hb_ctx {
   std::map<std::string, ProfRec> prof_recs;
   std::vector<cudaEvent_t> prof_free;
   // workspaces (grow only)
-  uint64_t *wsA = nullptr, *wsB = nullptr;
-  size_t wsA_bytes = 0, wsB_bytes = 0;
+  uint64_t *wsA = nullptr, *wsB = nullptr, *wsC = nullptr;
+  size_t wsA_bytes = 0, wsB_bytes = 0, wsC_bytes = 0;
+  bool stepwise = false;            // HB_GEMV_STEPWISE=1: evaluate he_gemv one reference call at a time (tests, A/B timing)
   // pool of ciphertext buffers keyed by capacity in bytes
   std::multimap<size_t, uint64_t *> pool;
   std::map<uint64_t *, size_t> live;
@@ -124,7 +126,11 @@ static void want_smem(K kernel, size_t bytes) {
   done[key] = bytes;
 }
 
+#ifdef HB_DEV_FAST   /* development builds: fewer template instantiations */
+#define HB_LOGN_CASES(X) X(12) X(16)
+#else
 #define HB_LOGN_CASES(X) X(7) X(10) X(11) X(12) X(13) X(14) X(15) X(16)
+#endif
 
 template <int LOGN>
 struct Launch {
@@ -146,16 +152,22 @@ struct Launch {
     want_smem(hbdev::k_poly_ntt<LOGN>, G::SMEM_BYTES);
     launch(c, "k_poly_ntt", hbdev::k_poly_ntt<LOGN>, (unsigned)(npoly * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, src, stride, W, out, c->dt, D);
   }
-  static void ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, unsigned ginv, const uint64_t *evk,
+  static void ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, unsigned g, unsigned ginv, const ulonglong2 *evk,
                       uint64_t *chat, unsigned D, unsigned batch) {
     want_smem(hbdev::k_ks_limb<LOGN>, 2 * G::SMEM_BYTES);
     launch(c, "k_ks_limb", hbdev::k_ks_limb<LOGN>, (unsigned)((size_t)batch * D * G::C), G::THREADS, 2 * G::SMEM_BYTES, G::C, src, bstride, W,
-           ginv, evk, c->ht.dimevk, chat, c->dt, D);
+           g, ginv, evk, c->ht.dimevk, chat, c->dt, D);
   }
-  static void mulpt_limb(hb_ctx *c, const uint64_t *ct, int W, const uint64_t *pthat, uint64_t *chat, unsigned D, unsigned batch) {
+  static void mulpt_limb(hb_ctx *c, const uint64_t *ct, int W, const ulonglong2 *pthat, uint64_t *chat, unsigned D, unsigned batch) {
     want_smem(hbdev::k_mulpt_limb<LOGN>, G::SMEM_BYTES);
     launch(c, "k_mulpt_limb", hbdev::k_mulpt_limb<LOGN>, (unsigned)((size_t)batch * 2 * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, ct, W, pthat,
            chat, c->dt, D);
+  }
+  static void mulacc_intt(hb_ctx *c, const uint64_t *hat, size_t jstride, const ulonglong2 *pthat, unsigned n1, uint64_t *chat,
+                          unsigned D, unsigned batch) {
+    want_smem(hbdev::k_mulacc_intt<LOGN>, G::SMEM_BYTES);
+    launch(c, "k_mulacc_intt", hbdev::k_mulacc_intt<LOGN>, (unsigned)((size_t)batch * 2 * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, hat, jstride,
+           pthat, n1, chat, c->dt, D);
   }
   static void tensor_intt(hb_ctx *c, const uint64_t *hatA, const uint64_t *hatB, uint64_t *dhat, unsigned D, unsigned batch) {
     want_smem(hbdev::k_tensor_intt<LOGN>, G::SMEM_BYTES);
@@ -178,14 +190,20 @@ static void do_poly_ntt(hb_ctx *c, const uint64_t *src, size_t stride, int W, ui
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
 }
-static void do_ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, unsigned ginv, const uint64_t *evk,
+static void do_ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, unsigned g, unsigned ginv, const ulonglong2 *evk,
                        uint64_t *chat, unsigned D, unsigned batch) {
-#define X(L) case L: Launch<L>::ks_limb(c, src, bstride, W, ginv, evk, chat, D, batch); break;
+#define X(L) case L: Launch<L>::ks_limb(c, src, bstride, W, g, ginv, evk, chat, D, batch); break;
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
 }
-static void do_mulpt_limb(hb_ctx *c, const uint64_t *ct, int W, const uint64_t *pthat, uint64_t *chat, unsigned D, unsigned batch) {
+static void do_mulpt_limb(hb_ctx *c, const uint64_t *ct, int W, const ulonglong2 *pthat, uint64_t *chat, unsigned D, unsigned batch) {
 #define X(L) case L: Launch<L>::mulpt_limb(c, ct, W, pthat, chat, D, batch); break;
+  switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
+#undef X
+}
+static void do_mulacc_intt(hb_ctx *c, const uint64_t *hat, size_t jstride, const ulonglong2 *pthat, unsigned n1, uint64_t *chat,
+                           unsigned D, unsigned batch) {
+#define X(L) case L: Launch<L>::mulacc_intt(c, hat, jstride, pthat, n1, chat, D, batch); break;
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
 }
@@ -193,6 +211,12 @@ static void do_tensor_intt(hb_ctx *c, const uint64_t *hatA, const uint64_t *hatB
 #define X(L) case L: Launch<L>::tensor_intt(c, hatA, hatB, dhat, D, batch); break;
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
+}
+
+// canonical limbs[j][N] (prime j % D) -> Shoup pairs
+static void do_shoup_prep(hb_ctx *c, const uint64_t *in, ulonglong2 *out, unsigned D, size_t nlimbs) {
+  const size_t total = nlimbs * c->ht.N;
+  launch(c, "k_shoup_prep", hbdev::k_shoup_prep, (unsigned)((total + 255) / 256), 256, 0, 1, in, out, c->dt, D, nlimbs);
 }
 
 static int wk_class(unsigned wk) { return wk <= 1 ? 1 : wk <= 2 ? 2 : wk <= 4 ? 4 : wk <= 8 ? 8 : 16; }
@@ -293,6 +317,10 @@ extern "C" hb_ctx *hb_ctx_create(unsigned logn, unsigned logq, unsigned slots, u
   t.ks_Ph = upload_vec(ctx, h.ks_Ph);
   t.ks_Pinv = upload_vec(ctx, h.ks_Pinv);
   t.N = h.N; t.logn = h.logn; t.dimub = h.dimub; t.WC = h.WC; t.WP = h.WP; t.dim = h.dim;
+  {
+    const char *e = getenv("HB_GEMV_STEPWISE");
+    ctx->stepwise = e && *e && *e != '0';
+  }
   ctx->ring = hb_ring_create(logn);
   ctx->enc_host.assign((size_t)h.WC * h.N, 0);
   return ctx;
@@ -311,6 +339,7 @@ extern "C" void hb_ctx_destroy(hb_ctx *ctx) {
   for (cudaEvent_t e : ctx->prof_free) cudaEventDestroy(e);
   cudaFree(ctx->wsA);
   cudaFree(ctx->wsB);
+  cudaFree(ctx->wsC);
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->own_stream);
@@ -549,11 +578,15 @@ extern "C" void hb_pt_upload(hb_ctx *ctx, hb_pt *pt, const uint64_t *host, doubl
   CUDA_OK(cudaStreamSynchronize(ctx->stream));
 }
 extern "C" void hb_evk_upload(hb_ctx *ctx, hb_evk *evk, const uint64_t *p0, const uint64_t *p1) {
+  // stored as Shoup pairs (w, floor(w 2^64 / p_d)): the key is a fixed multiplicand of every key switch
   const size_t half = (size_t)ctx->ht.dimevk * ctx->ht.N;
-  evk->p = (uint64_t *)hb_dev_alloc(ctx, 2 * half * 8);
-  CUDA_OK(cudaMemcpyAsync(evk->p, p0, half * 8, cudaMemcpyHostToDevice, ctx->stream));
-  CUDA_OK(cudaMemcpyAsync(evk->p + half, p1, half * 8, cudaMemcpyHostToDevice, ctx->stream));
-  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  if (ctx->ht.dimevk > ctx->ht.dimub) hb_die("hb_evk_upload: keys of %u limbs but the prime chain has %u", ctx->ht.dimevk, ctx->ht.dimub);
+  uint64_t *raw = (uint64_t *)hb_dev_alloc(ctx, 2 * half * 8);
+  evk->p = (uint64_t *)hb_dev_alloc(ctx, 2 * half * 16);
+  CUDA_OK(cudaMemcpyAsync(raw, p0, half * 8, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_OK(cudaMemcpyAsync(raw + half, p1, half * 8, cudaMemcpyHostToDevice, ctx->stream));
+  do_shoup_prep(ctx, raw, (ulonglong2 *)evk->p, ctx->ht.dimevk, (size_t)2 * ctx->ht.dimevk);
+  hb_dev_free(ctx, raw);   // synchronises
 }
 extern "C" void hb_evk_free(hb_ctx *ctx, hb_evk *evk) { hb_dev_free(ctx, evk->p); evk->p = nullptr; }
 
@@ -628,7 +661,7 @@ extern "C" void hb_he_rs(hb_ctx *ctx, hb_ct *ct) {
 extern "C" void hb_he_moddown(hb_ctx *ctx, hb_ct *ct) { rescale_like(ctx, ct, 0, "hb_he_moddown"); }
 
 // pthat[D][N] -> chat -> dst   (shared by hb_he_mulpt and the gemv plan)
-static void mulpt_with_hat(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const uint64_t *pthat, unsigned D, double ptnu) {
+static void mulpt_with_hat(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const ulonglong2 *pthat, unsigned D, double ptnu) {
   const int W = hb::words_of_level(ctx->ht, src->l), k = ctx->ht.logq_l[src->l];
   uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, (size_t)src->batch * 2 * D * ctx->ht.N * 8);
   do_mulpt_limb(ctx, src->words, W, pthat, chat, D, src->batch);
@@ -644,9 +677,19 @@ extern "C" void hb_he_mulpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_
   if (!pt || !pt->words) hb_die("hb_he_mulpt: plaintext handle is not allocated");
   const unsigned D = hb::dim_mulpt(ctx->ht, src->l, pt->nu);
   if (D == 0 || D > ctx->ht.dimub) hb_die("hb_he_mulpt: limb count %u outside the prime chain (%u)", D, ctx->ht.dimub);
-  uint64_t *pthat = ws_get(ctx, ctx->wsB, ctx->wsB_bytes, (size_t)D * ctx->ht.N * 8);
-  do_poly_ntt(ctx, pt->words, (size_t)ctx->ht.WC * ctx->ht.N, ctx->ht.WC, pthat, D, 1);
+  const size_t hatw = (size_t)D * ctx->ht.N;
+  uint64_t *raw = ws_get(ctx, ctx->wsB, ctx->wsB_bytes, hatw * 24);
+  ulonglong2 *pthat = (ulonglong2 *)(raw + hatw);
+  do_poly_ntt(ctx, pt->words, (size_t)ctx->ht.WC * ctx->ht.N, ctx->ht.WC, raw, D, 1);
+  do_shoup_prep(ctx, raw, pthat, D, D);
   mulpt_with_hat(ctx, dst, src, pthat, D, pt->nu);
+}
+
+// inverse of an odd number modulo 2N (Newton iteration)
+static unsigned inv_odd_mod_2n(const hb_ctx *ctx, unsigned g) {
+  unsigned x = g;
+  for (int i = 0; i < 5; i++) x *= 2 - g * x;
+  return x & (2 * ctx->ht.N - 1);
 }
 
 static unsigned pow5_inv_mod_2n(const hb_ctx *ctx, unsigned rot) {
@@ -669,7 +712,7 @@ static void keyswitch_inplace(hb_ctx *ctx, hb_ct *ct, unsigned ginv, const hb_ev
   const int W = hb::words_of_level(h, ct->l), k = h.logq_l[ct->l];
   const size_t bstride = (size_t)2 * W * h.N;
   uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, (size_t)ct->batch * 2 * D * h.N * 8);
-  do_ks_limb(ctx, ct->words + (size_t)W * h.N, bstride, W, ginv, key->p, chat, D, ct->batch);
+  do_ks_limb(ctx, ct->words + (size_t)W * h.N, bstride, W, inv_odd_mod_2n(ctx, ginv), ginv, (const ulonglong2 *)key->p, chat, D, ct->batch);
   uint64_t *out = pool_get(ctx, ct_capacity(ctx, ct->batch));
   do_ks_finish(ctx, chat, D, ct->words, nullptr, bstride, W, ginv, out, W, k, ct->batch);
   pool_put(ctx, ct->words);
@@ -708,7 +751,7 @@ extern "C" void hb_he_mul(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b
   do_recon_smod(ctx, dhat, Dm, dpoly, W, k, (size_t)batch * 3);      // d0,d1,d2 mod q_l  (he-mult.c:140-142)
   // relinearise d2 with rlk, add d0 and d1 (he-mult.c:40-85)
   uint64_t *chat = wsA;
-  do_ks_limb(ctx, dpoly + 2 * polyw, 3 * polyw, W, 1u, rlk->p, chat, Dk, batch);
+  do_ks_limb(ctx, dpoly + 2 * polyw, 3 * polyw, W, 1u, 1u, (const ulonglong2 *)rlk->p, chat, Dk, batch);
   const double nu1 = a->nu, nu2 = b->nu, B1 = a->B, B2 = b->B;
   ct->l = l;
   ct->nu = nu1 * nu2;
@@ -769,24 +812,45 @@ static const GemvPlan &gemv_plan(hb_ctx *ctx, const double *A, unsigned l) {
       hb_ring_encode(ctx->ring, S, rd.data(), Delta, host.data() + (size_t)idx * ptw, h.WC);
     }
   }
+  {
+    // May the n1 products of a giant step be summed before reconstruction?  Every |ct coefficient| <= q_l/2, so a
+    // coefficient of sum_j rot_j * pt_ij is bounded by 2^(k-1) * sum_j ||pt_ij||_1; it must stay below P_D/2 (> 2^(nbits-2)).
+    long double worst = 0;
+    for (unsigned i = 0; i < n2; i++) {
+      long double s1 = 0;
+      for (unsigned j = 0; j < n1; j++) {
+        const uint64_t *w = host.data() + (size_t)(i * n1 + j) * ptw;
+        for (unsigned c = 0; c < h.N; c++) {
+          long double v = 0;
+          const bool neg = (int64_t)w[(size_t)(h.WC - 1) * h.N + c] < 0;
+          for (int ww = (int)h.WC - 1; ww >= 0; ww--) {
+            uint64_t x = w[(size_t)ww * h.N + c];
+            v = v * 18446744073709551616.0L + (long double)(neg ? ~x : x);
+          }
+          s1 += neg ? v + 1 : v;
+        }
+      }
+      if (s1 > worst) worst = s1;
+    }
+    const long double lhs = (worst > 0 ? std::log2(worst) : 0) + (long double)(h.logq_l[l] - 1) + 0.01L;
+    plan.fused = lhs < (long double)h.Pfull[plan.D].bits() - 2;
+  }
   uint64_t *dpt = (uint64_t *)hb_dev_alloc(ctx, host.size() * 8);
   CUDA_OK(cudaMemcpyAsync(dpt, host.data(), host.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
-  plan.pthat = (uint64_t *)hb_dev_alloc(ctx, (size_t)S * plan.D * h.N * 8);
-  do_poly_ntt(ctx, dpt, ptw, h.WC, plan.pthat, plan.D, S);
+  uint64_t *raw = (uint64_t *)hb_dev_alloc(ctx, (size_t)S * plan.D * h.N * 8);
+  plan.pthat = (ulonglong2 *)hb_dev_alloc(ctx, (size_t)S * plan.D * h.N * 16);
+  do_poly_ntt(ctx, dpt, ptw, h.WC, raw, plan.D, S);
+  do_shoup_prep(ctx, raw, plan.pthat, plan.D, (size_t)S * plan.D);
   CUDA_OK(cudaStreamSynchronize(ctx->stream));
   CUDA_OK(cudaFree(dpt));
+  CUDA_OK(cudaFree(raw));
   ctx->plans.push_back(std::move(plan));
   return ctx->plans.back();
 }
 
-extern "C" void hb_he_gemv(hb_ctx *ctx, hb_ct *dst, const double *A, const hb_ct *ct, const hb_evk *rk) {
-  same_shape(dst, ct, "hb_he_gemv");
+// The reference schedule, one he_* call after the other (he-algo.c:57-87).
+static void gemv_stepwise(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_ct *ct, const hb_evk *rk, unsigned n1, unsigned n2) {
   const hb::HostTables &h = ctx->ht;
-  const unsigned S = h.slots;
-  const GemvPlan &plan = gemv_plan(ctx, A, ct->l);
-  unsigned n1 = (unsigned)std::sqrt((double)S);
-  if (S != n1 * n1) n1 = (unsigned)std::sqrt((double)(2 * S));
-  const unsigned n2 = S / n1;
   const double Delta = std::ldexp(1.0, (int)h.logDelta);
   hb_ct inner, outer, rot;
   hb_ct_alloc(ctx, &inner, ct->batch);
@@ -810,6 +874,61 @@ extern "C" void hb_he_gemv(hb_ctx *ctx, hb_ct *dst, const double *A, const hb_ct
   hb_ct_free(ctx, &inner);
   hb_ct_free(ctx, &outer);
   hb_ct_free(ctx, &rot);
+}
+
+// Same ciphertext, fewer transforms.  The reference recomputes he_rot(ct, j) for every giant step i although it does not
+// depend on i (he-algo.c:66-68): here the n1 baby rotations are key-switched once, transformed once
+// (hat_j = ntt(decompose(rot_j))), and each giant step sums its n1 diagonal products in the NTT domain before one
+// inverse transform and one reconstruction (k_mulacc_intt).  Every he_swk rounding of the reference is still performed
+// on the same integers, so the result is bit-identical (SURVEY H4 forbids sharing key-switch decompositions, not this).
+static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_ct *ct, const hb_evk *rk, unsigned n1, unsigned n2) {
+  const hb::HostTables &h = ctx->ht;
+  const double Delta = std::ldexp(1.0, (int)h.logDelta);
+  const unsigned batch = ct->batch, D = plan.D, l = ct->l;
+  const int W = hb::words_of_level(h, l), k = h.logq_l[l];
+  const size_t N = h.N, polyw = (size_t)W * N;
+  const size_t jstride = (size_t)batch * 2 * D * N;
+  uint64_t *hat = ws_get(ctx, ctx->wsC, ctx->wsC_bytes, (size_t)n1 * jstride * 8);
+  hb_ct inner, outer, rot;
+  hb_ct_alloc(ctx, &inner, batch);
+  hb_ct_alloc(ctx, &outer, batch);
+  hb_ct_alloc(ctx, &rot, batch);
+  for (unsigned j = 0; j < n1; j++) {
+    hb_ct_copy(ctx, &rot, ct);
+    hb_he_rot(ctx, &rot, (int)j, rk);
+    do_poly_ntt(ctx, rot.words, polyw, W, hat + (size_t)j * jstride, D, (size_t)batch * 2);
+  }
+  for (unsigned i = 0; i < n2; i++) {
+    const unsigned shift = i * n1;
+    uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, jstride * 8);
+    do_mulacc_intt(ctx, hat, jstride, plan.pthat + (size_t)shift * D * N, n1, chat, D, batch);
+    do_recon_smod(ctx, chat, D, inner.words, W, k, (size_t)batch * 2);
+    inner.l = l;
+    for (unsigned j = 0; j < n1; j++) {          // metadata exactly as he_mulpt / he_add update it
+      const double nu = ct->nu * Delta, B = ct->B * Delta;
+      if (!j) { inner.nu = nu; inner.B = B; }
+      else { inner.nu = inner.nu >= nu ? inner.nu : nu; inner.B = inner.B + B; }
+    }
+    hb_he_rot(ctx, &inner, (int)shift, rk);
+    if (!i) hb_ct_copy(ctx, &outer, &inner);
+    else hb_he_add(ctx, &outer, &outer, &inner);
+  }
+  hb_ct_copy(ctx, dst, &outer);
+  hb_he_rs(ctx, dst);
+  hb_ct_free(ctx, &inner);
+  hb_ct_free(ctx, &outer);
+  hb_ct_free(ctx, &rot);
+}
+
+extern "C" void hb_he_gemv(hb_ctx *ctx, hb_ct *dst, const double *A, const hb_ct *ct, const hb_evk *rk) {
+  same_shape(dst, ct, "hb_he_gemv");
+  const unsigned S = ctx->ht.slots;
+  const GemvPlan &plan = gemv_plan(ctx, A, ct->l);
+  unsigned n1 = (unsigned)std::sqrt((double)S);
+  if (S != n1 * n1) n1 = (unsigned)std::sqrt((double)(2 * S));
+  const unsigned n2 = S / n1;
+  if (plan.fused && !ctx->stepwise) gemv_fused(ctx, dst, plan, ct, rk, n1, n2);
+  else gemv_stepwise(ctx, dst, plan, ct, rk, n1, n2);
 }
 
 extern "C" void hb_ctr_hempc_eval(hb_ctx *ctx, hb_ct *up, const double *Ka, const double *Kb, const hb_ct *xhat,

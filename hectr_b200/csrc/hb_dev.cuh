@@ -6,6 +6,13 @@
 //   modmul   : GPQHE/src/reduce.c:59-66 (Montgomery) / :88-106 (Barrett) -- here Shoup (fixed operand)
 //              and a 2^120 Barrett (variable operands); a*b mod p is the same integer in [0,p).
 //
+// Arithmetic design (the path is bound by the integer pipes, not by HBM -- profiles/r01/):
+//   * every prime is p = 2^59 + c with c < 2^28, so 2^64 = 31.99.. p: a 64-bit word holds lazily reduced
+//     residues up to 31 p.  Forward butterflies never reduce (each stage adds 2p to the bound); inverse
+//     butterflies double the bound of the sum leg and reduce only where the compile-time bound requires it.
+//   * a * w - q * p is one chain of six IMADs accumulating onto the other butterfly leg (no carry fix-ups);
+//     q = umulhi(a, w') with the precomputed Shoup quotient w' = floor(w 2^64 / p).
+//
 // Geometry.  One limb (N coefficients mod one prime) is processed by a cluster of C CTAs, each owning a
 // contiguous chunk of M = N/C coefficients in (padded) shared memory; C = 1 up to N = 2^13, then 2/4/8 for
 // 2^14/2^15/2^16 so that a 512 KiB limb still makes exactly one HBM round trip.  The first four forward
@@ -18,6 +25,17 @@
 #include <cooperative_groups.h>
 
 namespace cg = cooperative_groups;
+
+// streaming accesses (evict-first) for data touched once, so the twiddle tables stay in L1
+#ifdef HB_STREAM
+#define HB_LD(p) __ldcs(p)
+#define HB_LDS2(p) __ldcs(p)
+#define HB_ST(p, v) __stcs(p, v)
+#else
+#define HB_LD(p) (*(p))
+#define HB_LDS2(p) __ldg(p)
+#define HB_ST(p, v) (*(p) = (v))
+#endif
 
 namespace hbdev {
 
@@ -40,20 +58,80 @@ struct Tables {  // device pointers, passed by value
 };
 
 // ---------------------------------------------------------------------------------------------------------
-// scalar modular arithmetic
+// 32-bit building blocks
 // ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t lo32(uint64_t x) { return (uint32_t)x; }
+__device__ __forceinline__ uint32_t hi32(uint64_t x) { return (uint32_t)(x >> 32); }
+__device__ __forceinline__ uint64_t pack64(uint32_t lo, uint32_t hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+__device__ __forceinline__ uint32_t madlo(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t madwide(uint32_t a, uint32_t b, uint64_t c) {
+  uint64_t r;
+  asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(a), "r"(b), "l"(c));
+  return r;
+}
+
+// The modulus as the kernels carry it: p, -p mod 2^64, and c = p - 2^59.
+struct Mod {
+  uint64_t p, pn;
+  uint32_t c;
+};
+__device__ __forceinline__ Mod make_mod(uint64_t p) {
+  Mod m;
+  m.p = p;
+  m.pn = 0 - p;
+  m.c = (uint32_t)(p - (1ULL << 59));
+  return m;
+}
+
+// acc + a*w - q*p  (mod 2^64): six IMADs, the low product pair accumulates in 64 bits.
+__device__ __forceinline__ uint64_t mac_msub(uint64_t acc, uint64_t a, uint64_t w, uint64_t q, uint64_t pn) {
+  uint32_t h = hi32(acc);
+  h = madlo(hi32(q), lo32(pn), h);
+  h = madlo(lo32(q), hi32(pn), h);
+  h = madlo(hi32(a), lo32(w), h);
+  h = madlo(lo32(a), hi32(w), h);
+  uint64_t r = pack64(lo32(acc), h);
+  r = madwide(lo32(q), lo32(pn), r);
+  r = madwide(lo32(a), lo32(w), r);
+  return r;
+}
+
 __device__ __forceinline__ uint64_t csub(uint64_t x, uint64_t m) { return x >= m ? x - m : x; }
 
 // a*w mod p in [0, 2p) for ANY 64-bit a, given wq = floor(w 2^64 / p), w < p.
-__device__ __forceinline__ uint64_t shoup_lazy(uint64_t a, uint64_t w, uint64_t wq, uint64_t p) {
-  uint64_t q = __umul64hi(a, wq);
-  return a * w - q * p;
+__device__ __forceinline__ uint64_t shoup_lazy(uint64_t a, uint64_t w, uint64_t wq, const Mod &m) {
+  return mac_msub(0, a, w, __umul64hi(a, wq), m.pn);
 }
+__device__ __forceinline__ uint64_t shoup(uint64_t a, uint64_t w, uint64_t wq, const Mod &m) {
+  return csub(shoup_lazy(a, w, wq, m), m.p);
+}
+// same, from the bare modulus (cold paths)
 __device__ __forceinline__ uint64_t shoup(uint64_t a, uint64_t w, uint64_t wq, uint64_t p) {
-  return csub(shoup_lazy(a, w, wq, p), p);
+  uint64_t q = __umul64hi(a, wq);
+  return csub(a * w - q * p, p);
 }
 
-// any 64-bit word -> [0,p)
+// Any 64-bit x -> the same residue in (0, 2p):  x = h 2^59 + r  ==  r - h c  (mod p); returned as
+// r + (31 - h) c + (p - 31 c).
+__device__ __forceinline__ uint64_t fold(uint64_t x, const Mod &m) {
+  const uint32_t xh = hi32(x);
+  const uint32_t e = (xh >> 27) ^ 31u;                       // 31 - h
+  uint64_t r = pack64(lo32(x), xh & 0x07ffffffu);
+  r = madwide(e, m.c, r);
+  return r + (m.p - 31ull * m.c);
+}
+// any 64-bit x -> [0,p)
+__device__ __forceinline__ uint64_t canon(uint64_t x, const Mod &m) { return csub(fold(x, m), m.p); }
+
+// any 64-bit word -> [0,p)  (cold paths)
 __device__ __forceinline__ uint64_t reduce_word(uint64_t a, const PrimeConsts &c) {
   uint64_t q = __umul64hi(a, c.one_q);
   return csub(a - q * c.p, c.p);
@@ -71,32 +149,33 @@ __device__ __forceinline__ uint64_t mulmod_barrett(uint64_t a, uint64_t b, uint6
 
 __device__ __forceinline__ uint64_t addmod(uint64_t a, uint64_t b, uint64_t p) { return csub(a + b, p); }
 
-// Forward butterflies.  LAZY (default): Harvey, values in [0,4p).  STRICT: the reference's exact
-// data flow, values in [0,p] including its "sum == p stays p" quirk (ntt.c:47-48).
+// Forward butterfly (ntt.c:44-48).  LAZY (default): X' = X + wY, Y' = X - wY + 2p with wY in [0,2p): the bound
+// of both legs grows by 2p and nothing is reduced.  STRICT: the reference's exact data flow, values in
+// [0,p] including its "sum == p stays p" quirk.
 template <bool STRICT>
-__device__ __forceinline__ void ct_bfly(uint64_t &X, uint64_t &Y, ulonglong2 w, uint64_t p) {
+__device__ __forceinline__ void ct_bfly(uint64_t &X, uint64_t &Y, ulonglong2 w, const Mod &m) {
   if (STRICT) {
-    uint64_t t = shoup(Y, w.x, w.y, p);
+    uint64_t t = shoup(Y, w.x, w.y, m);
     uint64_t x = X;
-    Y = (x >= t) ? x - t : x - t + p;
-    X = (x <= p - t) ? x + t : x + t - p;
+    Y = (x >= t) ? x - t : x - t + m.p;
+    X = (x <= m.p - t) ? x + t : x + t - m.p;
   } else {
-    uint64_t x = csub(X, 2 * p);
-    uint64_t t = shoup_lazy(Y, w.x, w.y, p);
-    X = x + t;
-    Y = x + 2 * p - t;
+    const uint64_t x = X;
+    const uint64_t xn = mac_msub(x, Y, w.x, __umul64hi(Y, w.y), m.pn);   // x + t
+    Y = x + x + 2 * m.p - xn;                                             // x - t + 2p
+    X = xn;
   }
 }
 
-// Inverse butterfly (ntt.c:62-67): inputs in [0,2p), outputs in [0,2p).
-__device__ __forceinline__ void gs_bfly(uint64_t &X, uint64_t &Y, ulonglong2 w, uint64_t p) {
-  uint64_t s = csub(X + Y, 2 * p);
-  uint64_t d = X + 2 * p - Y;
+// Inverse butterfly (ntt.c:62-67): X' = X + Y, Y' = (X - Y) w.  BY = bound of Y in units of p.
+template <int BY>
+__device__ __forceinline__ void gs_bfly(uint64_t &X, uint64_t &Y, ulonglong2 w, const Mod &m) {
+  const uint64_t s = X + Y;
+  uint32_t h = madlo((uint32_t)BY, hi32(m.p), hi32(X));
+  const uint64_t d = madwide((uint32_t)BY, lo32(m.p), pack64(lo32(X), h)) - Y;   // X + BY p - Y
   X = s;
-  Y = shoup_lazy(d, w.x, w.y, p);
+  Y = shoup_lazy(d, w.x, w.y, m);
 }
-
-__device__ __forceinline__ uint64_t canon4(uint64_t x, uint64_t p) { return csub(csub(x, 2 * p), p); }
 
 // ---------------------------------------------------------------------------------------------------------
 // geometry
@@ -108,36 +187,80 @@ struct Cfg {
   static constexpr int C = 1 << LOGC;          // CTAs per limb (cluster size)
   static constexpr int LOGM = LOGN - LOGC;
   static constexpr int M = 1 << LOGM;          // coefficients per CTA
-  static constexpr int THREADS = M / 16;       // one radix-16 tile per thread in the global pass
+  static constexpr int TILES16 = (M >= 16) ? M / 16 : 1;
+  static constexpr int THREADS = TILES16 > 256 ? 256 : TILES16;   // radix-16 tiles are looped over when M > 4096
   static constexpr int SMEM_WORDS = M + (M >> 4) * 2;   // 2 pad words per 16 (keeps 16-byte alignment)
   static constexpr int SMEM_BYTES = SMEM_WORDS * 8;
+  #ifndef HB_MINB12
+#define HB_MINB12 3
+#endif
+  static constexpr int MINBLOCKS = (LOGN <= 12) ? HB_MINB12 : (LOGN == 13 ? 3 : 2);
 };
 
 __device__ __forceinline__ int pidx(int i) { return i + ((i >> 4) << 1); }
 
-// Twiddle index of the butterfly at tile-bit `beta` for tile element t, tile of 2^R elements whose coarsest
-// block index is K0 (= 2^S + block):  k = (K0 << (R-1-beta)) + (t >> (beta+1)).
-template <int R, bool INV, bool STRICT>
-__device__ __forceinline__ void tile_compute(uint64_t (&x)[1 << R], const ulonglong2 *__restrict__ tw, unsigned K0,
-                                             uint64_t p) {
+// Forward tile: 2^R elements, stages beta = R-1 .. 0.  Twiddle index of the butterfly at tile-bit `beta` for tile
+// element t, tile whose coarsest block index is K0 (= 2^S + block):  k = (K0 << (R-1-beta)) + (t >> (beta+1)).
+template <int R, bool STRICT>
+__device__ __forceinline__ void tile_fwd(uint64_t (&x)[1 << R], const ulonglong2 *__restrict__ tw, unsigned K0,
+                                         const Mod &m) {
 #pragma unroll
   for (int a = 0; a < R; a++) {
-    const int beta = INV ? a : (R - 1 - a);
+    const int beta = R - 1 - a;
     const int half = 1 << beta;
 #pragma unroll
     for (int t = 0; t < (1 << R); t++) {
       if ((t & half) == 0) {
         ulonglong2 w = __ldg(&tw[(K0 << (R - 1 - beta)) + (t >> (beta + 1))]);
-        if (INV) gs_bfly(x[t], x[t + half], w, p);
-        else ct_bfly<STRICT>(x[t], x[t + half], w, p);
+        ct_bfly<STRICT>(x[t], x[t + half], w, m);
       }
     }
   }
 }
 
+// Inverse tile: stages beta = 0 .. R-1.  Every element enters below 2p.  The sum leg doubles its bound each
+// stage, the product leg returns to 2p; bounds are tracked at compile time (the loops are fully unrolled) and a
+// leg is folded back below 2p only when the next sum could pass 31p.  With FOLD_OUT every element leaves below
+// 2p again (needed between passes); the last pass multiplies by N^-1 instead, which accepts any input.
+template <int R, bool FOLD_OUT>
+__device__ __forceinline__ void tile_inv(uint64_t (&x)[1 << R], const ulonglong2 *__restrict__ tw, unsigned K0,
+                                         const Mod &m) {
+  int bnd[1 << R];
+#pragma unroll
+  for (int t = 0; t < (1 << R); t++) bnd[t] = 2;
+#pragma unroll
+  for (int a = 0; a < R; a++) {
+    const int beta = a;
+    const int half = 1 << beta;
+#pragma unroll
+    for (int t = 0; t < (1 << R); t++) {
+      if ((t & half) == 0) {
+        if (bnd[t] + bnd[t + half] > 31) {
+          if (bnd[t] > 2) { x[t] = fold(x[t], m); bnd[t] = 2; }
+          if (bnd[t + half] > 2) { x[t + half] = fold(x[t + half], m); bnd[t + half] = 2; }
+        }
+        ulonglong2 w = __ldg(&tw[(K0 << (R - 1 - beta)) + (t >> (beta + 1))]);
+        const int by = bnd[t + half];
+        if (by == 2) gs_bfly<2>(x[t], x[t + half], w, m);
+        else if (by == 4) gs_bfly<4>(x[t], x[t + half], w, m);
+        else if (by == 8) gs_bfly<8>(x[t], x[t + half], w, m);
+        else gs_bfly<16>(x[t], x[t + half], w, m);
+        bnd[t] += by;
+        bnd[t + half] = 2;
+      }
+    }
+  }
+  if (FOLD_OUT) {
+#pragma unroll
+    for (int t = 0; t < (1 << R); t++)
+      if (bnd[t] > 2) x[t] = fold(x[t], m);
+  }
+}
+
 // One chunk-local pass: stages [S, S+R) in forward numbering (len = N>>(S+1) ...), on this CTA's chunk.
-template <int LOGN, int S, int R, bool INV, bool STRICT>
-__device__ __forceinline__ void local_pass(uint64_t *sm, const ulonglong2 *__restrict__ tw, uint64_t p,
+// FOLD_IN (forward only): fold every element below 2p on entry (bound bookkeeping of ntt_forward).
+template <int LOGN, int S, int R, bool INV, bool STRICT, bool FOLD_IN>
+__device__ __forceinline__ void local_pass(uint64_t *sm, const ulonglong2 *__restrict__ tw, const Mod &m,
                                            unsigned chunk) {
   typedef Cfg<LOGN> G;
   constexpr int LOGST = LOGN - S - R;           // log2 of the element stride inside a tile
@@ -159,7 +282,12 @@ __device__ __forceinline__ void local_pass(uint64_t *sm, const ulonglong2 *__res
 #pragma unroll
       for (int t = 0; t < (1 << R); t++) x[t] = sm[pidx(g + t * ST)];
     }
-    tile_compute<R, INV, STRICT>(x, tw, blk0 + b, p);
+    if (FOLD_IN) {
+#pragma unroll
+      for (int t = 0; t < (1 << R); t++) x[t] = fold(x[t], m);
+    }
+    if (INV) tile_inv<R, true>(x, tw, blk0 + b, m);
+    else tile_fwd<R, STRICT>(x, tw, blk0 + b, m);
     if (ST == 1) {
 #pragma unroll
       for (int t = 0; t < (1 << R); t += 2)
@@ -177,22 +305,33 @@ struct PassSize {  // stages per pass when REM stages remain: ceil(REM / ceil(RE
   static constexpr int R = (REM + NP - 1) / NP;
 };
 
-template <int LOGN, int S, bool STRICT>
-__device__ __forceinline__ void fwd_local(uint64_t *sm, const ulonglong2 *tw, uint64_t p, unsigned chunk) {
+// BND = compile-time bound (units of p) of the values entering stage S.
+template <int LOGN, int S, bool STRICT, int BND>
+__device__ __forceinline__ void fwd_local(uint64_t *sm, const ulonglong2 *tw, const Mod &m, unsigned chunk) {
   if constexpr (S < LOGN) {
     constexpr int R = PassSize<LOGN - S>::R;
-    local_pass<LOGN, S, R, false, STRICT>(sm, tw, p, chunk);
+    constexpr bool FOLD = !STRICT && (BND + 2 * R > 31);
+    constexpr int OUT = (FOLD ? 2 : BND) + 2 * R;
+    local_pass<LOGN, S, R, false, STRICT, FOLD>(sm, tw, m, chunk);
     __syncthreads();
-    fwd_local<LOGN, S + R, STRICT>(sm, tw, p, chunk);
+    fwd_local<LOGN, S + R, STRICT, OUT>(sm, tw, m, chunk);
   }
 }
+// bound of the values ntt_forward leaves in shared memory, for inputs below BND0 p
+template <int LOGN, int S, int BND>
+struct FwdBound {
+  static constexpr int R = PassSize<(LOGN - S > 0) ? LOGN - S : 1>::R;
+  static constexpr int value = (S >= LOGN) ? BND : FwdBound<LOGN, (S >= LOGN) ? S : S + R, ((BND + 2 * R > 31) ? 2 : BND) + 2 * R>::value;
+};
+template <int LOGN, int BND>
+struct FwdBound<LOGN, LOGN, BND> { static constexpr int value = BND; };
 
 template <int LOGN, int S>
-__device__ __forceinline__ void inv_local(uint64_t *sm, const ulonglong2 *itw, uint64_t p, unsigned chunk) {
+__device__ __forceinline__ void inv_local(uint64_t *sm, const ulonglong2 *itw, const Mod &m, unsigned chunk) {
   if constexpr (S < LOGN) {
     constexpr int R = PassSize<LOGN - S>::R;
-    inv_local<LOGN, S + R>(sm, itw, p, chunk);
-    local_pass<LOGN, S, R, true, false>(sm, itw, p, chunk);
+    inv_local<LOGN, S + R>(sm, itw, m, chunk);
+    local_pass<LOGN, S, R, true, false, false>(sm, itw, m, chunk);
     __syncthreads();
   }
 }
@@ -202,93 +341,161 @@ __device__ __forceinline__ unsigned chunk_rank() {
   if constexpr (Cfg<LOGN>::C > 1) return cg::this_cluster().block_rank();
   else return 0;
 }
-template <int LOGN>
-__device__ __forceinline__ void cluster_barrier() {
-  if constexpr (Cfg<LOGN>::C > 1) cg::this_cluster().sync();
-  else __syncthreads();
-}
 
 // Forward transform of one limb into the cluster's shared memory.  load(gi) returns coefficient gi of the
-// natural-order input, < 4p (STRICT: <= p).  On return (all CTAs synchronised) this CTA's chunk holds outputs
-// [chunk*M, (chunk+1)*M) of the bit-reversed-order result, lazily reduced (< 4p; STRICT: exact reference values).
-template <int LOGN, bool STRICT, class Load>
-__device__ __forceinline__ void ntt_forward(uint64_t *sm, Load load, const ulonglong2 *__restrict__ tw, uint64_t p) {
+// natural-order input, below BND0 p (BND0 <= 7; STRICT: <= p).  On return (all CTAs synchronised) this CTA's chunk
+// holds outputs [chunk*M, (chunk+1)*M) of the bit-reversed-order result as lazily reduced 64-bit words (any
+// value; fold()/canon() them, or feed them to a Shoup multiplication) -- STRICT: the exact reference values.
+template <int LOGN, bool STRICT, int BND0, class Load>
+__device__ __forceinline__ void ntt_forward(uint64_t *sm, Load load, const ulonglong2 *__restrict__ tw, const Mod &m) {
   typedef Cfg<LOGN> G;
+  static_assert(BND0 + 8 <= 31, "entry bound too large");
   const unsigned chunk = chunk_rank<LOGN>();
   if constexpr (LOGN >= 4) {
     constexpr int ST0 = G::N / 16;
-    const int tau = chunk * G::THREADS + threadIdx.x;
-    uint64_t x[16];
+    constexpr int PER = G::TILES16 / G::THREADS;     // radix-16 tiles per thread in the global pass
+    if constexpr (G::C > 1) cg::this_cluster().sync();   // every CTA of the cluster is resident before remote writes
+#pragma unroll 1
+    for (int r = 0; r < PER; r++) {
+      const int tau = chunk * G::TILES16 + r * G::THREADS + threadIdx.x;
+      uint64_t x[16];
 #pragma unroll
-    for (int t = 0; t < 16; t++) x[t] = load(tau + t * ST0);
-    tile_compute<4, false, STRICT>(x, tw, 1u, p);
-    if constexpr (G::C > 1) {
-      cg::cluster_group cl = cg::this_cluster();
-      cl.sync();   // every CTA of the cluster is resident before remote shared memory is written
+      for (int t = 0; t < 16; t++) x[t] = load(tau + t * ST0);
+      tile_fwd<4, STRICT>(x, tw, 1u, m);
+      if constexpr (G::C > 1) {
+        cg::cluster_group cl = cg::this_cluster();
 #pragma unroll
-      for (int t = 0; t < 16; t++) {
-        const int gi = tau + t * ST0;
-        uint64_t *dst = cl.map_shared_rank(sm, gi >> G::LOGM);
-        dst[pidx(gi & (G::M - 1))] = x[t];
+        for (int t = 0; t < 16; t++) {
+          const int gi = tau + t * ST0;
+          uint64_t *dst = cl.map_shared_rank(sm, gi >> G::LOGM);
+          dst[pidx(gi & (G::M - 1))] = x[t];
+        }
+      } else {
+#pragma unroll
+        for (int t = 0; t < 16; t++) sm[pidx(tau + t * ST0)] = x[t];
       }
-      cl.sync();
-    } else {
-#pragma unroll
-      for (int t = 0; t < 16; t++) sm[pidx(tau + t * ST0)] = x[t];
-      __syncthreads();
     }
-    fwd_local<LOGN, 4, STRICT>(sm, tw, p, chunk);
+    if constexpr (G::C > 1) cg::this_cluster().sync();
+    else __syncthreads();
+    fwd_local<LOGN, 4, STRICT, BND0 + 8>(sm, tw, m, chunk);
   }
 }
 
-// Inverse transform of one limb held in the cluster's shared memory (values < 2p, bit-reversed order);
-// store(gi, v) receives natural-order coefficient gi, already scaled by N^-1 and canonical in [0,p).
-template <int LOGN, class Store>
+// C == 1 only: forward transform of a limb that already sits in shared memory (natural order, padded with pidx,
+// values below BND0 p, visible to the whole CTA after the barrier this function starts with).
+template <int LOGN, bool STRICT, int BND0>
+__device__ __forceinline__ void ntt_forward_resident(uint64_t *sm, const ulonglong2 *__restrict__ tw, const Mod &m) {
+  static_assert(Cfg<LOGN>::C == 1, "resident forward needs the whole limb in one CTA");
+  __syncthreads();
+  fwd_local<LOGN, 0, STRICT, BND0>(sm, tw, m, 0);
+}
+
+// Inverse transform of one limb held in the cluster's shared memory (values below 2p, bit-reversed order);
+// store(gi, v) receives natural-order coefficient gi, already scaled by N^-1, in [0,2p) -- canonical [0,p) when CANON.
+template <int LOGN, bool CANON, class Store>
 __device__ __forceinline__ void ntt_inverse(uint64_t *sm, Store store, const ulonglong2 *__restrict__ itw,
-                                            const PrimeConsts &pc) {
+                                            const PrimeConsts &pc, const Mod &m) {
   typedef Cfg<LOGN> G;
   const unsigned chunk = chunk_rank<LOGN>();
-  const uint64_t p = pc.p;
-  inv_local<LOGN, 4>(sm, itw, p, chunk);
+  inv_local<LOGN, 4>(sm, itw, m, chunk);
   constexpr int ST0 = G::N / 16;
-  const int tau = chunk * G::THREADS + threadIdx.x;
-  uint64_t x[16];
-  if constexpr (G::C > 1) {
-    cg::cluster_group cl = cg::this_cluster();
-    cl.sync();
+  constexpr int PER = G::TILES16 / G::THREADS;
+  if constexpr (G::C > 1) cg::this_cluster().sync();
+#pragma unroll 1
+  for (int r = 0; r < PER; r++) {
+    const int tau = chunk * G::TILES16 + r * G::THREADS + threadIdx.x;
+    uint64_t x[16];
+    if constexpr (G::C > 1) {
+      cg::cluster_group cl = cg::this_cluster();
+#pragma unroll
+      for (int t = 0; t < 16; t++) {
+        const int gi = tau + t * ST0;
+        const uint64_t *src = cl.map_shared_rank(sm, gi >> G::LOGM);
+        x[t] = src[pidx(gi & (G::M - 1))];
+      }
+    } else {
+#pragma unroll
+      for (int t = 0; t < 16; t++) x[t] = sm[pidx(tau + t * ST0)];
+    }
+    tile_inv<4, false>(x, itw, 1u, m);
 #pragma unroll
     for (int t = 0; t < 16; t++) {
-      const int gi = tau + t * ST0;
-      const uint64_t *src = cl.map_shared_rank(sm, gi >> G::LOGM);
-      x[t] = src[pidx(gi & (G::M - 1))];
+      uint64_t v = shoup_lazy(x[t], pc.ninv, pc.ninv_q, m);
+      store(tau + t * ST0, CANON ? csub(v, m.p) : v);
     }
-    cl.sync();   // nobody's shared memory is reused or released while peers still read it
-  } else {
-#pragma unroll
-    for (int t = 0; t < 16; t++) x[t] = sm[pidx(tau + t * ST0)];
-    __syncthreads();
   }
-  tile_compute<4, true, false>(x, itw, 1u, p);
-#pragma unroll
-  for (int t = 0; t < 16; t++) store(tau + t * ST0, shoup(x[t], pc.ninv, pc.ninv_q, p));
+  // nobody's shared memory is reused or released while peers still read it
+  if constexpr (G::C > 1) cg::this_cluster().sync();
+  else __syncthreads();
 }
 
 // ---------------------------------------------------------------------------------------------------------
 // multiword helpers (little-endian, two's complement)
 // ---------------------------------------------------------------------------------------------------------
-// residue of the signed W-word integer words[w*stride] modulo prime `pc` (non-negative, like gcry_mpi_mod in
-// rns_decompose, GPQHE/src/rns.c:37-48).  pow64W = 2^(64 W) mod p.
+// Residue (lazy, below 5p) of the signed W-word integer words[w*stride] modulo the prime -- the same residue class
+// as gcry_mpi_mod in rns_decompose, GPQHE/src/rns.c:37-48.  Horner in 2^64 with Shoup steps; a negative top word
+// subtracts 2^(64 W), i.e. adds p - (2^(64W) mod p) = negW.  WT > 0 fixes W at compile time (all loads issue first).
+template <int WT>
 __device__ __forceinline__ uint64_t decompose_words(const uint64_t *__restrict__ words, size_t stride, int W,
-                                                    const PrimeConsts &pc, uint64_t pow64W) {
-  const uint64_t p = pc.p;
-  uint64_t top = words[(size_t)(W - 1) * stride];
-  uint64_t acc = reduce_word(top, pc);
-  for (int w = W - 2; w >= 0; w--) {
-    uint64_t lo = reduce_word(words[(size_t)w * stride], pc);
-    acc = csub(shoup(acc, pc.r64, pc.r64_q, p) + lo, p);
+                                                    const PrimeConsts &pc, const Mod &m, uint64_t negW) {
+  uint64_t acc, top;
+  if constexpr (WT > 0) {
+    uint64_t raw[WT];
+#pragma unroll
+    for (int w = 0; w < WT; w++) raw[w] = HB_LD(&words[(size_t)w * stride]);
+    top = raw[WT - 1];
+    acc = top;                                               // any 64-bit value is a valid lazy residue
+#pragma unroll
+    for (int w = WT - 2; w >= 0; w--) acc = shoup_lazy(acc, pc.r64, pc.r64_q, m) + fold(raw[w], m);   // < 2p + 2p
+    if (WT == 1) acc = fold(acc, m);
+  } else {
+    top = HB_LD(&words[(size_t)(W - 1) * stride]);
+    acc = top;
+    for (int w = W - 2; w >= 0; w--)
+      acc = shoup_lazy(acc, pc.r64, pc.r64_q, m) + fold(HB_LD(&words[(size_t)w * stride]), m);
+    if (W == 1) acc = fold(acc, m);
   }
-  if ((int64_t)top < 0) acc = (acc >= pow64W) ? acc - pow64W : acc + p - pow64W;
-  return acc;
+  const uint64_t mask = (uint64_t)((int64_t)top >> 63);
+  return acc + (negW & mask);                                // < 5p
+}
+
+// C == 1: residues of sigma_g(poly) mod p into shared memory, natural order.  Coalesced reads of the source
+// coefficients i, scattered to k = i g mod 2N (sign flipped when k >= N): poly_rot / poly_conj, poly.c:263-283.
+template <int LOGN, int WT>
+__device__ __forceinline__ void stage_poly(uint64_t *sm, const uint64_t *__restrict__ poly, int W, unsigned g,
+                                           const PrimeConsts &pc, const Mod &m, uint64_t negW) {
+  typedef Cfg<LOGN> G;
+  const uint64_t p5 = 5 * m.p;
+#pragma unroll 4
+  for (int i = threadIdx.x; i < G::N; i += G::THREADS) {
+    const uint64_t v = decompose_words<WT>(poly + i, G::N, W, pc, m, negW);
+    const unsigned k = ((unsigned)i * g) & (2 * G::N - 1);
+    sm[pidx(k & (G::N - 1))] = (k >= (unsigned)G::N) ? p5 - v : v;
+  }
+}
+
+// Forward NTT (lazy) of the residues mod p of sigma_g(poly) into the cluster's shared memory; ginv = g^-1 mod 2N.
+template <int LOGN>
+__device__ __forceinline__ void poly_forward(uint64_t *sm, const uint64_t *__restrict__ poly, int W, unsigned g,
+                                             unsigned ginv, const PrimeConsts &pc, const Mod &m, uint64_t negW,
+                                             const ulonglong2 *__restrict__ tw) {
+  typedef Cfg<LOGN> G;
+  if constexpr (G::C == 1) {
+    if (W == 1) stage_poly<LOGN, 1>(sm, poly, W, g, pc, m, negW);
+    else if (W == 2) stage_poly<LOGN, 2>(sm, poly, W, g, pc, m, negW);
+    else stage_poly<LOGN, 0>(sm, poly, W, g, pc, m, negW);
+    ntt_forward_resident<LOGN, false, 5>(sm, tw, m);
+  } else {
+    const uint64_t p5 = 5 * m.p;
+    ntt_forward<LOGN, false, 5>(
+        sm,
+        [&](int gi) {
+          const unsigned ip = ((unsigned)gi * ginv) & (2 * G::N - 1);
+          const uint64_t v = decompose_words<0>(poly + (ip & (G::N - 1)), G::N, W, pc, m, negW);
+          return (ip >= (unsigned)G::N) ? p5 - v : v;
+        },
+        tw, m);
+  }
 }
 
 // sign-extend x (WK words) from bit k-1 in place; afterwards words >= ceil(k/64) hold the sign fill.

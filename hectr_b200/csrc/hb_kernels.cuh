@@ -10,39 +10,47 @@ namespace hbdev {
 // K2 / K3: stand-alone batched transforms (config B microbench; building blocks of he_mul)
 // =========================================================================================================
 // Results = ntt() of GPQHE/src/ntt.c:37-52.  STRICT reproduces the reference's [0,p] representation bit for
-// bit; the default returns the same residues canonicalised to [0,p) (p -> 0).
+// bit; the default returns the same residues canonicalised to [0,p) (p -> 0).  Inputs below 4p.
 template <int LOGN, bool STRICT>
-__global__ void __launch_bounds__(Cfg<LOGN>::THREADS)
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS, Cfg<LOGN>::MINBLOCKS)
 k_ntt_fwd(const uint64_t *__restrict__ in, uint64_t *__restrict__ out, Tables T, unsigned d0, unsigned D) {
   typedef Cfg<LOGN> G;
   extern __shared__ __align__(16) uint64_t smem[];
   const unsigned limb = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
   const unsigned d = d0 + limb % D;
-  const uint64_t p = T.primes[d].p;
+  const Mod m = make_mod(T.primes[d].p);
   const ulonglong2 *tw = T.tw + (size_t)d * G::N;
   const uint64_t *src = in + (size_t)limb * G::N;
-  ntt_forward<LOGN, STRICT>(smem, [&](int gi) { return src[gi]; }, tw, p);
+  if constexpr (G::C == 1) {
+#pragma unroll 8
+    for (int i = threadIdx.x; i < G::N; i += G::THREADS) smem[pidx(i)] = HB_LD(&src[i]);
+    ntt_forward_resident<LOGN, STRICT, 4>(smem, tw, m);
+  } else {
+    ntt_forward<LOGN, STRICT, 4>(smem, [&](int gi) { return HB_LD(&src[gi]); }, tw, m);
+  }
   uint64_t *dst = out + (size_t)limb * G::N + (size_t)chunk * G::M;
   for (int i = threadIdx.x; i < G::M; i += G::THREADS) {
     uint64_t v = smem[pidx(i)];
-    dst[i] = STRICT ? v : canon4(v, p);
+    dst[i] = STRICT ? v : canon(v, m);
   }
 }
 
-// Results = invntt() of GPQHE/src/ntt.c:54-73 (canonical [0,p)).  Inputs may be any value <= p.
+// Results = invntt() of GPQHE/src/ntt.c:54-73 (canonical [0,p)).  Inputs may be any value below 2p.
 template <int LOGN>
-__global__ void __launch_bounds__(Cfg<LOGN>::THREADS)
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS, Cfg<LOGN>::MINBLOCKS)
 k_ntt_inv(const uint64_t *__restrict__ in, uint64_t *__restrict__ out, Tables T, unsigned d0, unsigned D) {
   typedef Cfg<LOGN> G;
   extern __shared__ __align__(16) uint64_t smem[];
   const unsigned limb = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
   const unsigned d = d0 + limb % D;
   const PrimeConsts pc = T.primes[d];
+  const Mod m = make_mod(pc.p);
   const uint64_t *src = in + (size_t)limb * G::N + (size_t)chunk * G::M;
-  for (int i = threadIdx.x; i < G::M; i += G::THREADS) smem[pidx(i)] = src[i];
+#pragma unroll 8
+  for (int i = threadIdx.x; i < G::M; i += G::THREADS) smem[pidx(i)] = HB_LD(&src[i]);
   __syncthreads();
   uint64_t *dst = out + (size_t)limb * G::N;
-  ntt_inverse<LOGN>(smem, [&](int gi, uint64_t v) { dst[gi] = v; }, T.itw + (size_t)d * G::N, pc);
+  ntt_inverse<LOGN, true>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, T.itw + (size_t)d * G::N, pc, m);
 }
 
 // =========================================================================================================
@@ -50,7 +58,7 @@ k_ntt_inv(const uint64_t *__restrict__ in, uint64_t *__restrict__ out, Tables T,
 // =========================================================================================================
 // src: npoly polynomials, polynomial q at src + q*poly_stride, W words each.  out[q][d][N], canonical.
 template <int LOGN>
-__global__ void __launch_bounds__(Cfg<LOGN>::THREADS)
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS, Cfg<LOGN>::MINBLOCKS)
 k_poly_ntt(const uint64_t *__restrict__ src, size_t poly_stride, int W, uint64_t *__restrict__ out, Tables T,
            unsigned D) {
   typedef Cfg<LOGN> G;
@@ -58,12 +66,26 @@ k_poly_ntt(const uint64_t *__restrict__ src, size_t poly_stride, int W, uint64_t
   const unsigned idx = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
   const unsigned q = idx / D, d = idx % D;
   const PrimeConsts pc = T.primes[d];
-  const uint64_t pw = T.pow64[(size_t)d * (T.WC + 1) + W];
+  const Mod m = make_mod(pc.p);
+  const uint64_t negW = pc.p - T.pow64[(size_t)d * (T.WC + 1) + W];
   const uint64_t *poly = src + (size_t)q * poly_stride;
-  ntt_forward<LOGN, false>(smem, [&](int gi) { return decompose_words(poly + gi, G::N, W, pc, pw); },
-                           T.tw + (size_t)d * G::N, pc.p);
+  poly_forward<LOGN>(smem, poly, W, 1u, 1u, pc, m, negW, T.tw + (size_t)d * G::N);
   uint64_t *dst = out + ((size_t)q * D + d) * G::N + (size_t)chunk * G::M;
-  for (int i = threadIdx.x; i < G::M; i += G::THREADS) dst[i] = canon4(smem[pidx(i)], pc.p);
+  for (int i = threadIdx.x; i < G::M; i += G::THREADS) dst[i] = canon(smem[pidx(i)], m);
+}
+
+// canonical residues -> Shoup pairs (w, floor(w 2^64 / p)) for fixed multiplicands (keys, encoded diagonals).
+// limbs[j][N] uses prime j % D.  A residue stored as p becomes 0: the same class.
+__global__ void k_shoup_prep(const uint64_t *__restrict__ in, ulonglong2 *__restrict__ out, Tables T, unsigned D,
+                             size_t nlimbs) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= nlimbs * T.N) return;
+  const unsigned d = (unsigned)((gid / T.N) % D);
+  const uint64_t p = T.primes[d].p;
+  uint64_t w = in[gid];
+  if (w >= p) w -= p;
+  const unsigned __int128 num = ((unsigned __int128)w) << 64;
+  out[gid] = make_ulonglong2(w, (uint64_t)(num / p));
 }
 
 // =========================================================================================================
@@ -71,74 +93,120 @@ k_poly_ntt(const uint64_t *__restrict__ src, size_t poly_stride, int W, uint64_t
 //   chat[b][h][d] = invntt( ntt( decompose( sigma(src_b) ) mod p_d ) o evk.p_h[d] ),  h = 0,1
 // sigma is the automorphism X -> X^g fused into the load (poly_rot / poly_conj, poly.c:263-283), given as
 // ginv = g^-1 mod 2N:  sigma(a)[k] = +a[k*ginv mod 2N]  if that index is < N, else  -a[(k*ginv mod 2N) - N].
+// evk: Shoup pairs [2][dimevk][N].  chat is lazily reduced (below 2p): its only consumers multiply it by a
+// fixed constant first (crt_low), which accepts any 64-bit word.
 // =========================================================================================================
 template <int LOGN>
-__global__ void __launch_bounds__(Cfg<LOGN>::THREADS)
-k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, unsigned ginv,
-          const uint64_t *__restrict__ evk, unsigned dimevk, uint64_t *__restrict__ chat, Tables T, unsigned D) {
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS, (Cfg<LOGN>::MINBLOCKS > 2 ? 2 : Cfg<LOGN>::MINBLOCKS))
+k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, unsigned g, unsigned ginv,
+          const ulonglong2 *__restrict__ evk, unsigned dimevk, uint64_t *__restrict__ chat, Tables T, unsigned D) {
   typedef Cfg<LOGN> G;
   extern __shared__ __align__(16) uint64_t smem[];
   uint64_t *smA = smem, *smB = smem + G::SMEM_WORDS;
   const unsigned idx = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
+#ifdef HB_DMAJOR
+  const unsigned nb = gridDim.x / (G::C * D);
+  const unsigned d = idx / nb, b = idx % nb;
+#else
   const unsigned b = idx / D, d = idx % D;
+#endif
   const PrimeConsts pc = T.primes[d];
-  const uint64_t p = pc.p;
-  const uint64_t pw = T.pow64[(size_t)d * (T.WC + 1) + W];
+  const Mod m = make_mod(pc.p);
+  const uint64_t negW = pc.p - T.pow64[(size_t)d * (T.WC + 1) + W];
   const uint64_t *poly = src + (size_t)b * src_bstride;
-  ntt_forward<LOGN, false>(
-      smA,
-      [&](int gi) {
-        unsigned ip = ((unsigned)gi * ginv) & (2 * G::N - 1);
-        uint64_t v = decompose_words(poly + (ip & (G::N - 1)), G::N, W, pc, pw);
-        return (ip >= (unsigned)G::N && v) ? p - v : v;
-      },
-      T.tw + (size_t)d * G::N, p);
+  poly_forward<LOGN>(smA, poly, W, g, ginv, pc, m, negW, T.tw + (size_t)d * G::N);
 #pragma unroll 1
   for (int h = 0; h < 2; h++) {
-    const uint64_t *key = evk + ((size_t)h * dimevk + d) * G::N + (size_t)chunk * G::M;
-    for (int i = threadIdx.x; i < G::M; i += G::THREADS)
-      smB[pidx(i)] = mulmod_barrett(canon4(smA[pidx(i)], p), key[i], p, pc.mu);
+    const ulonglong2 *key = evk + ((size_t)h * dimevk + d) * G::N + (size_t)chunk * G::M;
+#pragma unroll 4
+    for (int i = threadIdx.x; i < G::M; i += G::THREADS) {
+      const ulonglong2 k = HB_LDS2(&key[i]);
+      smB[pidx(i)] = shoup_lazy(smA[pidx(i)], k.x, k.y, m);
+    }
     __syncthreads();
     uint64_t *dst = chat + (((size_t)b * 2 + h) * D + d) * G::N;
-    ntt_inverse<LOGN>(smB, [&](int gi, uint64_t v) { dst[gi] = v; }, T.itw + (size_t)d * G::N, pc);
+    ntt_inverse<LOGN, false>(smB, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, T.itw + (size_t)d * G::N, pc, m);
   }
 }
 
 // =========================================================================================================
 // ct x pt, per-limb:  he_mulpt  GPQHE/src/he-mult.c:176-188
-//   chat[b][h][d] = invntt( ntt(decompose(c_h)) o pthat[d] )
+//   chat[b][h][d] = invntt( ntt(decompose(c_h)) o pthat[d] )          pthat: Shoup pairs [D][N]
 // =========================================================================================================
 template <int LOGN>
-__global__ void __launch_bounds__(Cfg<LOGN>::THREADS)
-k_mulpt_limb(const uint64_t *__restrict__ ct, int W, const uint64_t *__restrict__ pthat,
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS, Cfg<LOGN>::MINBLOCKS)
+k_mulpt_limb(const uint64_t *__restrict__ ct, int W, const ulonglong2 *__restrict__ pthat,
              uint64_t *__restrict__ chat, Tables T, unsigned D) {
   typedef Cfg<LOGN> G;
   extern __shared__ __align__(16) uint64_t smem[];
   const unsigned idx = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
+#ifdef HB_DMAJOR
+  const unsigned nq = gridDim.x / (G::C * D);
+  const unsigned d = idx / nq, q = idx % nq;        // q = b*2 + h
+#else
   const unsigned q = idx / D, d = idx % D;          // q = b*2 + h
+#endif
   const PrimeConsts pc = T.primes[d];
-  const uint64_t p = pc.p;
-  const uint64_t pw = T.pow64[(size_t)d * (T.WC + 1) + W];
+  const Mod m = make_mod(pc.p);
+  const uint64_t negW = pc.p - T.pow64[(size_t)d * (T.WC + 1) + W];
   const uint64_t *poly = ct + (size_t)q * W * G::N;
-  ntt_forward<LOGN, false>(smem, [&](int gi) { return decompose_words(poly + gi, G::N, W, pc, pw); },
-                           T.tw + (size_t)d * G::N, p);
-  const uint64_t *pt = pthat + (size_t)d * G::N + (size_t)chunk * G::M;
-  for (int i = threadIdx.x; i < G::M; i += G::THREADS)
-    smem[pidx(i)] = mulmod_barrett(canon4(smem[pidx(i)], p), pt[i], p, pc.mu);
+  poly_forward<LOGN>(smem, poly, W, 1u, 1u, pc, m, negW, T.tw + (size_t)d * G::N);
+  const ulonglong2 *pt = pthat + (size_t)d * G::N + (size_t)chunk * G::M;
+#pragma unroll 4
+  for (int i = threadIdx.x; i < G::M; i += G::THREADS) {
+    const ulonglong2 k = HB_LDS2(&pt[i]);
+    smem[pidx(i)] = shoup_lazy(smem[pidx(i)], k.x, k.y, m);
+  }
   __syncthreads();
   uint64_t *dst = chat + ((size_t)q * D + d) * G::N;
-  ntt_inverse<LOGN>(smem, [&](int gi, uint64_t v) { dst[gi] = v; }, T.itw + (size_t)d * G::N, pc);
+  ntt_inverse<LOGN, false>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, T.itw + (size_t)d * G::N, pc, m);
+}
+
+// =========================================================================================================
+// rotation-sum inner step of he_gemv (GPQHE/src/he-algo.c:64-79), accumulated in the NTT domain:
+//   chat[q][d] = invntt( sum_j  hat[j][q][d] o pthat[j][d] ),   q = b*2 + h,  j < n1
+// hat[j] = ntt(decompose(rot_j(ct))) (k_poly_ntt), pthat[j] = Shoup pairs of the j-th encoded diagonal of this giant
+// step.  The reference multiplies, reconstructs and adds mod q_l one diagonal at a time; the transforms and the CRT
+// are linear, so the sum of the exact products is the same integer as long as it stays inside (-P_D/2, P_D/2),
+// which the host checks when it builds the plan (hb_api.cu gemv_plan).
+// =========================================================================================================
+template <int LOGN>
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS, Cfg<LOGN>::MINBLOCKS)
+k_mulacc_intt(const uint64_t *__restrict__ hat, size_t hat_jstride, const ulonglong2 *__restrict__ pthat, unsigned n1,
+              uint64_t *__restrict__ chat, Tables T, unsigned D) {
+  typedef Cfg<LOGN> G;
+  extern __shared__ __align__(16) uint64_t smem[];
+  const unsigned idx = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
+  const unsigned q = idx / D, d = idx % D;
+  const PrimeConsts pc = T.primes[d];
+  const Mod m = make_mod(pc.p);
+  const size_t off = (size_t)chunk * G::M;
+  const uint64_t *a = hat + ((size_t)q * D + d) * G::N + off;
+  const ulonglong2 *w = pthat + (size_t)d * G::N + off;
+#pragma unroll 2
+  for (int i = threadIdx.x; i < G::M; i += G::THREADS) {
+    uint64_t acc = 0;
+    for (unsigned j = 0; j < n1; j++) {
+      const ulonglong2 k = HB_LDS2(&w[(size_t)j * D * G::N + i]);
+      acc += shoup_lazy(HB_LD(&a[(size_t)j * hat_jstride + i]), k.x, k.y, m);      // each term below 2p
+      if ((j & 7) == 7) acc = fold(acc, m);
+    }
+    smem[pidx(i)] = fold(acc, m);
+  }
+  __syncthreads();
+  uint64_t *dst = chat + ((size_t)q * D + d) * G::N;
+  ntt_inverse<LOGN, false>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, T.itw + (size_t)d * G::N, pc, m);
 }
 
 // =========================================================================================================
 // ct x ct tensor, per-limb:  he_mul  GPQHE/src/he-mult.c:116-138
-//   in  hatA[b][2][D][N], hatB[b][2][D][N] = ntt of (a.c0, a.c1), (b.c0, b.c1)      (k_poly_ntt)
-//   out dhat[b][3][D][N] = invntt of (a0 b0, a0 b1 + a1 b0, a1 b1)
+//   in  hatA[b][2][D][N], hatB[b][2][D][N] = ntt of (a.c0, a.c1), (b.c0, b.c1)      (k_poly_ntt, canonical)
+//   out dhat[b][3][D][N] = invntt of (a0 b0, a0 b1 + a1 b0, a1 b1)                   (lazily reduced, below 2p)
 // The reference inverts a0 b1 and a1 b0 separately and adds mod p afterwards; the inverse transform is linear
-// mod p, so adding first gives the same canonical residues.
+// mod p, so adding first gives the same residues.
 // =========================================================================================================
 template <int LOGN>
-__global__ void __launch_bounds__(Cfg<LOGN>::THREADS)
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS, Cfg<LOGN>::MINBLOCKS)
 k_tensor_intt(const uint64_t *__restrict__ hatA, const uint64_t *__restrict__ hatB, uint64_t *__restrict__ dhat, Tables T,
               unsigned D) {
   typedef Cfg<LOGN> G;
@@ -146,6 +214,7 @@ k_tensor_intt(const uint64_t *__restrict__ hatA, const uint64_t *__restrict__ ha
   const unsigned idx = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
   const unsigned d = idx % D, which = (idx / D) % 3, b = idx / (3 * D);
   const PrimeConsts pc = T.primes[d];
+  const Mod m = make_mod(pc.p);
   const uint64_t p = pc.p;
   const size_t off = (size_t)d * G::N + (size_t)chunk * G::M;
   const uint64_t *a0 = hatA + ((size_t)b * 2 + 0) * D * G::N + off, *a1 = hatA + ((size_t)b * 2 + 1) * D * G::N + off;
@@ -159,7 +228,7 @@ k_tensor_intt(const uint64_t *__restrict__ hatA, const uint64_t *__restrict__ ha
   }
   __syncthreads();
   uint64_t *dst = dhat + (((size_t)b * 3 + which) * D + d) * G::N;
-  ntt_inverse<LOGN>(smem, [&](int gi, uint64_t v) { dst[gi] = v; }, T.itw + (size_t)d * G::N, pc);
+  ntt_inverse<LOGN, false>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, T.itw + (size_t)d * G::N, pc, m);
 }
 
 // =========================================================================================================

@@ -119,6 +119,7 @@ std::string build_tables(HostTables &t, unsigned logn, unsigned logq, unsigned s
   uint64_t p = (1ULL << LOGP) + 1;
   for (unsigned d = 0; d < t.dimub; d++) {
     do { p += 2ULL * N; } while (!is_prime_u64(p));
+    if (p - (1ULL << LOGP) >= (1ULL << 28)) return "internal: prime chain leaves 2^59 + 2^28 (the kernels fold with c = p - 2^59 < 2^28)";
     PrimeConsts &c = t.primes[d];
     c.p = p;
     c.mu = (uint64_t)((((u128)1) << 120) / p);

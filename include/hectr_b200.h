@@ -54,7 +54,7 @@ typedef struct hb_pt {             /* he_pt_t (gpqhe.h:93-97) */
 } hb_pt;
 
 typedef struct hb_evk {            /* he_evk_t (gpqhe.h:78-82) */
-  uint64_t *p;                     /* DEVICE pointer [2][dimevk][N] */
+  uint64_t *p;                     /* DEVICE pointer [2][dimevk][N] pairs (key limb, its Shoup quotient) */
 } hb_evk;
 
 /* ---- context: hectx_init / hectx_exit (precomp.c:431-453,465-) --------------------------------- */

@@ -153,6 +153,12 @@ def test_gemv_and_hempc(cfgA):
     want = ref.gemv(Ka, cts["xhat"], cfgA["rk"])
     assert got.l == want.l == 1
     assert np.array_equal(got.download()[0], ref.ct_to_words(want)), "he_gemv ciphertext differs"
+    assert got.nu == want.nu and got.B == want.B
+    # dense matrix (every diagonal non-zero, complex entries)
+    Ad = rng.standard_normal((S, S)) + 1j * rng.standard_normal((S, S))
+    gotd = eng.he_gemv(Ad, e["xhat"], keys)
+    wantd = ref.gemv(Ad, cts["xhat"], cfgA["rk"])
+    assert np.array_equal(gotd.download()[0], ref.ct_to_words(wantd)), "dense he_gemv ciphertext differs"
     # the ciphertext half of ctr_hempc (src/hempc.c:253-266)
     xd, ud = ref.sub(cts["xhat"], cts["xr"]), ref.sub(cts["uhat"], cts["ur"])
     du = ref.neg(ref.add(ref.gemv(Ka, xd, cfgA["rk"]), ref.gemv(Kb, ud, cfgA["rk"])))
@@ -165,6 +171,28 @@ def test_gemv_and_hempc(cfgA):
     dec = ref.decode(ref.dec(up_ref, sk))
     plain = vals["uhat"] - (Ka @ (vals["xhat"] - vals["xr"]) + Kb @ (vals["uhat"] - vals["ur"]))
     assert np.abs(dec - plain).max() < 1e-7
+
+
+def test_gemv_fused_equals_stepwise(cfgA, monkeypatch):
+    """The memoised / NTT-domain-accumulated he_gemv schedule against the call-by-call reference schedule on a
+    batch of random ciphertexts and a dense matrix (size-independent property: both must give the same words)."""
+    from hectr_b200 import Engine
+    eng, keys = cfgA["eng"], cfgA["keys"]
+    rng = np.random.default_rng(43)
+    S, l = 16, 2
+    a = random_ct_words(rng, 5, eng.words(l), eng.n, eng.logq(l))
+    A = rng.standard_normal((S, S)) + 1j * rng.standard_normal((S, S))
+    fused = eng.he_gemv(A, eng.ct(a, l), keys).download()
+    monkeypatch.setenv("HB_GEMV_STEPWISE", "1")
+    eng2 = Engine(*A_PARAMS)
+    try:
+        rk_arr = np.stack([cfgA["ref"].evk_to_array(cfgA["rk"][i]) for i in range(S)])
+        keys2 = eng2.keys(rk_arr)
+        step = eng2.he_gemv(A, eng2.ct(a, l), keys2).download()
+        keys2.free()
+    finally:
+        eng2.close()
+    assert np.array_equal(fused, step)
 
 
 def test_mul_relin(cfgA):
