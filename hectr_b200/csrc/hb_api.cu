@@ -63,6 +63,7 @@ struct hb_ctx {
   // workspaces (grow only)
   uint64_t *wsA = nullptr, *wsB = nullptr, *wsC = nullptr;
   size_t wsA_bytes = 0, wsB_bytes = 0, wsC_bytes = 0;
+  bool exact_tail = false;          // HB_KS_EXACT=1: always take the multiword key-switch tail (tests)
   bool stepwise = false;            // HB_GEMV_STEPWISE=1: evaluate he_gemv one reference call at a time (tests, A/B timing)
   // pool of ciphertext buffers keyed by capacity in bytes
   std::multimap<size_t, uint64_t *> pool;
@@ -251,6 +252,32 @@ static void do_ks_finish(hb_ctx *c, const uint64_t *chat, unsigned D, const uint
   const size_t total = (size_t)batch * 2 * c->ht.N;
   const unsigned grid = (unsigned)((total + threads - 1) / threads);
   const unsigned wk = (k + 63) / 64;
+  const hb::HostTables &h = c->ht;
+  if (D <= 8 && h.dim <= 4 && h.dim <= D && wk <= 2 && h.WP <= 4 && !c->exact_tail) {
+    hbdev::KsFast F;
+    memset(&F, 0, sizeof F);
+    F.D = D; F.dim = h.dim;
+    for (unsigned d = 0; d < D; d++) {
+      F.p[d] = h.primes[d].p; F.mu[d] = h.primes[d].mu;
+      F.inv[d] = h.crt_inv[(size_t)D * h.dimub + d]; F.invq[d] = h.crt_inv_q[(size_t)D * h.dimub + d];
+      for (unsigned w = 0; w < 2 && w < h.WC; w++) F.phat[d][w] = h.crt_phat[((size_t)D * h.dimub + d) * h.WC + w];
+    }
+    for (unsigned w = 0; w < 2 && w < h.WC; w++) { F.PD[w] = h.crt_P[(size_t)D * h.WC + w]; F.Pinv[w] = h.ks_Pinv[w]; }
+    for (unsigned e = 0; e < h.dim; e++) {
+      F.kinv[e] = h.ks_inv[e]; F.kinvq[e] = h.ks_inv_q[e];
+      for (unsigned w = 0; w < 2 && w < h.WP; w++) F.kphat[e][w] = h.ks_phat[(size_t)e * h.WP + w];
+    }
+    for (unsigned w = 0; w < 2 && w < h.WP; w++) F.kP[w] = h.ks_P[w];
+    bool done = true;
+#define KSF(DD, MM)                                                                                                             \
+    if (D == DD && h.dim == MM) {                                                                                               \
+      if (wk == 1) launch(c, "k_ks_finish_fast", hbdev::k_ks_finish_fast<1, 4, DD, MM>, grid, threads, 0, 1, chat, F, add0, add1, add_bstride, Wadd, ginv, out, Wout, k, c->dt, batch); \
+      else launch(c, "k_ks_finish_fast", hbdev::k_ks_finish_fast<2, 4, DD, MM>, grid, threads, 0, 1, chat, F, add0, add1, add_bstride, Wadd, ginv, out, Wout, k, c->dt, batch);        \
+    } else
+    KSF(5, 2) KSF(6, 2) KSF(5, 3) KSF(6, 3) KSF(7, 3) KSF(8, 3) done = false;
+#undef KSF
+    if (done) return;
+  }
   switch (wk_class(wk)) {
 #define X(WKC) case WKC: ks_finish_wp<WKC>(c, grid, threads, chat, D, add0, add1, add_bstride, Wadd, ginv, out, Wout, k, batch); break;
     X(1) X(2) X(4) X(8) X(16)
@@ -305,6 +332,9 @@ extern "C" hb_ctx *hb_ctx_create(unsigned logn, unsigned logq, unsigned slots, u
   t.primes = (const hbdev::PrimeConsts *)upload_vec(ctx, h.primes);
   t.tw = (const ulonglong2 *)upload_vec(ctx, h.tw);
   t.itw = (const ulonglong2 *)upload_vec(ctx, h.itw);
+  t.tw_tr = (const ulonglong2 *)upload_vec(ctx, h.tw_tr);
+  t.itw_tr = (const ulonglong2 *)upload_vec(ctx, h.itw_tr);
+  t.tr_stride = h.tr_stride;
   t.pow64 = upload_vec(ctx, h.pow64);
   t.crt_inv = upload_vec(ctx, h.crt_inv);
   t.crt_inv_q = upload_vec(ctx, h.crt_inv_q);
@@ -320,6 +350,8 @@ extern "C" hb_ctx *hb_ctx_create(unsigned logn, unsigned logq, unsigned slots, u
   {
     const char *e = getenv("HB_GEMV_STEPWISE");
     ctx->stepwise = e && *e && *e != '0';
+    e = getenv("HB_KS_EXACT");
+    ctx->exact_tail = e && *e && *e != '0';
   }
   ctx->ring = hb_ring_create(logn);
   ctx->enc_host.assign((size_t)h.WC * h.N, 0);

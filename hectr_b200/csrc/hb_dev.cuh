@@ -46,6 +46,8 @@ struct PrimeConsts {  // must match hb::PrimeConsts
 struct Tables {  // device pointers, passed by value
   const PrimeConsts *primes;   // [dimub]
   const ulonglong2 *tw, *itw;  // [dimub][N] (w, floor(w 2^64 / p))
+  const ulonglong2 *tw_tr, *itw_tr;   // [dimub][TR_STRIDE]: the stride-1 pass's twiddles, lane-transposed (hb_tables.hpp)
+  unsigned tr_stride;
   const uint64_t *pow64;       // [dimub][WC+1]
   const uint64_t *crt_inv, *crt_inv_q;  // [dimub+1][dimub]
   const uint64_t *crt_phat;    // [dimub+1][dimub][WC]
@@ -199,11 +201,37 @@ struct Cfg {
 
 __device__ __forceinline__ int pidx(int i) { return i + ((i >> 4) << 1); }
 
+// Twiddle tables of one prime and one direction.  nat: index = bit-reversed exponent (entry k of stage s at 2^s + k).
+// tr: the stride-1 pass (last forward pass, first inverse pass) gives every thread its own 2^R - 1 twiddles; read
+// from `nat` that is up to 32 cache lines per warp load, so a lane-transposed copy keeps each load at 4 lines:
+//   slot (2^e - 1) + u of global tile K  at  ((K >> 5) (2^R - 1) + slot) 32 + (K & 31),  holding nat[((2^S + K) << e) + u]
+// (e = 0 is the coarsest stage of the tile, S = log2 N - R).  Built by hb::build_tables.
+struct Tw {
+  const ulonglong2 *nat, *tr;
+};
+__device__ __forceinline__ Tw make_tw(const Tables &T, unsigned d, bool inverse) {
+  Tw t;
+  t.nat = (inverse ? T.itw : T.tw) + (size_t)d * T.N;
+  t.tr = (inverse ? T.itw_tr : T.tw_tr) + (size_t)d * T.tr_stride;
+  return t;
+}
+// twiddle (e, u) of a tile: natural table addressed by the tile's coarsest block index K0, or the transposed copy
+template <int R, bool TR>
+struct TileTw {
+  const ulonglong2 *base;
+  unsigned K0;
+  __device__ __forceinline__ TileTw(const Tw &tw, unsigned K0_, unsigned K) : K0(K0_) {
+    base = TR ? tw.tr + (size_t)(K >> 5) * (((1 << R) - 1) * 32) + (K & 31) : tw.nat;
+  }
+  __device__ __forceinline__ ulonglong2 get(int e, int u) const {
+    return TR ? __ldg(&base[(((1 << e) - 1) + u) * 32]) : __ldg(&base[(K0 << e) + u]);
+  }
+};
+
 // Forward tile: 2^R elements, stages beta = R-1 .. 0.  Twiddle index of the butterfly at tile-bit `beta` for tile
 // element t, tile whose coarsest block index is K0 (= 2^S + block):  k = (K0 << (R-1-beta)) + (t >> (beta+1)).
-template <int R, bool STRICT>
-__device__ __forceinline__ void tile_fwd(uint64_t (&x)[1 << R], const ulonglong2 *__restrict__ tw, unsigned K0,
-                                         const Mod &m) {
+template <int R, bool STRICT, class TW>
+__device__ __forceinline__ void tile_fwd(uint64_t (&x)[1 << R], const TW &tw, const Mod &m) {
 #pragma unroll
   for (int a = 0; a < R; a++) {
     const int beta = R - 1 - a;
@@ -211,7 +239,7 @@ __device__ __forceinline__ void tile_fwd(uint64_t (&x)[1 << R], const ulonglong2
 #pragma unroll
     for (int t = 0; t < (1 << R); t++) {
       if ((t & half) == 0) {
-        ulonglong2 w = __ldg(&tw[(K0 << (R - 1 - beta)) + (t >> (beta + 1))]);
+        ulonglong2 w = tw.get(R - 1 - beta, t >> (beta + 1));
         ct_bfly<STRICT>(x[t], x[t + half], w, m);
       }
     }
@@ -222,9 +250,8 @@ __device__ __forceinline__ void tile_fwd(uint64_t (&x)[1 << R], const ulonglong2
 // stage, the product leg returns to 2p; bounds are tracked at compile time (the loops are fully unrolled) and a
 // leg is folded back below 2p only when the next sum could pass 31p.  With FOLD_OUT every element leaves below
 // 2p again (needed between passes); the last pass multiplies by N^-1 instead, which accepts any input.
-template <int R, bool FOLD_OUT>
-__device__ __forceinline__ void tile_inv(uint64_t (&x)[1 << R], const ulonglong2 *__restrict__ tw, unsigned K0,
-                                         const Mod &m) {
+template <int R, bool FOLD_OUT, class TW>
+__device__ __forceinline__ void tile_inv(uint64_t (&x)[1 << R], const TW &tw, const Mod &m) {
   int bnd[1 << R];
 #pragma unroll
   for (int t = 0; t < (1 << R); t++) bnd[t] = 2;
@@ -239,7 +266,7 @@ __device__ __forceinline__ void tile_inv(uint64_t (&x)[1 << R], const ulonglong2
           if (bnd[t] > 2) { x[t] = fold(x[t], m); bnd[t] = 2; }
           if (bnd[t + half] > 2) { x[t + half] = fold(x[t + half], m); bnd[t + half] = 2; }
         }
-        ulonglong2 w = __ldg(&tw[(K0 << (R - 1 - beta)) + (t >> (beta + 1))]);
+        ulonglong2 w = tw.get(R - 1 - beta, t >> (beta + 1));
         const int by = bnd[t + half];
         if (by == 2) gs_bfly<2>(x[t], x[t + half], w, m);
         else if (by == 4) gs_bfly<4>(x[t], x[t + half], w, m);
@@ -260,8 +287,7 @@ __device__ __forceinline__ void tile_inv(uint64_t (&x)[1 << R], const ulonglong2
 // One chunk-local pass: stages [S, S+R) in forward numbering (len = N>>(S+1) ...), on this CTA's chunk.
 // FOLD_IN (forward only): fold every element below 2p on entry (bound bookkeeping of ntt_forward).
 template <int LOGN, int S, int R, bool INV, bool STRICT, bool FOLD_IN>
-__device__ __forceinline__ void local_pass(uint64_t *sm, const ulonglong2 *__restrict__ tw, const Mod &m,
-                                           unsigned chunk) {
+__device__ __forceinline__ void local_pass(uint64_t *sm, const Tw &tw, const Mod &m, unsigned chunk) {
   typedef Cfg<LOGN> G;
   constexpr int LOGST = LOGN - S - R;           // log2 of the element stride inside a tile
   constexpr int ST = 1 << LOGST;
@@ -286,8 +312,9 @@ __device__ __forceinline__ void local_pass(uint64_t *sm, const ulonglong2 *__res
 #pragma unroll
       for (int t = 0; t < (1 << R); t++) x[t] = fold(x[t], m);
     }
-    if (INV) tile_inv<R, true>(x, tw, blk0 + b, m);
-    else tile_fwd<R, STRICT>(x, tw, blk0 + b, m);
+    const TileTw<R, ST == 1> ttw(tw, blk0 + b, (chunk << (G::LOGM - R)) + tile);
+    if (INV) tile_inv<R, true>(x, ttw, m);
+    else tile_fwd<R, STRICT>(x, ttw, m);
     if (ST == 1) {
 #pragma unroll
       for (int t = 0; t < (1 << R); t += 2)
@@ -307,7 +334,7 @@ struct PassSize {  // stages per pass when REM stages remain: ceil(REM / ceil(RE
 
 // BND = compile-time bound (units of p) of the values entering stage S.
 template <int LOGN, int S, bool STRICT, int BND>
-__device__ __forceinline__ void fwd_local(uint64_t *sm, const ulonglong2 *tw, const Mod &m, unsigned chunk) {
+__device__ __forceinline__ void fwd_local(uint64_t *sm, const Tw &tw, const Mod &m, unsigned chunk) {
   if constexpr (S < LOGN) {
     constexpr int R = PassSize<LOGN - S>::R;
     constexpr bool FOLD = !STRICT && (BND + 2 * R > 31);
@@ -327,7 +354,7 @@ template <int LOGN, int BND>
 struct FwdBound<LOGN, LOGN, BND> { static constexpr int value = BND; };
 
 template <int LOGN, int S>
-__device__ __forceinline__ void inv_local(uint64_t *sm, const ulonglong2 *itw, const Mod &m, unsigned chunk) {
+__device__ __forceinline__ void inv_local(uint64_t *sm, const Tw &itw, const Mod &m, unsigned chunk) {
   if constexpr (S < LOGN) {
     constexpr int R = PassSize<LOGN - S>::R;
     inv_local<LOGN, S + R>(sm, itw, m, chunk);
@@ -347,7 +374,7 @@ __device__ __forceinline__ unsigned chunk_rank() {
 // holds outputs [chunk*M, (chunk+1)*M) of the bit-reversed-order result as lazily reduced 64-bit words (any
 // value; fold()/canon() them, or feed them to a Shoup multiplication) -- STRICT: the exact reference values.
 template <int LOGN, bool STRICT, int BND0, class Load>
-__device__ __forceinline__ void ntt_forward(uint64_t *sm, Load load, const ulonglong2 *__restrict__ tw, const Mod &m) {
+__device__ __forceinline__ void ntt_forward(uint64_t *sm, Load load, const Tw &tw, const Mod &m) {
   typedef Cfg<LOGN> G;
   static_assert(BND0 + 8 <= 31, "entry bound too large");
   const unsigned chunk = chunk_rank<LOGN>();
@@ -361,7 +388,7 @@ __device__ __forceinline__ void ntt_forward(uint64_t *sm, Load load, const ulong
       uint64_t x[16];
 #pragma unroll
       for (int t = 0; t < 16; t++) x[t] = load(tau + t * ST0);
-      tile_fwd<4, STRICT>(x, tw, 1u, m);
+      tile_fwd<4, STRICT>(x, TileTw<4, false>(tw, 1u, 0u), m);
       if constexpr (G::C > 1) {
         cg::cluster_group cl = cg::this_cluster();
 #pragma unroll
@@ -384,7 +411,7 @@ __device__ __forceinline__ void ntt_forward(uint64_t *sm, Load load, const ulong
 // C == 1 only: forward transform of a limb that already sits in shared memory (natural order, padded with pidx,
 // values below BND0 p, visible to the whole CTA after the barrier this function starts with).
 template <int LOGN, bool STRICT, int BND0>
-__device__ __forceinline__ void ntt_forward_resident(uint64_t *sm, const ulonglong2 *__restrict__ tw, const Mod &m) {
+__device__ __forceinline__ void ntt_forward_resident(uint64_t *sm, const Tw &tw, const Mod &m) {
   static_assert(Cfg<LOGN>::C == 1, "resident forward needs the whole limb in one CTA");
   __syncthreads();
   fwd_local<LOGN, 0, STRICT, BND0>(sm, tw, m, 0);
@@ -393,8 +420,8 @@ __device__ __forceinline__ void ntt_forward_resident(uint64_t *sm, const ulonglo
 // Inverse transform of one limb held in the cluster's shared memory (values below 2p, bit-reversed order);
 // store(gi, v) receives natural-order coefficient gi, already scaled by N^-1, in [0,2p) -- canonical [0,p) when CANON.
 template <int LOGN, bool CANON, class Store>
-__device__ __forceinline__ void ntt_inverse(uint64_t *sm, Store store, const ulonglong2 *__restrict__ itw,
-                                            const PrimeConsts &pc, const Mod &m) {
+__device__ __forceinline__ void ntt_inverse(uint64_t *sm, Store store, const Tw &itw, const PrimeConsts &pc,
+                                            const Mod &m) {
   typedef Cfg<LOGN> G;
   const unsigned chunk = chunk_rank<LOGN>();
   inv_local<LOGN, 4>(sm, itw, m, chunk);
@@ -417,7 +444,7 @@ __device__ __forceinline__ void ntt_inverse(uint64_t *sm, Store store, const ulo
 #pragma unroll
       for (int t = 0; t < 16; t++) x[t] = sm[pidx(tau + t * ST0)];
     }
-    tile_inv<4, false>(x, itw, 1u, m);
+    tile_inv<4, false>(x, TileTw<4, false>(itw, 1u, 0u), m);
 #pragma unroll
     for (int t = 0; t < 16; t++) {
       uint64_t v = shoup_lazy(x[t], pc.ninv, pc.ninv_q, m);
@@ -478,7 +505,7 @@ __device__ __forceinline__ void stage_poly(uint64_t *sm, const uint64_t *__restr
 template <int LOGN>
 __device__ __forceinline__ void poly_forward(uint64_t *sm, const uint64_t *__restrict__ poly, int W, unsigned g,
                                              unsigned ginv, const PrimeConsts &pc, const Mod &m, uint64_t negW,
-                                             const ulonglong2 *__restrict__ tw) {
+                                             const Tw &tw) {
   typedef Cfg<LOGN> G;
   if constexpr (G::C == 1) {
     if (W == 1) stage_poly<LOGN, 1>(sm, poly, W, g, pc, m, negW);

@@ -19,7 +19,7 @@ k_ntt_fwd(const uint64_t *__restrict__ in, uint64_t *__restrict__ out, Tables T,
   const unsigned limb = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
   const unsigned d = d0 + limb % D;
   const Mod m = make_mod(T.primes[d].p);
-  const ulonglong2 *tw = T.tw + (size_t)d * G::N;
+  const Tw tw = make_tw(T, d, false);
   const uint64_t *src = in + (size_t)limb * G::N;
   if constexpr (G::C == 1) {
 #pragma unroll 8
@@ -50,7 +50,7 @@ k_ntt_inv(const uint64_t *__restrict__ in, uint64_t *__restrict__ out, Tables T,
   for (int i = threadIdx.x; i < G::M; i += G::THREADS) smem[pidx(i)] = HB_LD(&src[i]);
   __syncthreads();
   uint64_t *dst = out + (size_t)limb * G::N;
-  ntt_inverse<LOGN, true>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, T.itw + (size_t)d * G::N, pc, m);
+  ntt_inverse<LOGN, true>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
 }
 
 // =========================================================================================================
@@ -69,7 +69,7 @@ k_poly_ntt(const uint64_t *__restrict__ src, size_t poly_stride, int W, uint64_t
   const Mod m = make_mod(pc.p);
   const uint64_t negW = pc.p - T.pow64[(size_t)d * (T.WC + 1) + W];
   const uint64_t *poly = src + (size_t)q * poly_stride;
-  poly_forward<LOGN>(smem, poly, W, 1u, 1u, pc, m, negW, T.tw + (size_t)d * G::N);
+  poly_forward<LOGN>(smem, poly, W, 1u, 1u, pc, m, negW, make_tw(T, d, false));
   uint64_t *dst = out + ((size_t)q * D + d) * G::N + (size_t)chunk * G::M;
   for (int i = threadIdx.x; i < G::M; i += G::THREADS) dst[i] = canon(smem[pidx(i)], m);
 }
@@ -114,7 +114,7 @@ k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, unsigned 
   const Mod m = make_mod(pc.p);
   const uint64_t negW = pc.p - T.pow64[(size_t)d * (T.WC + 1) + W];
   const uint64_t *poly = src + (size_t)b * src_bstride;
-  poly_forward<LOGN>(smA, poly, W, g, ginv, pc, m, negW, T.tw + (size_t)d * G::N);
+  poly_forward<LOGN>(smA, poly, W, g, ginv, pc, m, negW, make_tw(T, d, false));
 #pragma unroll 1
   for (int h = 0; h < 2; h++) {
     const ulonglong2 *key = evk + ((size_t)h * dimevk + d) * G::N + (size_t)chunk * G::M;
@@ -125,7 +125,7 @@ k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, unsigned 
     }
     __syncthreads();
     uint64_t *dst = chat + (((size_t)b * 2 + h) * D + d) * G::N;
-    ntt_inverse<LOGN, false>(smB, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, T.itw + (size_t)d * G::N, pc, m);
+    ntt_inverse<LOGN, false>(smB, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
   }
 }
 
@@ -150,7 +150,7 @@ k_mulpt_limb(const uint64_t *__restrict__ ct, int W, const ulonglong2 *__restric
   const Mod m = make_mod(pc.p);
   const uint64_t negW = pc.p - T.pow64[(size_t)d * (T.WC + 1) + W];
   const uint64_t *poly = ct + (size_t)q * W * G::N;
-  poly_forward<LOGN>(smem, poly, W, 1u, 1u, pc, m, negW, T.tw + (size_t)d * G::N);
+  poly_forward<LOGN>(smem, poly, W, 1u, 1u, pc, m, negW, make_tw(T, d, false));
   const ulonglong2 *pt = pthat + (size_t)d * G::N + (size_t)chunk * G::M;
 #pragma unroll 4
   for (int i = threadIdx.x; i < G::M; i += G::THREADS) {
@@ -159,7 +159,7 @@ k_mulpt_limb(const uint64_t *__restrict__ ct, int W, const ulonglong2 *__restric
   }
   __syncthreads();
   uint64_t *dst = chat + ((size_t)q * D + d) * G::N;
-  ntt_inverse<LOGN, false>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, T.itw + (size_t)d * G::N, pc, m);
+  ntt_inverse<LOGN, false>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
 }
 
 // =========================================================================================================
@@ -195,7 +195,7 @@ k_mulacc_intt(const uint64_t *__restrict__ hat, size_t hat_jstride, const ulongl
   }
   __syncthreads();
   uint64_t *dst = chat + ((size_t)q * D + d) * G::N;
-  ntt_inverse<LOGN, false>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, T.itw + (size_t)d * G::N, pc, m);
+  ntt_inverse<LOGN, false>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
 }
 
 // =========================================================================================================
@@ -228,7 +228,7 @@ k_tensor_intt(const uint64_t *__restrict__ hatA, const uint64_t *__restrict__ ha
   }
   __syncthreads();
   uint64_t *dst = dhat + (((size_t)b * 3 + which) * D + d) * G::N;
-  ntt_inverse<LOGN, false>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, T.itw + (size_t)d * G::N, pc, m);
+  ntt_inverse<LOGN, false>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
 }
 
 // =========================================================================================================
@@ -304,15 +304,11 @@ __global__ void k_recon_smod(const uint64_t *__restrict__ chat, unsigned D, uint
 // first `dim` limbs (P = p_0...p_{dim-1}); see DESIGN.md "key-switch tail" for the proof.
 // add0/add1: optional polynomials (batch stride given) with the automorphism ginv applied on the fly.
 // =========================================================================================================
+// exact path for one coefficient: t = (x - R) P^-1 mod 2^(64 WK), roundup = [R > floor(P/2)]
 template <int WK, int WPK>
-__global__ void k_ks_finish(const uint64_t *__restrict__ chat, unsigned D, const uint64_t *__restrict__ add0,
-                            const uint64_t *__restrict__ add1, size_t add_bstride, int Wadd, unsigned ginv,
-                            uint64_t *__restrict__ out, int Wout, int k, Tables T, unsigned batch) {
+__device__ __forceinline__ void ks_exact(const uint64_t *__restrict__ limbs, unsigned D, const Tables &T, uint64_t (&t)[WK],
+                                      bool &roundup_out) {
   const unsigned N = T.N;
-  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= (size_t)batch * 2 * N) return;
-  const unsigned i = gid % N, h = (gid / N) & 1, b = gid / (2 * (size_t)N);
-  const uint64_t *limbs = chat + ((size_t)b * 2 + h) * D * N + i;
   uint64_t acc[WK];
   crt_low<WK>([&](unsigned d) { return limbs[(size_t)d * N]; }, D, T, acc);
   // ---- R = x mod P, exact ----
@@ -407,7 +403,6 @@ __global__ void k_ks_finish(const uint64_t *__restrict__ chat, unsigned D, const
       bw = nb;
     }
   }
-  uint64_t t[WK];
 #pragma unroll
   for (int w = 0; w < WK; w++) t[w] = 0;
 #pragma unroll
@@ -425,11 +420,17 @@ __global__ void k_ks_finish(const uint64_t *__restrict__ chat, unsigned D, const
       carry = hh;
     }
   }
-  // ---- + roundup + sigma(add_h)[i] ----
+  roundup_out = roundup;
+}
+
+// t + roundup + sigma(add_h)[i], centred mod 2^k, stored as Wout words
+template <int WK>
+__device__ __forceinline__ void ks_tail(uint64_t (&t)[WK], bool roundup, const uint64_t *__restrict__ add, size_t add_bstride,
+                                        int Wadd, unsigned ginv, unsigned N, unsigned b, unsigned h, unsigned i,
+                                        uint64_t *__restrict__ out, int Wout, int k) {
   uint64_t addw[WK];
 #pragma unroll
   for (int w = 0; w < WK; w++) addw[w] = 0;
-  const uint64_t *add = h ? add1 : add0;
   bool negate = false;
   if (add) {
     unsigned ip = (i * ginv) & (2 * N - 1);
@@ -465,7 +466,119 @@ __global__ void k_ks_finish(const uint64_t *__restrict__ chat, unsigned D, const
   uint64_t *o = out + ((size_t)b * 2 + h) * Wout * N + i;
 #pragma unroll
   for (int w = 0; w < WK; w++)
-    if (w < Wout) o[(size_t)w * N] = t[w];
+    if (w < Wout) HB_ST(&o[(size_t)w * N], t[w]);
+}
+
+// ---- fast path ------------------------------------------------------------------------------------------------
+// Same integers as ks_exact for small rings (D <= 8 limbs, dim <= 4, q_l <= 2^128): all constants travel as a kernel
+// parameter (constant bank, no table loads), the limb residues stay lazy (below 2p), and the two floors that ks_exact
+// settles with multiword comparisons -- v = round(sum y_d / p_d) and R/P = frac(sum z_e / p_e) -- are read off 56-bit
+// fixed-point sums whose error is below 2 D units.  When a sum lands within 64 units of a decision boundary (probability
+// about 2^-48 per coefficient, or an exactly zero R) the thread takes ks_exact instead, so the result is always exact.
+struct KsFast {
+  uint64_t p[8], mu[8], inv[8], invq[8], phat[8][2], PD[2];      // CRT over the D limbs (x mod 2^128)
+  uint64_t kinv[4], kinvq[4], kphat[4][2], kP[2], Pinv[2];       // R = x mod P over the first dim limbs; P^-1 mod 2^128
+  unsigned D, dim;
+};
+
+template <int WK>
+__device__ __forceinline__ void mac_low(uint64_t (&acc)[WK], uint64_t y, const uint64_t (&w)[2]) {   // acc += y * w (low WK words)
+  if (WK == 1) { acc[0] += y * w[0]; return; }
+  const uint64_t lo = y * w[0];
+  const uint64_t hi = __umul64hi(y, w[0]) + y * w[1];
+  acc[0] += lo;
+  acc[WK - 1] += hi + (acc[0] < lo);
+}
+
+// the whole exact tail for one coefficient, out of line so that its registers and arrays stay off the fast path
+template <int WK, int WPK>
+__device__ __noinline__ void ks_slow(const uint64_t *__restrict__ limbs, unsigned D, const Tables &T,
+                                     const uint64_t *__restrict__ add, size_t add_bstride, int Wadd, unsigned ginv, unsigned b,
+                                     unsigned h, unsigned i, uint64_t *__restrict__ out, int Wout, int k) {
+  uint64_t t[WK];
+  bool roundup;
+  ks_exact<WK, WPK>(limbs, D, T, t, roundup);
+  ks_tail<WK>(t, roundup, add, add_bstride, Wadd, ginv, T.N, b, h, i, out, Wout, k);
+}
+
+template <int WK, int WPK, int D, int DIM>
+__global__ void __launch_bounds__(128) k_ks_finish_fast(const uint64_t *__restrict__ chat, const __grid_constant__ KsFast F,
+                                                        const uint64_t *__restrict__ add0, const uint64_t *__restrict__ add1,
+                                                        size_t add_bstride, int Wadd, unsigned ginv, uint64_t *__restrict__ out,
+                                                        int Wout, int k, const __grid_constant__ Tables T, unsigned batch) {
+  static_assert(WK <= 2 && D <= 8 && DIM <= 4 && DIM <= D, "fast key-switch tail: q_l <= 2^128, D <= 8, dim <= 4");
+  const unsigned N = T.N;
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)batch * 2 * N) return;
+  const unsigned i = gid % N, h = (gid / N) & 1, b = gid / (2 * (size_t)N);
+  const uint64_t *limbs = chat + ((size_t)b * 2 + h) * D * N + i;
+  uint64_t a[D];
+#pragma unroll
+  for (int d = 0; d < D; d++) a[d] = HB_LD(&limbs[(size_t)d * N]);
+  uint64_t acc[WK], Rl[WK];
+#pragma unroll
+  for (int w = 0; w < WK; w++) { acc[w] = 0; Rl[w] = 0; }
+  uint64_t Fx = 0, Fr = 0;
+#pragma unroll
+  for (int d = 0; d < D; d++) {
+    const Mod m = make_mod(F.p[d]);
+    const uint64_t y = shoup_lazy(a[d], F.inv[d], F.invq[d], m);
+    Fx += __umul64hi(y, F.mu[d]);
+    mac_low<WK>(acc, y, F.phat[d]);
+  }
+#pragma unroll
+  for (int e = 0; e < DIM; e++) {
+    const Mod m = make_mod(F.p[e]);
+    const uint64_t z = shoup_lazy(a[e], F.kinv[e], F.kinvq[e], m);
+    Fr += __umul64hi(z, F.mu[e]);
+    mac_low<WK>(Rl, z, F.kphat[e]);
+  }
+  const uint64_t ONE = 1ULL << 56, HALF = 1ULL << 55, MASK = ONE - 1, MARGIN = 64;
+  const uint64_t fx = (Fx + HALF) & MASK, fr = Fr & MASK;
+  const bool unsure = fx < MARGIN || fx > ONE - MARGIN || fr < MARGIN || fr > ONE - MARGIN ||
+                      (fr > HALF - MARGIN && fr < HALF + MARGIN);
+  const uint64_t *add = h ? add1 : add0;
+  if (unsure) {
+    ks_slow<WK, WPK>(limbs, D, T, add, add_bstride, Wadd, ginv, b, h, i, out, Wout, k);
+    return;
+  }
+  const uint64_t v = (Fx + HALF) >> 56, v2 = Fr >> 56;
+  const bool roundup = fr > HALF;
+  // diff = (acc - v P_D) - (Rl - v2 P)  (mod 2^(64 WK));  t = diff * P^-1
+  uint64_t t[WK];
+  if (WK == 1) {
+    const uint64_t diff = acc[0] - v * F.PD[0] - Rl[0] + v2 * F.kP[0];
+    t[0] = diff * F.Pinv[0];
+  } else {
+    uint64_t dlt[WK], sub[WK];
+#pragma unroll
+    for (int w = 0; w < WK; w++) { dlt[w] = 0; sub[w] = 0; }
+    mac_low<WK>(dlt, v, F.PD);
+    mac_low<WK>(sub, v2, F.kP);
+    unsigned __int128 A = ((unsigned __int128)acc[WK - 1] << 64) | acc[0];
+    A -= ((unsigned __int128)dlt[WK - 1] << 64) | dlt[0];
+    A -= ((unsigned __int128)Rl[WK - 1] << 64) | Rl[0];
+    A += ((unsigned __int128)sub[WK - 1] << 64) | sub[0];
+    const uint64_t d0 = (uint64_t)A, d1 = (uint64_t)(A >> 64);
+    t[0] = d0 * F.Pinv[0];
+    t[WK - 1] = __umul64hi(d0, F.Pinv[0]) + d0 * F.Pinv[1] + d1 * F.Pinv[0];
+  }
+  ks_tail<WK>(t, roundup, add, add_bstride, Wadd, ginv, N, b, h, i, out, Wout, k);
+}
+
+template <int WK, int WPK>
+__global__ void k_ks_finish(const uint64_t *__restrict__ chat, unsigned D, const uint64_t *__restrict__ add0,
+                            const uint64_t *__restrict__ add1, size_t add_bstride, int Wadd, unsigned ginv,
+                            uint64_t *__restrict__ out, int Wout, int k, Tables T, unsigned batch) {
+  const unsigned N = T.N;
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)batch * 2 * N) return;
+  const unsigned i = gid % N, h = (gid / N) & 1, b = gid / (2 * (size_t)N);
+  const uint64_t *limbs = chat + ((size_t)b * 2 + h) * D * N + i;
+  uint64_t t[WK];
+  bool roundup;
+  ks_exact<WK, WPK>(limbs, D, T, t, roundup);
+  ks_tail<WK>(t, roundup, h ? add1 : add0, add_bstride, Wadd, ginv, N, b, h, i, out, Wout, k);
 }
 
 // =========================================================================================================

@@ -67,6 +67,18 @@ uint64_t least_generator(uint64_t p) {
 
 uint64_t shoup_quotient(uint64_t w, uint64_t p) { return (uint64_t)((((u128)w) << 64) / p); }
 
+// The device splits the stages [first, logn) into passes of R = ceil(rem / ceil(rem / 4)) stages (hb_dev.cuh PassSize);
+// this returns the R of the last one (the stride-1 pass).
+unsigned last_pass_stages(unsigned logn, unsigned first) {
+  unsigned s = first, r = 0;
+  while (s < logn) {
+    const unsigned rem = logn - s, np = (rem + 3) / 4;
+    r = (rem + np - 1) / np;
+    s += r;
+  }
+  return r;
+}
+
 unsigned security_logq_bound(unsigned logn) {  // 128-bit classical column, precomp.c:57-64
   switch (logn) {
     case 10: return 27;
@@ -116,6 +128,14 @@ std::string build_tables(HostTables &t, unsigned logn, unsigned logq, unsigned s
   t.tw.assign((size_t)t.dimub * N * 2, 0);
   t.itw.assign((size_t)t.dimub * N * 2, 0);
   t.pow64.assign((size_t)t.dimub * (t.WC + 1), 0);
+  // lane-transposed copy for the stride-1 pass: R stages, 2^S tiles (S = logn - R)
+  t.last_R = last_pass_stages(logn, 0);
+  if (logn > 4 && last_pass_stages(logn, 4) != t.last_R) return "internal: the two pass chains disagree on the last pass";
+  const unsigned trR = t.last_R, trS = logn - trR, trSlots = (1u << trR) - 1;
+  const unsigned trBlocks = ((1u << trS) + 31) / 32;
+  t.tr_stride = trBlocks * trSlots * 32;
+  t.tw_tr.assign((size_t)t.dimub * t.tr_stride * 2, 0);
+  t.itw_tr.assign((size_t)t.dimub * t.tr_stride * 2, 0);
   uint64_t p = (1ULL << LOGP) + 1;
   for (unsigned d = 0; d < t.dimub; d++) {
     do { p += 2ULL * N; } while (!is_prime_u64(p));
@@ -140,6 +160,15 @@ std::string build_tables(HostTables &t, unsigned logn, unsigned logq, unsigned s
       pw = mulmod(pw, c.root, p);
       pwi = mulmod(pwi, rootinv, p);
     }
+    uint64_t *ttr = &t.tw_tr[(size_t)d * t.tr_stride * 2], *itr = &t.itw_tr[(size_t)d * t.tr_stride * 2];
+    for (unsigned K = 0; K < (1u << trS); K++)
+      for (unsigned e = 0; e < trR; e++)
+        for (unsigned u = 0; u < (1u << e); u++) {
+          const size_t src = ((((size_t)1 << trS) + K) << e) + u;
+          const size_t dst = ((size_t)(K >> 5) * trSlots + ((1u << e) - 1) + u) * 32 + (K & 31);
+          ttr[2 * dst] = tw[2 * src];   ttr[2 * dst + 1] = tw[2 * src + 1];
+          itr[2 * dst] = itw[2 * src];  itr[2 * dst + 1] = itw[2 * src + 1];
+        }
     uint64_t r = 1;
     for (unsigned w = 0; w <= t.WC; w++) { t.pow64[(size_t)d * (t.WC + 1) + w] = r; r = mulmod(r, c.r64, p); }
   }

@@ -34,6 +34,9 @@ struct HostTables {
   std::vector<unsigned> logq_l;          // [L+1]
   std::vector<PrimeConsts> primes;       // [dimub]
   std::vector<uint64_t> tw, itw;         // [dimub][N][2]: (w, floor(w*2^64/p)), index = bit-reversed exponent
+  // the stride-1 NTT pass's twiddles, lane-transposed (hb_dev.cuh struct Tw): [dimub][tr_stride][2]
+  std::vector<uint64_t> tw_tr, itw_tr;
+  unsigned tr_stride = 0, last_R = 0;
   std::vector<uint64_t> pow64;           // [dimub][WC+1]: 2^(64*w) mod p
   std::vector<uint64_t> crt_inv, crt_inv_q;  // [dimub+1][dimub]
   std::vector<uint64_t> crt_phat;        // [dimub+1][dimub][WC]
@@ -50,6 +53,7 @@ uint64_t powmod(uint64_t a, uint64_t e, uint64_t m);
 bool is_prime_u64(uint64_t n);
 uint64_t least_generator(uint64_t p);
 uint64_t shoup_quotient(uint64_t w, uint64_t p);
+unsigned last_pass_stages(unsigned logn, unsigned first);   // stages of the stride-1 NTT pass (device PassSize chain)
 unsigned security_logq_bound(unsigned logn);
 
 // Returns empty string on success, otherwise the reason the parameters are rejected

@@ -85,10 +85,11 @@ def main():
         Kb = np.zeros((S, S), dtype=np.complex128)
         Ka[:8, :3] = rng.standard_normal((8, 3))
         Kb[:8, :2] = rng.standard_normal((8, 2))
-        base = rand_ct(rng, min(a.batch, 64), W, n, k)
-        reps = (a.batch + base.shape[0] - 1) // base.shape[0]
-        words = np.concatenate([base] * reps)[: a.batch]
-        cts = [eng.ct(words, l) for _ in range(4)]
+        cts = []
+        for _ in range(4):          # four DIFFERENT inputs: xhat - xr must not be the zero ciphertext
+            base = rand_ct(rng, min(a.batch, 64), W, n, k)
+            reps = (a.batch + base.shape[0] - 1) // base.shape[0]
+            cts.append(eng.ct(np.concatenate([base] * reps)[: a.batch], l))
         out = eng.ct(batch=a.batch)
         eng.ctr_hempc_eval(Ka, Kb, *cts, keys, out=out)      # warm (builds the gemv plans)
         eng.sync()

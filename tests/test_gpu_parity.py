@@ -112,6 +112,21 @@ def test_rot_all_rotations(cfgA, l):
             assert np.array_equal(got[bi], want), (l, r, bi)
 
 
+def test_rot_zero_c1_takes_exact_tail(cfgA):
+    """c1 = 0 makes every key-switch product exactly 0 = 0 mod P: the fixed-point fast tail cannot decide R/P there and
+    must fall back to the multiword path (k_ks_finish_fast -> ks_exact); the result is still the reference's."""
+    ref, eng, keys = cfgA["ref"], cfgA["eng"], cfgA["keys"]
+    rng = np.random.default_rng(77)
+    l = 2
+    a = random_ct_words(rng, 2, eng.words(l), eng.n, eng.logq(l))
+    a[:, 1] = 0
+    a[1, 0, :, ::3] = 0
+    got = eng.he_rot(eng.ct(a, l), 3, keys).download()
+    for bi in range(2):
+        want = ref.ct_to_words(ref.rot(_ref_ct(ref, a[bi], l), 3, cfgA["rk"]))
+        assert np.array_equal(got[bi], want)
+
+
 def test_mulpt(cfgA):
     ref, eng = cfgA["ref"], cfgA["eng"]
     rng = np.random.default_rng(31)
