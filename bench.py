@@ -145,13 +145,18 @@ def pinned_array(eng, shape):
 # algorithmic bytes per launch, config A, batch B instances per launch
 def algorithmic_bytes(kernel: str, B: int, n: int, W: int, D_ks: int, D_pt: int):
     ct_poly = n * W * 8
+    hat = B * 2 * D_pt * n * 8
     table = {
         # one key switch: read d0,d1 + write c0,c1 + keys shared over the batch (2*D*N*8 / B per unit)
         "k_ks_limb": B * (2 * ct_poly + 2 * ct_poly) + 2 * D_ks * n * 8,
         "k_ks_finish": B * (2 * ct_poly + 2 * ct_poly) + 2 * D_ks * n * 8,
+        "k_ks_finish_fast": B * (2 * ct_poly + 2 * ct_poly) + 2 * D_ks * n * 8,
         # one ct x pt: ct in + ct out + plaintext (shared)
         "k_mulpt_limb": B * (2 * ct_poly + 2 * ct_poly) + D_pt * n * 8,
         "k_recon_smod": B * (2 * ct_poly + 2 * ct_poly) + D_pt * n * 8,
+        # memoised gemv: rotated ct in -> NTT limbs out; n1 limb sets in -> one limb set out
+        "k_poly_ntt": B * 2 * ct_poly + hat,
+        "k_mulacc_intt": 4 * hat + hat,
         "k_ct_addsub": B * 3 * 2 * ct_poly,
         "k_ct_rescale": B * 2 * 2 * ct_poly,
     }
