@@ -176,8 +176,10 @@ def run_ours(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from hectr_b200.sharding import gather_results, shard_range
     total = args.instances
-    per = total // world
+    lo, hi = shard_range(total, rank, world)        # contiguous block of controller instances for this GPU
+    per = hi - lo
     assert per * world == total, "instances must divide by the number of GPUs"
 
     eng = Engine(PARAMS["logn"], PARAMS["logq"], PARAMS["slots"], PARAMS["logDelta"], device=local)
@@ -202,14 +204,13 @@ def run_ours(args):
     for nm in names:
         lib.hb_ct_upload(ctx, C.byref(dev[nm].h), host[nm].ctypes.data_as(C.c_void_p), l, Delta, 1.0)
     up = eng.ct(batch=per)
-    gather_in = torch.empty(per * 2 * Wout * n, dtype=torch.int64, device="cuda")
-    gather_out = torch.empty(world * per * 2 * Wout * n, dtype=torch.int64, device="cuda") if world > 1 else None
+    gather_in = torch.empty((per, 2 * Wout * n), dtype=torch.int64, device="cuda")
 
     def step():
         eng.ctr_hempc_eval(Ka, Kb, dev["xhat"], dev["xr"], dev["uhat"], dev["ur"], keys, out=up)
         if world > 1:      # the only collective: gather the result ciphertexts (north_star)
             lib.hb_ct_export(ctx, C.byref(up.h), C.c_void_p(gather_in.data_ptr()))
-            dist.all_gather_into_tensor(gather_out, gather_in)
+            gather_results(gather_in, total)
 
     def barrier():
         torch.cuda.synchronize()

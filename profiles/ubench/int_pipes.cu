@@ -28,6 +28,12 @@ __global__ void k(uint32_t *out, uint32_t s0, uint32_t s1) {
       if (OP == 7) { asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(w[i]) : "r"(a[i]), "r"(b[i])); asm volatile("add.u32 %0, %0, %1;" : "+r"(b[i]) : "r"(s0)); }  // WIDE + IADD3 pair
       if (OP == 8) asm volatile("shf.r.wrap.b32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b[i]), "r"(s1));        // SHF
       if (OP == 9) asm volatile("mul.wide.u32 %0, %1, %2;" : "=l"(w[i]) : "r"(a[i]), "r"((uint32_t)w[i]));   // IMAD.WIDE no acc (dependent via lo word)
+      if (OP == 10) { double d = __longlong_as_double(w[i]); asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(d) : "d"(1.0000001), "d"(0.5)); w[i] = __double_as_longlong(d); }   // DFMA
+      if (OP == 11) { double d = __longlong_as_double(w[i]); asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(d) : "d"(1.0000001), "d"(0.5)); w[i] = __double_as_longlong(d);
+                      asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b[i]), "r"(s1)); }        // DFMA + IMAD pair
+      if (OP == 12) { asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(w[i]) : "r"(a[i]), "r"(b[i])); asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b[i]), "r"(s1)); }  // WIDE + IMAD pair
+      if (OP == 13) { asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b[i]), "r"(s1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(b[i]) : "r"(s0)); asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(b[i]) : "r"(a[i]), "r"(s1)); }  // IMAD + 2 ALU
+      if (OP == 14) { asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b[i]), "r"(s1)); float f = __uint_as_float(b[i]); asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(f) : "f"(1.0001f), "f"(0.5f)); b[i] = __float_as_uint(f); }  // IMAD + FFMA pair (heavy + lite?)
     }
   }
   long long t1 = clock64();
@@ -74,6 +80,11 @@ int main() {
     run<8>("SHF", 1, c, 512);
     run<6>("IMAD+IADD3", 2, c, 512);
     run<7>("WIDE+IADD3", 2, c, 512);
+    run<10>("DFMA", 1, c, 512);
+    run<11>("DFMA+IMAD", 2, c, 512);
+    run<12>("WIDE+IMAD", 2, c, 512);
+    run<13>("IMAD+IADD3+LOP3", 3, c, 512);
+    run<14>("IMAD+FFMA", 2, c, 512);
   }
   return 0;
 }
