@@ -41,8 +41,10 @@ def test_small_tables(small, gold):
     assert list(map(int, eng.primes())) == [int(v) for v in gold["primes"]]
     i = eng.info
     assert [i.L, i.dim, i.dimevk, i.dimub] == [int(v) for v in gold["derived"]]
-    assert np.array_equal(eng.twiddles(0), gold["zetas0"])
-    assert np.array_equal(eng.twiddles(0, inverse=True), gold["zetas_inv0"])
+    # the engine keeps plain powers zeta^brv(i); the reference stores them in Montgomery form, * 2^64 mod p (precomp.c:259-260)
+    p0 = int(gold["primes"][0])
+    assert [int(v) * (1 << 64) % p0 for v in eng.twiddles(0)] == [int(v) for v in gold["zetas0"]]
+    assert [int(v) * (1 << 64) % p0 for v in eng.twiddles(0, inverse=True)] == [int(v) for v in gold["zetas_inv0"]]
 
 
 def test_small_transforms(small, gold):
