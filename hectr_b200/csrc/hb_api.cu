@@ -69,6 +69,10 @@ struct hb_ctx {
   std::multimap<size_t, uint64_t *> pool;
   std::map<uint64_t *, size_t> live;
   hb_ring *ring = nullptr;
+  std::map<unsigned, uint16_t *> perms;   // g -> device perm_g[N] (k_ks_baby)
+  uint64_t *wsD = nullptr;
+  size_t wsD_bytes = 0;
+  bool no_hoist = false;            // HB_GEMV_NOHOIST=1: one key-switch launch per baby rotation (A/B timing, tests)
   std::vector<GemvPlan> plans;
   std::vector<uint64_t> enc_host;   // [WC][N] scratch for hb_he_ecd / gemv plans
 };
@@ -159,6 +163,12 @@ struct Launch {
     launch(c, "k_ks_limb", hbdev::k_ks_limb<LOGN>, (unsigned)((size_t)batch * D * G::C), G::THREADS, 2 * G::SMEM_BYTES, G::C, src, bstride, W,
            g, ginv, evk, c->ht.dimevk, chat, c->dt, D);
   }
+  static void ks_baby(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hbdev::BabySet &S, uint64_t *chat, size_t jstride,
+                      unsigned D, unsigned batch) {
+    want_smem(hbdev::k_ks_baby<LOGN>, 2 * G::SMEM_BYTES);
+    launch(c, "k_ks_baby", hbdev::k_ks_baby<LOGN>, (unsigned)((size_t)batch * D * G::C), G::THREADS, 2 * G::SMEM_BYTES, G::C, src, bstride, W,
+           S, c->ht.dimevk, chat, jstride, c->dt, D);
+  }
   static void mulpt_limb(hb_ctx *c, const uint64_t *ct, int W, const ulonglong2 *pthat, uint64_t *chat, unsigned D, unsigned batch) {
     want_smem(hbdev::k_mulpt_limb<LOGN>, G::SMEM_BYTES);
     launch(c, "k_mulpt_limb", hbdev::k_mulpt_limb<LOGN>, (unsigned)((size_t)batch * 2 * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, ct, W, pthat,
@@ -197,6 +207,12 @@ static void do_ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, un
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
 }
+static void do_ks_baby(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hbdev::BabySet &S, uint64_t *chat, size_t jstride,
+                       unsigned D, unsigned batch) {
+#define X(L) case L: Launch<L>::ks_baby(c, src, bstride, W, S, chat, jstride, D, batch); break;
+  switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
+#undef X
+}
 static void do_mulpt_limb(hb_ctx *c, const uint64_t *ct, int W, const ulonglong2 *pthat, uint64_t *chat, unsigned D, unsigned batch) {
 #define X(L) case L: Launch<L>::mulpt_limb(c, ct, W, pthat, chat, D, batch); break;
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
@@ -215,21 +231,26 @@ static void do_tensor_intt(hb_ctx *c, const uint64_t *hatA, const uint64_t *hatB
 }
 
 // canonical limbs[j][N] (prime j % D) -> Shoup pairs
-static void do_shoup_prep(hb_ctx *c, const uint64_t *in, ulonglong2 *out, unsigned D, size_t nlimbs) {
+// scale: 0 plain, 1 times N^-1, 2 times N^-1 (P_Dw/p_d)^-1 (see k_shoup_prep)
+static void do_shoup_prep(hb_ctx *c, const uint64_t *in, ulonglong2 *out, unsigned D, size_t nlimbs, int scale, unsigned Dw) {
   const size_t total = nlimbs * c->ht.N;
-  launch(c, "k_shoup_prep", hbdev::k_shoup_prep, (unsigned)((total + 255) / 256), 256, 0, 1, in, out, c->dt, D, nlimbs);
+  launch(c, "k_shoup_prep", hbdev::k_shoup_prep, (unsigned)((total + 255) / 256), 256, 0, 1, in, out, c->dt, D, nlimbs, scale, Dw);
 }
 
 static int wk_class(unsigned wk) { return wk <= 1 ? 1 : wk <= 2 ? 2 : wk <= 4 ? 4 : wk <= 8 ? 8 : 16; }
 static int wp_class(unsigned wp) { return wp <= 4 ? 4 : wp <= 8 ? 8 : wp <= 12 ? 12 : 20; }
 
-static void do_recon_smod(hb_ctx *c, const uint64_t *chat, unsigned D, uint64_t *out, int Wout, int k, size_t npoly) {
+// pre: the limbs already carry the CRT weight (P_D/p_d)^-1 (k_mulpt_limb, k_mulacc_intt)
+static void do_recon_smod(hb_ctx *c, const uint64_t *chat, unsigned D, uint64_t *out, int Wout, int k, size_t npoly, bool pre) {
   const unsigned threads = 128;
   const size_t total = npoly * c->ht.N;
   const unsigned grid = (unsigned)((total + threads - 1) / threads);
   const unsigned wk = (k + 63) / 64;
   switch (wk_class(wk)) {
-#define X(WKC) case WKC: launch(c, "k_recon_smod", hbdev::k_recon_smod<WKC>, grid, threads, 0, 1, chat, D, out, Wout, k, c->dt, (unsigned)npoly); break;
+#define X(WKC) case WKC:                                                                                                           \
+    if (pre) launch(c, "k_recon_smod", hbdev::k_recon_smod<WKC, true>, grid, threads, 0, 1, chat, D, out, Wout, k, c->dt, (unsigned)npoly);  \
+    else launch(c, "k_recon_smod", hbdev::k_recon_smod<WKC, false>, grid, threads, 0, 1, chat, D, out, Wout, k, c->dt, (unsigned)npoly);     \
+    break;
     X(1) X(2) X(4) X(8) X(16)
 #undef X
   }
@@ -259,12 +280,11 @@ static void do_ks_finish(hb_ctx *c, const uint64_t *chat, unsigned D, const uint
     F.D = D; F.dim = h.dim;
     for (unsigned d = 0; d < D; d++) {
       F.p[d] = h.primes[d].p; F.mu[d] = h.primes[d].mu;
-      F.inv[d] = h.crt_inv[(size_t)D * h.dimub + d]; F.invq[d] = h.crt_inv_q[(size_t)D * h.dimub + d];
       for (unsigned w = 0; w < 2 && w < h.WC; w++) F.phat[d][w] = h.crt_phat[((size_t)D * h.dimub + d) * h.WC + w];
     }
     for (unsigned w = 0; w < 2 && w < h.WC; w++) { F.PD[w] = h.crt_P[(size_t)D * h.WC + w]; F.Pinv[w] = h.ks_Pinv[w]; }
     for (unsigned e = 0; e < h.dim; e++) {
-      F.kinv[e] = h.ks_inv[e]; F.kinvq[e] = h.ks_inv_q[e];
+      F.kinv[e] = h.ks_z[((size_t)D * h.dim + e) * 2]; F.kinvq[e] = h.ks_z[((size_t)D * h.dim + e) * 2 + 1];
       for (unsigned w = 0; w < 2 && w < h.WP; w++) F.kphat[e][w] = h.ks_phat[(size_t)e * h.WP + w];
     }
     for (unsigned w = 0; w < 2 && w < h.WP; w++) F.kP[w] = h.ks_P[w];
@@ -346,12 +366,16 @@ extern "C" hb_ctx *hb_ctx_create(unsigned logn, unsigned logq, unsigned slots, u
   t.ks_P = upload_vec(ctx, h.ks_P);
   t.ks_Ph = upload_vec(ctx, h.ks_Ph);
   t.ks_Pinv = upload_vec(ctx, h.ks_Pinv);
+  t.dec_s = (const ulonglong2 *)upload_vec(ctx, h.dec_s);
+  t.ks_z = (const ulonglong2 *)upload_vec(ctx, h.ks_z);
   t.N = h.N; t.logn = h.logn; t.dimub = h.dimub; t.WC = h.WC; t.WP = h.WP; t.dim = h.dim;
   {
     const char *e = getenv("HB_GEMV_STEPWISE");
     ctx->stepwise = e && *e && *e != '0';
     e = getenv("HB_KS_EXACT");
     ctx->exact_tail = e && *e && *e != '0';
+    e = getenv("HB_GEMV_NOHOIST");
+    ctx->no_hoist = e && *e && *e != '0';
   }
   ctx->ring = hb_ring_create(logn);
   ctx->enc_host.assign((size_t)h.WC * h.N, 0);
@@ -372,6 +396,8 @@ extern "C" void hb_ctx_destroy(hb_ctx *ctx) {
   cudaFree(ctx->wsA);
   cudaFree(ctx->wsB);
   cudaFree(ctx->wsC);
+  cudaFree(ctx->wsD);
+  for (auto &kv : ctx->perms) cudaFree(kv.second);
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->own_stream);
@@ -617,7 +643,7 @@ extern "C" void hb_evk_upload(hb_ctx *ctx, hb_evk *evk, const uint64_t *p0, cons
   evk->p = (uint64_t *)hb_dev_alloc(ctx, 2 * half * 16);
   CUDA_OK(cudaMemcpyAsync(raw, p0, half * 8, cudaMemcpyHostToDevice, ctx->stream));
   CUDA_OK(cudaMemcpyAsync(raw + half, p1, half * 8, cudaMemcpyHostToDevice, ctx->stream));
-  do_shoup_prep(ctx, raw, (ulonglong2 *)evk->p, ctx->ht.dimevk, (size_t)2 * ctx->ht.dimevk);
+  do_shoup_prep(ctx, raw, (ulonglong2 *)evk->p, ctx->ht.dimevk, (size_t)2 * ctx->ht.dimevk, 1, 0);   // key * N^-1
   hb_dev_free(ctx, raw);   // synchronises
 }
 extern "C" void hb_evk_free(hb_ctx *ctx, hb_evk *evk) { hb_dev_free(ctx, evk->p); evk->p = nullptr; }
@@ -701,7 +727,7 @@ static void mulpt_with_hat(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const ulon
   const double nu = src->nu, B = src->B;
   dst->nu = nu * ptnu;
   dst->B = B * ptnu;
-  do_recon_smod(ctx, chat, D, dst->words, W, k, (size_t)src->batch * 2);
+  do_recon_smod(ctx, chat, D, dst->words, W, k, (size_t)src->batch * 2, true);
 }
 
 extern "C" void hb_he_mulpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt) {
@@ -713,7 +739,7 @@ extern "C" void hb_he_mulpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_
   uint64_t *raw = ws_get(ctx, ctx->wsB, ctx->wsB_bytes, hatw * 24);
   ulonglong2 *pthat = (ulonglong2 *)(raw + hatw);
   do_poly_ntt(ctx, pt->words, (size_t)ctx->ht.WC * ctx->ht.N, ctx->ht.WC, raw, D, 1);
-  do_shoup_prep(ctx, raw, pthat, D, D);
+  do_shoup_prep(ctx, raw, pthat, D, D, 2, D);
   mulpt_with_hat(ctx, dst, src, pthat, D, pt->nu);
 }
 
@@ -780,7 +806,7 @@ extern "C" void hb_he_mul(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b
   do_poly_ntt(ctx, a->words, polyw, W, hatA, Dm, (size_t)batch * 2);
   do_poly_ntt(ctx, b->words, polyw, W, hatB, Dm, (size_t)batch * 2);
   do_tensor_intt(ctx, hatA, hatB, dhat, Dm, batch);
-  do_recon_smod(ctx, dhat, Dm, dpoly, W, k, (size_t)batch * 3);      // d0,d1,d2 mod q_l  (he-mult.c:140-142)
+  do_recon_smod(ctx, dhat, Dm, dpoly, W, k, (size_t)batch * 3, false);      // d0,d1,d2 mod q_l  (he-mult.c:140-142)
   // relinearise d2 with rlk, add d0 and d1 (he-mult.c:40-85)
   uint64_t *chat = wsA;
   do_ks_limb(ctx, dpoly + 2 * polyw, 3 * polyw, W, 1u, 1u, (const ulonglong2 *)rlk->p, chat, Dk, batch);
@@ -872,7 +898,7 @@ static const GemvPlan &gemv_plan(hb_ctx *ctx, const double *A, unsigned l) {
   uint64_t *raw = (uint64_t *)hb_dev_alloc(ctx, (size_t)S * plan.D * h.N * 8);
   plan.pthat = (ulonglong2 *)hb_dev_alloc(ctx, (size_t)S * plan.D * h.N * 16);
   do_poly_ntt(ctx, dpt, ptw, h.WC, raw, plan.D, S);
-  do_shoup_prep(ctx, raw, plan.pthat, plan.D, (size_t)S * plan.D);
+  do_shoup_prep(ctx, raw, plan.pthat, plan.D, (size_t)S * plan.D, 2, plan.D);
   CUDA_OK(cudaStreamSynchronize(ctx->stream));
   CUDA_OK(cudaFree(dpt));
   CUDA_OK(cudaFree(raw));
@@ -908,11 +934,29 @@ static void gemv_stepwise(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const h
   hb_ct_free(ctx, &rot);
 }
 
+// perm_g[i] = brv(((2 brv(i) + 1) g mod 2N - 1) / 2): where ntt(sigma_g a) reads ntt(a) (k_ks_baby)
+static const uint16_t *perm_table(hb_ctx *ctx, unsigned g) {
+  auto it = ctx->perms.find(g);
+  if (it != ctx->perms.end()) return it->second;
+  const unsigned N = ctx->ht.N, logn = ctx->ht.logn;
+  std::vector<uint16_t> h(N);
+  auto brv = [&](unsigned x) { unsigned r = 0; for (unsigned b = 0; b < logn; b++) r |= ((x >> b) & 1u) << (logn - 1 - b); return r; };
+  for (unsigned i = 0; i < N; i++) {
+    const unsigned e = (unsigned)(((uint64_t)(2 * brv(i) + 1) * g) & (2 * N - 1));
+    h[i] = (uint16_t)brv((e - 1) / 2);
+  }
+  uint16_t *d = (uint16_t *)hb_dev_alloc(ctx, (size_t)N * 2);
+  CUDA_OK(cudaMemcpyAsync(d, h.data(), (size_t)N * 2, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  ctx->perms[g] = d;
+  return d;
+}
+
 // Same ciphertext, fewer transforms.  The reference recomputes he_rot(ct, j) for every giant step i although it does not
-// depend on i (he-algo.c:66-68): here the n1 baby rotations are key-switched once, transformed once
-// (hat_j = ntt(decompose(rot_j))), and each giant step sums its n1 diagonal products in the NTT domain before one
-// inverse transform and one reconstruction (k_mulacc_intt).  Every he_swk rounding of the reference is still performed
-// on the same integers, so the result is bit-identical (SURVEY H4 forbids sharing key-switch decompositions, not this).
+// depend on i (he-algo.c:66-68): here the n1 baby rotations are key-switched once -- from ONE decomposition and forward
+// transform of ct.c1 (k_ks_baby) --, transformed once (hat_j = ntt(decompose(rot_j))), and each giant step sums its n1
+// diagonal products in the NTT domain before one inverse transform and one reconstruction (k_mulacc_intt).  Every
+// he_swk rounding of the reference is still performed on the same integers, so the result is bit-identical.
 static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_ct *ct, const hb_evk *rk, unsigned n1, unsigned n2) {
   const hb::HostTables &h = ctx->ht;
   const double Delta = std::ldexp(1.0, (int)h.logDelta);
@@ -925,16 +969,41 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
   hb_ct_alloc(ctx, &inner, batch);
   hb_ct_alloc(ctx, &outer, batch);
   hb_ct_alloc(ctx, &rot, batch);
-  for (unsigned j = 0; j < n1; j++) {
-    hb_ct_copy(ctx, &rot, ct);
-    hb_he_rot(ctx, &rot, (int)j, rk);
-    do_poly_ntt(ctx, rot.words, polyw, W, hat + (size_t)j * jstride, D, (size_t)batch * 2);
+  if (ctx->no_hoist || N > 65536) {
+    for (unsigned j = 0; j < n1; j++) {
+      hb_ct_copy(ctx, &rot, ct);
+      hb_he_rot(ctx, &rot, (int)j, rk);
+      do_poly_ntt(ctx, rot.words, polyw, W, hat + (size_t)j * jstride, D, (size_t)batch * 2);
+    }
+  } else {
+    const unsigned Dk = hb::dim_keyswitch(h, l);
+    if (Dk > h.dimevk || Dk > h.dimub) hb_die("hb_he_gemv: needs %u limbs but keys hold %u and the prime chain %u", Dk, h.dimevk, h.dimub);
+    const size_t bstride = (size_t)2 * polyw, cstride = (size_t)batch * 2 * Dk * N;
+    uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, (size_t)n1 * cstride * 8);
+    uint64_t *rots = ws_get(ctx, ctx->wsD, ctx->wsD_bytes, (size_t)n1 * batch * bstride * 8);
+    std::vector<unsigned> ginv(n1);
+    for (unsigned j0 = 0; j0 < n1; j0 += 4) {
+      hbdev::BabySet S;
+      memset(&S, 0, sizeof S);
+      S.nj = n1 - j0 < 4 ? n1 - j0 : 4;
+      for (unsigned t = 0; t < S.nj; t++) {
+        const unsigned j = j0 + t;
+        if (!rk[j].p) hb_die("hb_he_gemv: rotation key %u is not loaded", j);
+        ginv[j] = pow5_inv_mod_2n(ctx, j);
+        S.evk[t] = (const ulonglong2 *)rk[j].p;
+        S.perm[t] = perm_table(ctx, inv_odd_mod_2n(ctx, ginv[j]));
+      }
+      do_ks_baby(ctx, ct->words + polyw, bstride, W, S, chat + (size_t)j0 * cstride, cstride, Dk, batch);
+    }
+    for (unsigned j = 0; j < n1; j++)     // tails: c0 = rdiv(.) + sigma_j(ct.c0), c1 = rdiv(.)   (he-automorphism.c:68-76)
+      do_ks_finish(ctx, chat + (size_t)j * cstride, Dk, ct->words, nullptr, bstride, W, ginv[j], rots + (size_t)j * batch * bstride, W, k, batch);
+    do_poly_ntt(ctx, rots, polyw, W, hat, D, (size_t)n1 * batch * 2);
   }
   for (unsigned i = 0; i < n2; i++) {
     const unsigned shift = i * n1;
     uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, jstride * 8);
     do_mulacc_intt(ctx, hat, jstride, plan.pthat + (size_t)shift * D * N, n1, chat, D, batch);
-    do_recon_smod(ctx, chat, D, inner.words, W, k, (size_t)batch * 2);
+    do_recon_smod(ctx, chat, D, inner.words, W, k, (size_t)batch * 2, true);
     inner.l = l;
     for (unsigned j = 0; j < n1; j++) {          // metadata exactly as he_mulpt / he_add update it
       const double nu = ct->nu * Delta, B = ct->B * Delta;
@@ -1033,7 +1102,7 @@ extern "C" void hb_poly_ntt(hb_ctx *ctx, const uint64_t *polys, unsigned W, size
 extern "C" void hb_rns2words(hb_ctx *ctx, const uint64_t *limbs, size_t npoly, unsigned D, unsigned k, unsigned Wout, uint64_t *out) {
   check_primes(ctx, 0, D, "hb_rns2words");
   if (k == 0 || k > 64 * ctx->ht.WC) hb_die("hb_rns2words: modulus 2^%u outside (0, 2^%u]", k, 64 * ctx->ht.WC);
-  if (npoly) do_recon_smod(ctx, limbs, D, out, (int)Wout, (int)k, npoly);
+  if (npoly) do_recon_smod(ctx, limbs, D, out, (int)Wout, (int)k, npoly, false);
 }
 extern "C" void hb_poly_rot(hb_ctx *ctx, const uint64_t *polys, unsigned W, size_t npoly, int rot, uint64_t *out) {
   const unsigned ginv = rot < 0 ? 2 * ctx->ht.N - 1 : pow5_inv_mod_2n(ctx, (unsigned)rot);

@@ -56,6 +56,8 @@ struct Tables {  // device pointers, passed by value
   const uint64_t *ks_phat;     // [dim][WP]
   const uint64_t *ks_P, *ks_Ph;         // [WP]
   const uint64_t *ks_Pinv;     // [WC]
+  const ulonglong2 *dec_s;     // [dimub+1][dimub][WC+1]  word weights of the scaled decomposition (hb_tables.hpp)
+  const ulonglong2 *ks_z;      // [dimub+1][dim]
   unsigned N, logn, dimub, WC, WP, dim;
 };
 
@@ -418,8 +420,11 @@ __device__ __forceinline__ void ntt_forward_resident(uint64_t *sm, const Tw &tw,
 }
 
 // Inverse transform of one limb held in the cluster's shared memory (values below 2p, bit-reversed order);
-// store(gi, v) receives natural-order coefficient gi, already scaled by N^-1, in [0,2p) -- canonical [0,p) when CANON.
-template <int LOGN, bool CANON, class Store>
+// store(gi, v) receives natural-order coefficient gi:
+//   INV_LAZY   scaled by N^-1, in [0,2p)        INV_CANON  scaled by N^-1, canonical [0,p)
+//   INV_RAW    NOT scaled (the caller folded N^-1 into a fixed multiplicand beforehand), folded into (0,2p)
+enum { INV_LAZY = 0, INV_CANON = 1, INV_RAW = 2 };
+template <int LOGN, int MODE, class Store>
 __device__ __forceinline__ void ntt_inverse(uint64_t *sm, Store store, const Tw &itw, const PrimeConsts &pc,
                                             const Mod &m) {
   typedef Cfg<LOGN> G;
@@ -444,11 +449,15 @@ __device__ __forceinline__ void ntt_inverse(uint64_t *sm, Store store, const Tw 
 #pragma unroll
       for (int t = 0; t < 16; t++) x[t] = sm[pidx(tau + t * ST0)];
     }
-    tile_inv<4, false>(x, TileTw<4, false>(itw, 1u, 0u), m);
+    tile_inv<4, MODE == INV_RAW>(x, TileTw<4, false>(itw, 1u, 0u), m);
 #pragma unroll
     for (int t = 0; t < 16; t++) {
-      uint64_t v = shoup_lazy(x[t], pc.ninv, pc.ninv_q, m);
-      store(tau + t * ST0, CANON ? csub(v, m.p) : v);
+      if (MODE == INV_RAW) {
+        store(tau + t * ST0, x[t]);
+      } else {
+        uint64_t v = shoup_lazy(x[t], pc.ninv, pc.ninv_q, m);
+        store(tau + t * ST0, MODE == INV_CANON ? csub(v, m.p) : v);
+      }
     }
   }
   // nobody's shared memory is reused or released while peers still read it
@@ -486,42 +495,106 @@ __device__ __forceinline__ uint64_t decompose_words(const uint64_t *__restrict__
   return acc + (negW & mask);                                // < 5p
 }
 
+// The same residue times a fixed scalar s: sum_w word_w * (2^(64 w) s mod p), one Shoup product per word.  The word
+// weights (pairs) are held in registers for WT > 0 (c[0..WT), negW = p - weight of 2^(64 WT)); WT == 0 reads them from dc.
+// Returned below 5p for W <= 2, below 3p otherwise.
+template <int WT>
+struct DecScale {
+  ulonglong2 c[WT > 0 ? WT : 1];
+  uint64_t negW;
+  const ulonglong2 *dc;
+  __device__ __forceinline__ DecScale(const ulonglong2 *__restrict__ dc_, int W, const Mod &m) : dc(dc_) {
+    if constexpr (WT > 0) {
+#pragma unroll
+      for (int w = 0; w < WT; w++) c[w] = __ldg(&dc_[w]);
+    }
+    negW = m.p - __ldg(&dc_[W]).x;
+  }
+};
+template <int WT>
+__device__ __forceinline__ uint64_t decompose_scaled(const uint64_t *__restrict__ words, size_t stride, int W,
+                                                     const DecScale<WT> &ds, const Mod &m) {
+  uint64_t acc = 0, top;
+  if constexpr (WT > 0) {
+    uint64_t raw[WT];
+#pragma unroll
+    for (int w = 0; w < WT; w++) raw[w] = HB_LD(&words[(size_t)w * stride]);
+    top = raw[WT - 1];
+#pragma unroll
+    for (int w = 0; w < WT; w++) acc += shoup_lazy(raw[w], ds.c[w].x, ds.c[w].y, m);     // each below 2p
+  } else {
+    top = 0;
+    for (int w = 0; w < W; w++) {
+      const ulonglong2 c = __ldg(&ds.dc[w]);
+      top = HB_LD(&words[(size_t)w * stride]);
+      acc += shoup_lazy(top, c.x, c.y, m);
+      if ((w & 7) == 7) acc = fold(acc, m);
+    }
+    acc = fold(acc, m);
+  }
+  return acc + (ds.negW & (uint64_t)((int64_t)top >> 63));
+}
+
 // C == 1: residues of sigma_g(poly) mod p into shared memory, natural order.  Coalesced reads of the source
 // coefficients i, scattered to k = i g mod 2N (sign flipped when k >= N): poly_rot / poly_conj, poly.c:263-283.
-template <int LOGN, int WT>
+template <int LOGN, int WT, bool SCALED>
 __device__ __forceinline__ void stage_poly(uint64_t *sm, const uint64_t *__restrict__ poly, int W, unsigned g,
-                                           const PrimeConsts &pc, const Mod &m, uint64_t negW) {
+                                           const PrimeConsts &pc, const Mod &m, uint64_t negW,
+                                           const ulonglong2 *__restrict__ dc) {
   typedef Cfg<LOGN> G;
   const uint64_t p5 = 5 * m.p;
+  if constexpr (SCALED) {
+    const DecScale<WT> ds(dc, W, m);
 #pragma unroll 4
-  for (int i = threadIdx.x; i < G::N; i += G::THREADS) {
-    const uint64_t v = decompose_words<WT>(poly + i, G::N, W, pc, m, negW);
-    const unsigned k = ((unsigned)i * g) & (2 * G::N - 1);
-    sm[pidx(k & (G::N - 1))] = (k >= (unsigned)G::N) ? p5 - v : v;
+    for (int i = threadIdx.x; i < G::N; i += G::THREADS) {
+      const uint64_t v = decompose_scaled<WT>(poly + i, G::N, W, ds, m);
+      const unsigned k = ((unsigned)i * g) & (2 * G::N - 1);
+      sm[pidx(k & (G::N - 1))] = (k >= (unsigned)G::N) ? p5 - v : v;
+    }
+  } else {
+#pragma unroll 4
+    for (int i = threadIdx.x; i < G::N; i += G::THREADS) {
+      const uint64_t v = decompose_words<WT>(poly + i, G::N, W, pc, m, negW);
+      const unsigned k = ((unsigned)i * g) & (2 * G::N - 1);
+      sm[pidx(k & (G::N - 1))] = (k >= (unsigned)G::N) ? p5 - v : v;
+    }
   }
 }
 
 // Forward NTT (lazy) of the residues mod p of sigma_g(poly) into the cluster's shared memory; ginv = g^-1 mod 2N.
-template <int LOGN>
+// dc != nullptr: the residues are multiplied by the scalar whose word weights dc holds (decompose_scaled).
+template <int LOGN, bool SCALED = false>
 __device__ __forceinline__ void poly_forward(uint64_t *sm, const uint64_t *__restrict__ poly, int W, unsigned g,
                                              unsigned ginv, const PrimeConsts &pc, const Mod &m, uint64_t negW,
-                                             const Tw &tw) {
+                                             const Tw &tw, const ulonglong2 *__restrict__ dc = nullptr) {
   typedef Cfg<LOGN> G;
   if constexpr (G::C == 1) {
-    if (W == 1) stage_poly<LOGN, 1>(sm, poly, W, g, pc, m, negW);
-    else if (W == 2) stage_poly<LOGN, 2>(sm, poly, W, g, pc, m, negW);
-    else stage_poly<LOGN, 0>(sm, poly, W, g, pc, m, negW);
+    if (W == 1) stage_poly<LOGN, 1, SCALED>(sm, poly, W, g, pc, m, negW, dc);
+    else if (W == 2) stage_poly<LOGN, 2, SCALED>(sm, poly, W, g, pc, m, negW, dc);
+    else stage_poly<LOGN, 0, SCALED>(sm, poly, W, g, pc, m, negW, dc);
     ntt_forward_resident<LOGN, false, 5>(sm, tw, m);
   } else {
     const uint64_t p5 = 5 * m.p;
-    ntt_forward<LOGN, false, 5>(
-        sm,
-        [&](int gi) {
-          const unsigned ip = ((unsigned)gi * ginv) & (2 * G::N - 1);
-          const uint64_t v = decompose_words<0>(poly + (ip & (G::N - 1)), G::N, W, pc, m, negW);
-          return (ip >= (unsigned)G::N) ? p5 - v : v;
-        },
-        tw, m);
+    if constexpr (SCALED) {
+      const DecScale<0> ds(dc, W, m);
+      ntt_forward<LOGN, false, 5>(
+          sm,
+          [&](int gi) {
+            const unsigned ip = ((unsigned)gi * ginv) & (2 * G::N - 1);
+            const uint64_t v = decompose_scaled<0>(poly + (ip & (G::N - 1)), G::N, W, ds, m);
+            return (ip >= (unsigned)G::N) ? p5 - v : v;
+          },
+          tw, m);
+    } else {
+      ntt_forward<LOGN, false, 5>(
+          sm,
+          [&](int gi) {
+            const unsigned ip = ((unsigned)gi * ginv) & (2 * G::N - 1);
+            const uint64_t v = decompose_words<0>(poly + (ip & (G::N - 1)), G::N, W, pc, m, negW);
+            return (ip >= (unsigned)G::N) ? p5 - v : v;
+          },
+          tw, m);
+    }
   }
 }
 

@@ -50,7 +50,7 @@ k_ntt_inv(const uint64_t *__restrict__ in, uint64_t *__restrict__ out, Tables T,
   for (int i = threadIdx.x; i < G::M; i += G::THREADS) smem[pidx(i)] = HB_LD(&src[i]);
   __syncthreads();
   uint64_t *dst = out + (size_t)limb * G::N;
-  ntt_inverse<LOGN, true>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
+  ntt_inverse<LOGN, INV_CANON>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
 }
 
 // =========================================================================================================
@@ -76,14 +76,19 @@ k_poly_ntt(const uint64_t *__restrict__ src, size_t poly_stride, int W, uint64_t
 
 // canonical residues -> Shoup pairs (w, floor(w 2^64 / p)) for fixed multiplicands (keys, encoded diagonals).
 // limbs[j][N] uses prime j % D.  A residue stored as p becomes 0: the same class.
+// scale: 0 = as is; 1 = times N^-1 (the inverse transform after the product then skips its own scaling);
+//        2 = times N^-1 (P_Dw/p_d)^-1, the CRT weight for Dw limbs as well (the reconstruction skips its multiply).
 __global__ void k_shoup_prep(const uint64_t *__restrict__ in, ulonglong2 *__restrict__ out, Tables T, unsigned D,
-                             size_t nlimbs) {
+                             size_t nlimbs, int scale, unsigned Dw) {
   const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= nlimbs * T.N) return;
   const unsigned d = (unsigned)((gid / T.N) % D);
-  const uint64_t p = T.primes[d].p;
+  const PrimeConsts pc = T.primes[d];
+  const uint64_t p = pc.p;
   uint64_t w = in[gid];
   if (w >= p) w -= p;
+  if (scale >= 1) w = shoup(w, pc.ninv, pc.ninv_q, p);
+  if (scale >= 2) w = shoup(w, T.crt_inv[(size_t)Dw * T.dimub + d], T.crt_inv_q[(size_t)Dw * T.dimub + d], p);
   const unsigned __int128 num = ((unsigned __int128)w) << 64;
   out[gid] = make_ulonglong2(w, (uint64_t)(num / p));
 }
@@ -93,8 +98,9 @@ __global__ void k_shoup_prep(const uint64_t *__restrict__ in, ulonglong2 *__rest
 //   chat[b][h][d] = invntt( ntt( decompose( sigma(src_b) ) mod p_d ) o evk.p_h[d] ),  h = 0,1
 // sigma is the automorphism X -> X^g fused into the load (poly_rot / poly_conj, poly.c:263-283), given as
 // ginv = g^-1 mod 2N:  sigma(a)[k] = +a[k*ginv mod 2N]  if that index is < N, else  -a[(k*ginv mod 2N) - N].
-// evk: Shoup pairs [2][dimevk][N].  chat is lazily reduced (below 2p): its only consumers multiply it by a
-// fixed constant first (crt_low), which accepts any 64-bit word.
+// evk: Shoup pairs [2][dimevk][N] of key * N^-1 (hb_evk_upload), so the inverse transforms do not scale.  The source
+// residues are decomposed with the CRT weight (P_D/p_d)^-1 folded into the word weights (decompose_scaled), so chat
+// holds y_d = a_d (P_D/p_d)^-1 mod p_d directly, lazily reduced (below 2p): the tail starts at the CRT sum.
 // =========================================================================================================
 template <int LOGN>
 __global__ void __launch_bounds__(Cfg<LOGN>::THREADS, (Cfg<LOGN>::MINBLOCKS > 2 ? 2 : Cfg<LOGN>::MINBLOCKS))
@@ -114,7 +120,8 @@ k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, unsigned 
   const Mod m = make_mod(pc.p);
   const uint64_t negW = pc.p - T.pow64[(size_t)d * (T.WC + 1) + W];
   const uint64_t *poly = src + (size_t)b * src_bstride;
-  poly_forward<LOGN>(smA, poly, W, g, ginv, pc, m, negW, make_tw(T, d, false));
+  const ulonglong2 *dc = T.dec_s + ((size_t)D * T.dimub + d) * (T.WC + 1);
+  poly_forward<LOGN, true>(smA, poly, W, g, ginv, pc, m, negW, make_tw(T, d, false), dc);
 #pragma unroll 1
   for (int h = 0; h < 2; h++) {
     const ulonglong2 *key = evk + ((size_t)h * dimevk + d) * G::N + (size_t)chunk * G::M;
@@ -125,13 +132,68 @@ k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, unsigned 
     }
     __syncthreads();
     uint64_t *dst = chat + (((size_t)b * 2 + h) * D + d) * G::N;
-    ntt_inverse<LOGN, false>(smB, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
+    ntt_inverse<LOGN, INV_RAW>(smB, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
+  }
+}
+
+// =========================================================================================================
+// Baby rotations of he_gemv (GPQHE/src/he-algo.c:66-68), per-limb half of nj key switches of the SAME ciphertext:
+//   chat[j][b][h][d] = y-weighted invntt( ntt( decompose( sigma_j(c1_b) ) mod p_d ) o rk[j].p_h[d] ),  j < nj
+// sigma_j only permutes (and negates) coefficients, and the negacyclic transform of sigma_g(a) is a permutation of the
+// transform of a:  ntt(sigma_g a)[i] = ntt(a)[perm_g[i]],  perm_g[i] = brv(((2 brv(i) + 1) g mod 2N - 1) / 2)
+// (position i holds the evaluation at zeta^(2 brv(i) + 1)).  So ONE decomposition and ONE forward transform serve all
+// nj rotations; every key product, inverse transform, reconstruction and rounding of the reference is still performed
+// on the same residues (the identity is exact modulo p_d), hence the same ciphertexts.
+// =========================================================================================================
+struct BabySet {
+  const ulonglong2 *evk[4];      // rk[j] (Shoup pairs [2][dimevk][N], times N^-1)
+  const uint16_t *perm[4];       // perm_{g_j}[N]
+  unsigned nj;
+};
+
+template <int LOGN>
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS, (Cfg<LOGN>::MINBLOCKS > 2 ? 2 : Cfg<LOGN>::MINBLOCKS))
+k_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const __grid_constant__ BabySet S, unsigned dimevk,
+          uint64_t *__restrict__ chat, size_t chat_jstride, Tables T, unsigned D) {
+  typedef Cfg<LOGN> G;
+  extern __shared__ __align__(16) uint64_t smem[];
+  uint64_t *smA = smem, *smB = smem + G::SMEM_WORDS;
+  const unsigned idx = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
+  const unsigned b = idx / D, d = idx % D;
+  const PrimeConsts pc = T.primes[d];
+  const Mod m = make_mod(pc.p);
+  const uint64_t negW = pc.p - T.pow64[(size_t)d * (T.WC + 1) + W];
+  const uint64_t *poly = src + (size_t)b * src_bstride;
+  const ulonglong2 *dc = T.dec_s + ((size_t)D * T.dimub + d) * (T.WC + 1);
+  poly_forward<LOGN, true>(smA, poly, W, 1u, 1u, pc, m, negW, make_tw(T, d, false), dc);
+  if constexpr (G::C > 1) cg::this_cluster().sync();        // peers' chunks of the transform are complete
+  const Tw itw = make_tw(T, d, true);
+#pragma unroll 1
+  for (unsigned j = 0; j < S.nj; j++) {
+    const uint16_t *perm = S.perm[j] + (size_t)chunk * G::M;
+#pragma unroll 1
+    for (int h = 0; h < 2; h++) {
+      const ulonglong2 *key = S.evk[j] + ((size_t)h * dimevk + d) * G::N + (size_t)chunk * G::M;
+#pragma unroll 4
+      for (int i = threadIdx.x; i < G::M; i += G::THREADS) {
+        const ulonglong2 k = HB_LDS2(&key[i]);
+        const unsigned s = __ldg(&perm[i]);
+        uint64_t v;
+        if constexpr (G::C > 1) v = cg::this_cluster().map_shared_rank(smA, s >> G::LOGM)[pidx(s & (G::M - 1))];
+        else v = smA[pidx(s)];
+        smB[pidx(i)] = shoup_lazy(v, k.x, k.y, m);
+      }
+      __syncthreads();
+      uint64_t *dst = chat + (size_t)j * chat_jstride + (((size_t)b * 2 + h) * D + d) * G::N;
+      ntt_inverse<LOGN, INV_RAW>(smB, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, itw, pc, m);
+    }
   }
 }
 
 // =========================================================================================================
 // ct x pt, per-limb:  he_mulpt  GPQHE/src/he-mult.c:176-188
-//   chat[b][h][d] = invntt( ntt(decompose(c_h)) o pthat[d] )          pthat: Shoup pairs [D][N]
+//   chat[b][h][d] = (P_D/p_d)^-1 invntt( ntt(decompose(c_h)) o pthat[d] )
+// pthat: Shoup pairs [D][N] of ntt(pt) N^-1 (P_D/p_d)^-1 (k_shoup_prep scale 2): no scaling pass, no CRT multiply later.
 // =========================================================================================================
 template <int LOGN>
 __global__ void __launch_bounds__(Cfg<LOGN>::THREADS, Cfg<LOGN>::MINBLOCKS)
@@ -159,14 +221,14 @@ k_mulpt_limb(const uint64_t *__restrict__ ct, int W, const ulonglong2 *__restric
   }
   __syncthreads();
   uint64_t *dst = chat + ((size_t)q * D + d) * G::N;
-  ntt_inverse<LOGN, false>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
+  ntt_inverse<LOGN, INV_RAW>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
 }
 
 // =========================================================================================================
 // rotation-sum inner step of he_gemv (GPQHE/src/he-algo.c:64-79), accumulated in the NTT domain:
 //   chat[q][d] = invntt( sum_j  hat[j][q][d] o pthat[j][d] ),   q = b*2 + h,  j < n1
 // hat[j] = ntt(decompose(rot_j(ct))) (k_poly_ntt), pthat[j] = Shoup pairs of the j-th encoded diagonal of this giant
-// step.  The reference multiplies, reconstructs and adds mod q_l one diagonal at a time; the transforms and the CRT
+// step, pre-scaled like k_mulpt_limb's.  The reference multiplies, reconstructs and adds mod q_l one diagonal at a time; the transforms and the CRT
 // are linear, so the sum of the exact products is the same integer as long as it stays inside (-P_D/2, P_D/2),
 // which the host checks when it builds the plan (hb_api.cu gemv_plan).
 // =========================================================================================================
@@ -195,7 +257,7 @@ k_mulacc_intt(const uint64_t *__restrict__ hat, size_t hat_jstride, const ulongl
   }
   __syncthreads();
   uint64_t *dst = chat + ((size_t)q * D + d) * G::N;
-  ntt_inverse<LOGN, false>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
+  ntt_inverse<LOGN, INV_RAW>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
 }
 
 // =========================================================================================================
@@ -228,7 +290,7 @@ k_tensor_intt(const uint64_t *__restrict__ hatA, const uint64_t *__restrict__ ha
   }
   __syncthreads();
   uint64_t *dst = dhat + (((size_t)b * 3 + which) * D + d) * G::N;
-  ntt_inverse<LOGN, false>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
+  ntt_inverse<LOGN, INV_LAZY>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
 }
 
 // =========================================================================================================
@@ -237,7 +299,8 @@ k_tensor_intt(const uint64_t *__restrict__ hatA, const uint64_t *__restrict__ ha
 //   y_d = a_d (P_D/p_d)^-1 mod p_d,  v = round(sum_d y_d / p_d)  (120-bit fixed point, error < D 2^-60).
 //   Only x mod 2^(64 WK) is formed: every consumer reduces modulo a power of two afterwards.
 // =========================================================================================================
-template <int WK, class Get>
+// PRE: the limbs already carry the weight (a(d) = y_d, lazily reduced below 2p) -- k_ks_limb, k_mulpt_limb, k_mulacc_intt.
+template <int WK, bool PRE, class Get>
 __device__ __forceinline__ void crt_low(Get a, unsigned D, const Tables &T, uint64_t (&acc)[WK]) {
 #pragma unroll
   for (int w = 0; w < WK; w++) acc[w] = 0;
@@ -246,7 +309,7 @@ __device__ __forceinline__ void crt_low(Get a, unsigned D, const Tables &T, uint
   const uint64_t *phat = T.crt_phat + (size_t)D * T.dimub * T.WC;
   for (unsigned d = 0; d < D; d++) {
     const uint64_t p = T.primes[d].p, mu = T.primes[d].mu;
-    const uint64_t y = shoup(a(d), inv[d], invq[d], p);
+    const uint64_t y = PRE ? csub(a(d), p) : shoup(a(d), inv[d], invq[d], p);
     uint64_t lo = y * mu, hi = __umul64hi(y, mu);
     Flo += lo;
     Fhi += hi + (Flo < lo);
@@ -279,7 +342,7 @@ __device__ __forceinline__ void crt_low(Get a, unsigned D, const Tables &T, uint
 }
 
 // out polynomial q (of npoly) = smod(reconstruct(chat[q][0..D)), 2^k)   -- poly_rns2mpi, poly.c:109-120
-template <int WK>
+template <int WK, bool PRE>
 __global__ void k_recon_smod(const uint64_t *__restrict__ chat, unsigned D, uint64_t *__restrict__ out, int Wout,
                              int k, Tables T, unsigned npoly) {
   const unsigned N = T.N;
@@ -288,7 +351,7 @@ __global__ void k_recon_smod(const uint64_t *__restrict__ chat, unsigned D, uint
   const unsigned q = gid / N, i = gid % N;
   const uint64_t *limbs = chat + (size_t)q * D * N + i;
   uint64_t acc[WK];
-  crt_low<WK>([&](unsigned d) { return limbs[(size_t)d * N]; }, D, T, acc);
+  crt_low<WK, PRE>([&](unsigned d) { return limbs[(size_t)d * N]; }, D, T, acc);
   sext_bits<WK>(acc, k);
   uint64_t *o = out + (size_t)q * Wout * N + i;
 #pragma unroll
@@ -310,7 +373,7 @@ __device__ __forceinline__ void ks_exact(const uint64_t *__restrict__ limbs, uns
                                       bool &roundup_out) {
   const unsigned N = T.N;
   uint64_t acc[WK];
-  crt_low<WK>([&](unsigned d) { return limbs[(size_t)d * N]; }, D, T, acc);
+  crt_low<WK, true>([&](unsigned d) { return limbs[(size_t)d * N]; }, D, T, acc);
   // ---- R = x mod P, exact ----
   uint64_t R[WPK];
 #pragma unroll
@@ -319,7 +382,8 @@ __device__ __forceinline__ void ks_exact(const uint64_t *__restrict__ limbs, uns
   const int WP = T.WP;
   for (unsigned d = 0; d < T.dim; d++) {
     const uint64_t p = T.primes[d].p, mu = T.primes[d].mu;
-    const uint64_t z = shoup(limbs[(size_t)d * N], T.ks_inv[d], T.ks_inv_q[d], p);
+    const ulonglong2 kz = T.ks_z[(size_t)D * T.dim + d];                      // limbs hold y_d: re-weight for P
+    const uint64_t z = shoup(limbs[(size_t)d * N], kz.x, kz.y, p);
     uint64_t lo = z * mu, hi = __umul64hi(z, mu);
     Flo += lo;
     Fhi += hi + (Flo < lo);
@@ -476,8 +540,8 @@ __device__ __forceinline__ void ks_tail(uint64_t (&t)[WK], bool roundup, const u
 // fixed-point sums whose error is below 2 D units.  When a sum lands within 64 units of a decision boundary (probability
 // about 2^-48 per coefficient, or an exactly zero R) the thread takes ks_exact instead, so the result is always exact.
 struct KsFast {
-  uint64_t p[8], mu[8], inv[8], invq[8], phat[8][2], PD[2];      // CRT over the D limbs (x mod 2^128)
-  uint64_t kinv[4], kinvq[4], kphat[4][2], kP[2], Pinv[2];       // R = x mod P over the first dim limbs; P^-1 mod 2^128
+  uint64_t p[8], mu[8], phat[8][2], PD[2];                       // CRT over the D pre-weighted limbs (x mod 2^128)
+  uint64_t kinv[4], kinvq[4], kphat[4][2], kP[2], Pinv[2];       // R = x mod P over the first dim limbs (kinv = ks_z: re-weight); P^-1 mod 2^128
   unsigned D, dim;
 };
 
@@ -521,8 +585,7 @@ __global__ void __launch_bounds__(128) k_ks_finish_fast(const uint64_t *__restri
   uint64_t Fx = 0, Fr = 0;
 #pragma unroll
   for (int d = 0; d < D; d++) {
-    const Mod m = make_mod(F.p[d]);
-    const uint64_t y = shoup_lazy(a[d], F.inv[d], F.invq[d], m);
+    const uint64_t y = a[d];                                     // already a_d (P_D/p_d)^-1, below 2p
     Fx += __umul64hi(y, F.mu[d]);
     mac_low<WK>(acc, y, F.phat[d]);
   }

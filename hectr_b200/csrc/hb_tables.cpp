@@ -217,6 +217,25 @@ std::string build_tables(HostTables &t, unsigned logn, unsigned logq, unsigned s
   t.ks_P = P.low(t.WP);
   t.ks_Ph = P.shr1().low(t.WP);
   t.ks_Pinv = inv_mod_2k(P.low(WC), WC);
+
+  // ---- pre-scaling constants ---------------------------------------------------------------------------
+  t.dec_s.assign((size_t)(DU + 1) * DU * (WC + 1) * 2, 0);
+  t.ks_z.assign((size_t)(DU + 1) * t.dim * 2, 0);
+  for (unsigned D = 1; D <= DU; D++) {
+    for (unsigned d = 0; d < D; d++) {
+      const uint64_t pd = t.primes[d].p, inv = t.crt_inv[(size_t)D * DU + d];
+      for (unsigned w = 0; w <= WC; w++) {
+        const uint64_t c = mulmod(t.pow64[(size_t)d * (WC + 1) + w], inv, pd);
+        uint64_t *o = &t.dec_s[(((size_t)D * DU + d) * (WC + 1) + w) * 2];
+        o[0] = c; o[1] = shoup_quotient(c, pd);
+      }
+      if (d < t.dim) {
+        const uint64_t z = mulmod(t.ks_inv[d], powmod(inv, pd - 2, pd), pd);
+        uint64_t *o = &t.ks_z[((size_t)D * t.dim + d) * 2];
+        o[0] = z; o[1] = shoup_quotient(z, pd);
+      }
+    }
+  }
   return "";
 }
 

@@ -45,6 +45,12 @@ struct HostTables {
   std::vector<uint64_t> ks_phat;         // [dim][WP]
   std::vector<uint64_t> ks_P, ks_Ph;     // [WP]
   std::vector<uint64_t> ks_Pinv;         // [WC]
+  // Pre-scaling constants (Shoup pairs).  The kernels push the CRT weight (P_D/p_d)^-1 mod p_d through the linear
+  // transforms, so the limbs reach the reconstruction already multiplied by it:
+  //   dec_s[D][d][w] = 2^(64 w) (P_D/p_d)^-1 mod p_d, w <= WC : word weights of the scaled rns_decompose
+  //   ks_z[D][e]     = (P/p_e)^-1 ((P_D/p_e)^-1)^-1 mod p_e, e < dim : from a D-limb weight to the weight of R = x mod P
+  std::vector<uint64_t> dec_s;           // [dimub+1][dimub][WC+1][2]
+  std::vector<uint64_t> ks_z;            // [dimub+1][dim][2]
   std::vector<BigU> Pfull;               // [dimub+1] P_D (host only; tests / diagnostics)
 };
 
