@@ -53,6 +53,8 @@ struct hb_ctx {
   std::vector<void *> table_allocs;
   int device = 0, sm_count = 0;
   cudaStream_t stream = nullptr, own_stream = nullptr;
+  cudaStream_t up_stream = nullptr, down_stream = nullptr;        // host-buffer pipeline (hb_ctr_hempc_eval_host)
+  cudaEvent_t ev_up[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_down[2] = {nullptr, nullptr};
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   uint64_t launches = 0;
   // optional per-kernel CUDA-event timing (bench.py roofline): name -> (launches, event pairs)
@@ -398,6 +400,11 @@ extern "C" void hb_ctx_destroy(hb_ctx *ctx) {
   cudaFree(ctx->wsC);
   cudaFree(ctx->wsD);
   for (auto &kv : ctx->perms) cudaFree(kv.second);
+  if (ctx->up_stream) {
+    cudaStreamDestroy(ctx->up_stream);
+    cudaStreamDestroy(ctx->down_stream);
+    for (int s2 = 0; s2 < 2; s2++) { cudaEventDestroy(ctx->ev_up[s2]); cudaEventDestroy(ctx->ev_comp[s2]); cudaEventDestroy(ctx->ev_down[s2]); }
+  }
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->own_stream);
@@ -598,6 +605,11 @@ extern "C" void hb_ct_alloc(hb_ctx *ctx, hb_ct *ct, unsigned batch) {
   ct->l = ctx->ht.L; ct->nu = 0; ct->B = 0; ct->batch = batch;
   ct->words = pool_get(ctx, ct_capacity(ctx, batch));
   CUDA_OK(cudaMemsetAsync(ct->words, 0, ct_capacity(ctx, batch), ctx->stream));   // gcry_mpi_new(0) == 0
+}
+// temporaries that are fully overwritten before they are read: no zero fill
+static void ct_alloc_tmp(hb_ctx *ctx, hb_ct *ct, unsigned batch) {
+  ct->l = ctx->ht.L; ct->nu = 0; ct->B = 0; ct->batch = batch;
+  ct->words = pool_get(ctx, ct_capacity(ctx, batch));
 }
 extern "C" void hb_ct_free(hb_ctx *ctx, hb_ct *ct) {
   pool_put(ctx, ct->words);
@@ -911,9 +923,9 @@ static void gemv_stepwise(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const h
   const hb::HostTables &h = ctx->ht;
   const double Delta = std::ldexp(1.0, (int)h.logDelta);
   hb_ct inner, outer, rot;
-  hb_ct_alloc(ctx, &inner, ct->batch);
-  hb_ct_alloc(ctx, &outer, ct->batch);
-  hb_ct_alloc(ctx, &rot, ct->batch);
+  ct_alloc_tmp(ctx, &inner, ct->batch);
+  ct_alloc_tmp(ctx, &outer, ct->batch);
+  ct_alloc_tmp(ctx, &rot, ct->batch);
   for (unsigned i = 0; i < n2; i++) {
     const unsigned shift = i * n1;
     for (unsigned j = 0; j < n1; j++) {
@@ -966,9 +978,9 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
   const size_t jstride = (size_t)batch * 2 * D * N;
   uint64_t *hat = ws_get(ctx, ctx->wsC, ctx->wsC_bytes, (size_t)n1 * jstride * 8);
   hb_ct inner, outer, rot;
-  hb_ct_alloc(ctx, &inner, batch);
-  hb_ct_alloc(ctx, &outer, batch);
-  hb_ct_alloc(ctx, &rot, batch);
+  ct_alloc_tmp(ctx, &inner, batch);
+  ct_alloc_tmp(ctx, &outer, batch);
+  ct_alloc_tmp(ctx, &rot, batch);
   if (ctx->no_hoist || N > 65536) {
     for (unsigned j = 0; j < n1; j++) {
       hb_ct_copy(ctx, &rot, ct);
@@ -1038,8 +1050,8 @@ extern "C" void hb_ctr_hempc_eval(hb_ctx *ctx, hb_ct *up, const double *Ka, cons
   same_shape(xhat, uhat, "hb_ctr_hempc_eval"); same_shape(up, xhat, "hb_ctr_hempc_eval");
   const unsigned batch = xhat->batch;
   hb_ct xdiff, udiff, KaX, KbU, du, ucopy;
-  hb_ct_alloc(ctx, &xdiff, batch); hb_ct_alloc(ctx, &udiff, batch); hb_ct_alloc(ctx, &KaX, batch);
-  hb_ct_alloc(ctx, &KbU, batch); hb_ct_alloc(ctx, &du, batch); hb_ct_alloc(ctx, &ucopy, batch);
+  ct_alloc_tmp(ctx, &xdiff, batch); ct_alloc_tmp(ctx, &udiff, batch); ct_alloc_tmp(ctx, &KaX, batch);
+  ct_alloc_tmp(ctx, &KbU, batch); ct_alloc_tmp(ctx, &du, batch); ct_alloc_tmp(ctx, &ucopy, batch);
   hb_he_sub(ctx, &xdiff, xhat, xr);              // hempc.c:253
   hb_he_sub(ctx, &udiff, uhat, ur);              // hempc.c:255
   hb_he_gemv(ctx, &KaX, Ka, &xdiff, rk);         // hempc.c:257
@@ -1053,22 +1065,66 @@ extern "C" void hb_ctr_hempc_eval(hb_ctx *ctx, hb_ct *up, const double *Ka, cons
   hb_ct_free(ctx, &KbU); hb_ct_free(ctx, &du); hb_ct_free(ctx, &ucopy);
 }
 
+// End to end from host buffers.  The batch is cut into chunks that flow through three streams -- upload (copy stream),
+// evaluate (the context's stream), download (second copy stream) -- with two sets of device buffers, so the PCIe
+// transfers of chunk c+1 and c-1 overlap the evaluation of chunk c.  HB_E2E_CHUNK sets the chunk size (instances).
 extern "C" void hb_ctr_hempc_eval_host(hb_ctx *ctx, unsigned batch, unsigned l, const double *Ka, const double *Kb,
                                        const uint64_t *in_xhat, const uint64_t *in_xr, const uint64_t *in_uhat,
                                        const uint64_t *in_ur, const hb_evk *rk, uint64_t *out_up) {
   check_level(ctx, l);
   if (l == 0) hb_die("hb_ctr_hempc_eval_host: inputs must be above level 0");
-  hb_ct xhat, xr, uhat, ur, up;
-  hb_ct_alloc(ctx, &xhat, batch); hb_ct_alloc(ctx, &xr, batch); hb_ct_alloc(ctx, &uhat, batch);
-  hb_ct_alloc(ctx, &ur, batch); hb_ct_alloc(ctx, &up, batch);
+  if (batch == 0) return;
   const double Delta = std::ldexp(1.0, (int)ctx->ht.logDelta);
-  hb_ct_upload(ctx, &xhat, in_xhat, l, Delta, 1.0);
-  hb_ct_upload(ctx, &xr, in_xr, l, Delta, 1.0);
-  hb_ct_upload(ctx, &uhat, in_uhat, l, Delta, 1.0);
-  hb_ct_upload(ctx, &ur, in_ur, l, Delta, 1.0);
-  hb_ctr_hempc_eval(ctx, &up, Ka, Kb, &xhat, &xr, &uhat, &ur, rk);
-  hb_ct_download(ctx, &up, out_up);
-  hb_ct_free(ctx, &xhat); hb_ct_free(ctx, &xr); hb_ct_free(ctx, &uhat); hb_ct_free(ctx, &ur); hb_ct_free(ctx, &up);
+  unsigned chunk = 512;
+  if (const char *e = getenv("HB_E2E_CHUNK")) { const long v = atol(e); if (v > 0) chunk = (unsigned)v; }
+  if (chunk > batch) chunk = batch;
+  const uint64_t *host_in[4] = {in_xhat, in_xr, in_uhat, in_ur};
+  const size_t in_words = (size_t)2 * hb::words_of_level(ctx->ht, l) * ctx->ht.N;         // per instance
+  const size_t out_words = (size_t)2 * hb::words_of_level(ctx->ht, l - 1) * ctx->ht.N;
+  if (!ctx->up_stream) {
+    CUDA_OK(cudaStreamCreateWithFlags(&ctx->up_stream, cudaStreamNonBlocking));
+    CUDA_OK(cudaStreamCreateWithFlags(&ctx->down_stream, cudaStreamNonBlocking));
+    for (int s = 0; s < 2; s++) {
+      CUDA_OK(cudaEventCreateWithFlags(&ctx->ev_up[s], cudaEventDisableTiming));
+      CUDA_OK(cudaEventCreateWithFlags(&ctx->ev_comp[s], cudaEventDisableTiming));
+      CUDA_OK(cudaEventCreateWithFlags(&ctx->ev_down[s], cudaEventDisableTiming));
+    }
+  }
+  const unsigned nsets = batch > chunk ? 2 : 1;
+  hb_ct in[2][4], up[2];
+  for (unsigned s = 0; s < nsets; s++) {
+    for (int q = 0; q < 4; q++) ct_alloc_tmp(ctx, &in[s][q], chunk);
+    ct_alloc_tmp(ctx, &up[s], chunk);
+  }
+  // pool buffers may still be read by work queued earlier on the context's stream: order the upload stream after it
+  CUDA_OK(cudaEventRecord(ctx->ev_comp[0], ctx->stream));
+  CUDA_OK(cudaStreamWaitEvent(ctx->up_stream, ctx->ev_comp[0], 0));
+  const unsigned nchunks = (batch + chunk - 1) / chunk;
+  for (unsigned c = 0; c < nchunks; c++) {
+    const unsigned s = c & (nsets - 1), b0 = c * chunk, nb = batch - b0 < chunk ? batch - b0 : chunk;
+    if (c >= nsets) CUDA_OK(cudaStreamWaitEvent(ctx->up_stream, ctx->ev_comp[s], 0));      // chunk c-2 no longer reads in[s]
+    for (int q = 0; q < 4; q++) {
+      in[s][q].batch = nb; in[s][q].l = l; in[s][q].nu = Delta; in[s][q].B = 1.0;
+      CUDA_OK(cudaMemcpyAsync(in[s][q].words, host_in[q] + (size_t)b0 * in_words, (size_t)nb * in_words * 8, cudaMemcpyHostToDevice,
+                              ctx->up_stream));
+    }
+    CUDA_OK(cudaEventRecord(ctx->ev_up[s], ctx->up_stream));
+    CUDA_OK(cudaStreamWaitEvent(ctx->stream, ctx->ev_up[s], 0));
+    if (c >= nsets) CUDA_OK(cudaStreamWaitEvent(ctx->stream, ctx->ev_down[s], 0));         // chunk c-2's result has left up[s]
+    up[s].batch = nb;
+    hb_ctr_hempc_eval(ctx, &up[s], Ka, Kb, &in[s][0], &in[s][1], &in[s][2], &in[s][3], rk);
+    CUDA_OK(cudaEventRecord(ctx->ev_comp[s], ctx->stream));
+    CUDA_OK(cudaStreamWaitEvent(ctx->down_stream, ctx->ev_comp[s], 0));
+    CUDA_OK(cudaMemcpyAsync(out_up + (size_t)b0 * out_words, up[s].words, (size_t)nb * out_words * 8, cudaMemcpyDeviceToHost, ctx->down_stream));
+    CUDA_OK(cudaEventRecord(ctx->ev_down[s], ctx->down_stream));
+  }
+  CUDA_OK(cudaStreamSynchronize(ctx->down_stream));
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  for (unsigned s = 0; s < nsets; s++) {
+    for (int q = 0; q < 4; q++) { in[s][q].batch = chunk; hb_ct_free(ctx, &in[s][q]); }
+    up[s].batch = chunk;
+    hb_ct_free(ctx, &up[s]);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------

@@ -4,7 +4,15 @@
 #pragma once
 #include "hb_dev.cuh"
 
+#ifndef HB_KS_MINB
+#define HB_KS_MINB 3     /* resident CTAs per SM the two-buffer key-switch kernels are compiled for, N <= 2^12 */
+#endif
+
 namespace hbdev {
+
+// two shared-memory buffers per CTA: 3 x 74 KB fit one SM up to N = 2^12; from 2^13 (M = 8192, 147 KB) only one CTA does
+template <int LOGN>
+struct KsBlocks { static constexpr int value = (LOGN <= 12) ? HB_KS_MINB : 1; };
 
 // =========================================================================================================
 // K2 / K3: stand-alone batched transforms (config B microbench; building blocks of he_mul)
@@ -103,7 +111,7 @@ __global__ void k_shoup_prep(const uint64_t *__restrict__ in, ulonglong2 *__rest
 // holds y_d = a_d (P_D/p_d)^-1 mod p_d directly, lazily reduced (below 2p): the tail starts at the CRT sum.
 // =========================================================================================================
 template <int LOGN>
-__global__ void __launch_bounds__(Cfg<LOGN>::THREADS, (Cfg<LOGN>::MINBLOCKS > 2 ? 2 : Cfg<LOGN>::MINBLOCKS))
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS, KsBlocks<LOGN>::value)
 k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, unsigned g, unsigned ginv,
           const ulonglong2 *__restrict__ evk, unsigned dimevk, uint64_t *__restrict__ chat, Tables T, unsigned D) {
   typedef Cfg<LOGN> G;
@@ -152,7 +160,7 @@ struct BabySet {
 };
 
 template <int LOGN>
-__global__ void __launch_bounds__(Cfg<LOGN>::THREADS, (Cfg<LOGN>::MINBLOCKS > 2 ? 2 : Cfg<LOGN>::MINBLOCKS))
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS, KsBlocks<LOGN>::value)
 k_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const __grid_constant__ BabySet S, unsigned dimevk,
           uint64_t *__restrict__ chat, size_t chat_jstride, Tables T, unsigned D) {
   typedef Cfg<LOGN> G;

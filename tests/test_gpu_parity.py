@@ -210,6 +210,35 @@ def test_gemv_fused_equals_stepwise(cfgA, monkeypatch):
     assert np.array_equal(fused, step)
 
 
+def test_eval_host_pipeline_matches_device(cfgA, monkeypatch):
+    """hb_ctr_hempc_eval_host cuts the batch into chunks that flow through upload / evaluate / download streams: ragged
+    chunks (7 instances in chunks of 3) and a one-chunk batch must give the words of the device-resident call, and the
+    hoisted baby rotations (one forward transform for n1 key switches) the words of one key switch per rotation."""
+    from hectr_b200 import Engine
+    eng, keys = cfgA["eng"], cfgA["keys"]
+    rng = np.random.default_rng(47)
+    S, l = 16, 2
+    Ka = np.zeros((S, S), dtype=np.complex128)
+    Kb = np.zeros((S, S), dtype=np.complex128)
+    Ka[:8, :3] = rng.standard_normal((8, 3))
+    Kb[:8, :2] = rng.standard_normal((8, 2))
+    w = [random_ct_words(rng, 7, eng.words(l), eng.n, eng.logq(l)) for _ in range(4)]
+    want = eng.ctr_hempc_eval(Ka, Kb, *[eng.ct(x, l) for x in w], keys).download()
+    monkeypatch.setenv("HB_E2E_CHUNK", "3")
+    assert np.array_equal(eng.ctr_hempc_eval_host(Ka, Kb, *w, keys, l), want)
+    monkeypatch.setenv("HB_E2E_CHUNK", "64")
+    assert np.array_equal(eng.ctr_hempc_eval_host(Ka, Kb, *w, keys, l), want)
+    monkeypatch.setenv("HB_GEMV_NOHOIST", "1")
+    eng2 = Engine(*A_PARAMS)
+    try:
+        rk_arr = np.stack([cfgA["ref"].evk_to_array(cfgA["rk"][i]) for i in range(S)])
+        keys2 = eng2.keys(rk_arr)
+        assert np.array_equal(eng2.ctr_hempc_eval(Ka, Kb, *[eng2.ct(x, l) for x in w], keys2).download(), want)
+        keys2.free()
+    finally:
+        eng2.close()
+
+
 def test_mul_relin(cfgA):
     ref, eng, pk, sk = cfgA["ref"], cfgA["eng"], cfgA["pk"], cfgA["sk"]
     rlk = ref.genrlk(sk)
