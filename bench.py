@@ -281,11 +281,12 @@ def run_ours(args):
     avg_ms = prof[dom]["ms"] / prof[dom]["launches"]
     abytes = algorithmic_bytes(dom, per, n, W, D_ks, D_pt)
     achieved = abytes / (avg_ms / 1e3) / 1e9 if abytes else None
-    traffic = None
+    traffic, heavy = None, None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get(dom, {}).get(str(per))
+            rec = json.load(open(tpath)).get(dom, {})
+            traffic, heavy = rec.get(str(per)), rec.get("fmaheavy_pct")
         except Exception:
             traffic = None
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -294,6 +295,8 @@ def run_ours(args):
                 "share_of_step": prof[dom]["ms"] / tot_ms,
                 "kernels": {kname: {"launches": v["launches"], "ms": round(v["ms"], 3), "share": round(v["ms"] / tot_ms, 4)}
                             for kname, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])},
+                "int_pipe": {"unit": "sm__pipe_fmaheavy_cycles_active % of peak (the pipe IMAD/IMAD.WIDE issue to)", "pct": heavy,
+                             "source": "profiles/r01/ncu_summary.md (ncu --set full capture of this kernel at this batch)"},
                 "note": "integer-pipe bound path (59-bit modular butterflies); HBM fraction is reported as the contract asks"}
 
     cpu = None

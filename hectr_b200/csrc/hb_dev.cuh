@@ -198,7 +198,10 @@ struct Cfg {
   #ifndef HB_MINB12
 #define HB_MINB12 3
 #endif
-  static constexpr int MINBLOCKS = (LOGN <= 12) ? HB_MINB12 : (LOGN == 13 ? 3 : 2);
+#ifndef HB_MINB_BIG
+#define HB_MINB_BIG 3     /* 3 x 74 KB of shared memory and 80 registers: three resident CTAs for N >= 2^14 too */
+#endif
+  static constexpr int MINBLOCKS = (LOGN <= 12) ? HB_MINB12 : (LOGN == 13 ? 3 : HB_MINB_BIG);
 };
 
 __device__ __forceinline__ int pidx(int i) { return i + ((i >> 4) << 1); }
