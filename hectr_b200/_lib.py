@@ -30,6 +30,10 @@ class HbEvk(C.Structure):
     _fields_ = [("p", C.c_void_p)]
 
 
+class HbSk(C.Structure):
+    _fields_ = [("hat", C.c_void_p), ("scaled", C.c_void_p * 64)]
+
+
 ctx_p = C.c_void_p
 ct_p = C.POINTER(HbCt)
 pt_p = C.POINTER(HbPt)
@@ -98,6 +102,11 @@ PROTOTYPES = {
     "hb_he_gemv": (None, [ctx_p, ct_p, vp, ct_p, evk_p]),
     "hb_ctr_hempc_eval": (None, [ctx_p, ct_p, vp, vp, ct_p, ct_p, ct_p, ct_p, evk_p]),
     "hb_ctr_hempc_eval_host": (None, [ctx_p, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp, evk_p, vp]),
+    "hb_pk_upload": (None, [ctx_p, evk_p, vp, vp]),
+    "hb_sk_upload": (None, [ctx_p, C.POINTER(HbSk), vp]),
+    "hb_sk_free": (None, [ctx_p, C.POINTER(HbSk)]),
+    "hb_he_enc_pk": (None, [ctx_p, ct_p, vp, C.c_double, evk_p, vp, vp, vp]),
+    "hb_he_dec": (None, [ctx_p, vp, ct_p, C.POINTER(HbSk)]),
     "hb_ntt_forward": (None, [ctx_p, vp, vp, C.c_size_t, C.c_uint, C.c_uint, C.c_int]),
     "hb_ntt_inverse": (None, [ctx_p, vp, vp, C.c_size_t, C.c_uint, C.c_uint]),
     "hb_ntt_forward_host": (None, [ctx_p, vp, vp, C.c_size_t, C.c_uint, C.c_uint, C.c_int]),

@@ -160,10 +160,10 @@ struct Launch {
     launch(c, "k_poly_ntt", hbdev::k_poly_ntt<LOGN>, (unsigned)(npoly * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, src, stride, W, out, c->dt, D);
   }
   static void ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, unsigned g, unsigned ginv, const ulonglong2 *evk,
-                      uint64_t *chat, unsigned D, unsigned batch) {
+                      unsigned key_limbs, uint64_t *chat, unsigned D, unsigned batch) {
     want_smem(hbdev::k_ks_limb<LOGN>, 2 * G::SMEM_BYTES);
     launch(c, "k_ks_limb", hbdev::k_ks_limb<LOGN>, (unsigned)((size_t)batch * D * G::C), G::THREADS, 2 * G::SMEM_BYTES, G::C, src, bstride, W,
-           g, ginv, evk, c->ht.dimevk, chat, c->dt, D);
+           g, ginv, evk, key_limbs, chat, c->dt, D);
   }
   static void ks_baby(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hbdev::BabySet &S, uint64_t *chat, size_t jstride,
                       unsigned D, unsigned batch) {
@@ -171,9 +171,10 @@ struct Launch {
     launch(c, "k_ks_baby", hbdev::k_ks_baby<LOGN>, (unsigned)((size_t)batch * D * G::C), G::THREADS, 2 * G::SMEM_BYTES, G::C, src, bstride, W,
            S, c->ht.dimevk, chat, jstride, c->dt, D);
   }
-  static void mulpt_limb(hb_ctx *c, const uint64_t *ct, int W, const ulonglong2 *pthat, uint64_t *chat, unsigned D, unsigned batch) {
+  static void mulpt_limb(hb_ctx *c, const uint64_t *ct, size_t poly_stride, int W, const ulonglong2 *pthat, uint64_t *chat, unsigned D,
+                         size_t npoly) {
     want_smem(hbdev::k_mulpt_limb<LOGN>, G::SMEM_BYTES);
-    launch(c, "k_mulpt_limb", hbdev::k_mulpt_limb<LOGN>, (unsigned)((size_t)batch * 2 * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, ct, W, pthat,
+    launch(c, "k_mulpt_limb", hbdev::k_mulpt_limb<LOGN>, (unsigned)(npoly * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, ct, poly_stride, W, pthat,
            chat, c->dt, D);
   }
   static void mulacc_intt(hb_ctx *c, const uint64_t *hat, size_t jstride, const ulonglong2 *pthat, unsigned n1, uint64_t *chat,
@@ -203,9 +204,10 @@ static void do_poly_ntt(hb_ctx *c, const uint64_t *src, size_t stride, int W, ui
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
 }
+// key_limbs: limbs per half of the key array (dimevk for evaluation keys, dim for an uploaded public key)
 static void do_ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, unsigned g, unsigned ginv, const ulonglong2 *evk,
-                       uint64_t *chat, unsigned D, unsigned batch) {
-#define X(L) case L: Launch<L>::ks_limb(c, src, bstride, W, g, ginv, evk, chat, D, batch); break;
+                       unsigned key_limbs, uint64_t *chat, unsigned D, unsigned batch) {
+#define X(L) case L: Launch<L>::ks_limb(c, src, bstride, W, g, ginv, evk, key_limbs, chat, D, batch); break;
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
 }
@@ -215,8 +217,9 @@ static void do_ks_baby(hb_ctx *c, const uint64_t *src, size_t bstride, int W, co
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
 }
-static void do_mulpt_limb(hb_ctx *c, const uint64_t *ct, int W, const ulonglong2 *pthat, uint64_t *chat, unsigned D, unsigned batch) {
-#define X(L) case L: Launch<L>::mulpt_limb(c, ct, W, pthat, chat, D, batch); break;
+static void do_mulpt_limb(hb_ctx *c, const uint64_t *ct, size_t poly_stride, int W, const ulonglong2 *pthat, uint64_t *chat, unsigned D,
+                          size_t npoly) {
+#define X(L) case L: Launch<L>::mulpt_limb(c, ct, poly_stride, W, pthat, chat, D, npoly); break;
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
 }
@@ -734,7 +737,7 @@ extern "C" void hb_he_moddown(hb_ctx *ctx, hb_ct *ct) { rescale_like(ctx, ct, 0,
 static void mulpt_with_hat(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const ulonglong2 *pthat, unsigned D, double ptnu) {
   const int W = hb::words_of_level(ctx->ht, src->l), k = ctx->ht.logq_l[src->l];
   uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, (size_t)src->batch * 2 * D * ctx->ht.N * 8);
-  do_mulpt_limb(ctx, src->words, W, pthat, chat, D, src->batch);
+  do_mulpt_limb(ctx, src->words, (size_t)W * ctx->ht.N, W, pthat, chat, D, (size_t)src->batch * 2);
   dst->l = src->l;
   const double nu = src->nu, B = src->B;
   dst->nu = nu * ptnu;
@@ -782,7 +785,7 @@ static void keyswitch_inplace(hb_ctx *ctx, hb_ct *ct, unsigned ginv, const hb_ev
   const int W = hb::words_of_level(h, ct->l), k = h.logq_l[ct->l];
   const size_t bstride = (size_t)2 * W * h.N;
   uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, (size_t)ct->batch * 2 * D * h.N * 8);
-  do_ks_limb(ctx, ct->words + (size_t)W * h.N, bstride, W, inv_odd_mod_2n(ctx, ginv), ginv, (const ulonglong2 *)key->p, chat, D, ct->batch);
+  do_ks_limb(ctx, ct->words + (size_t)W * h.N, bstride, W, inv_odd_mod_2n(ctx, ginv), ginv, (const ulonglong2 *)key->p, h.dimevk, chat, D, ct->batch);
   uint64_t *out = pool_get(ctx, ct_capacity(ctx, ct->batch));
   do_ks_finish(ctx, chat, D, ct->words, nullptr, bstride, W, ginv, out, W, k, ct->batch);
   pool_put(ctx, ct->words);
@@ -821,7 +824,7 @@ extern "C" void hb_he_mul(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b
   do_recon_smod(ctx, dhat, Dm, dpoly, W, k, (size_t)batch * 3, false);      // d0,d1,d2 mod q_l  (he-mult.c:140-142)
   // relinearise d2 with rlk, add d0 and d1 (he-mult.c:40-85)
   uint64_t *chat = wsA;
-  do_ks_limb(ctx, dpoly + 2 * polyw, 3 * polyw, W, 1u, 1u, (const ulonglong2 *)rlk->p, chat, Dk, batch);
+  do_ks_limb(ctx, dpoly + 2 * polyw, 3 * polyw, W, 1u, 1u, (const ulonglong2 *)rlk->p, h.dimevk, chat, Dk, batch);
   const double nu1 = a->nu, nu2 = b->nu, B1 = a->B, B2 = b->B;
   ct->l = l;
   ct->nu = nu1 * nu2;
@@ -1125,6 +1128,107 @@ extern "C" void hb_ctr_hempc_eval_host(hb_ctx *ctx, unsigned batch, unsigned l, 
     up[s].batch = chunk;
     hb_ct_free(ctx, &up[s]);
   }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// client side on the device: he_enc_pk / he_dec (he-encrypt.c:37-74,107-123)
+// ---------------------------------------------------------------------------------------------------------
+static void do_recon_add(hb_ctx *c, const uint64_t *chat, unsigned D, uint64_t *out, int Wout, int k, size_t npoly, unsigned H,
+                         const uint64_t *addw0, const uint64_t *addw1, size_t addw_stride, int Waddw, const int64_t *adds0,
+                         const int64_t *adds1) {
+  const unsigned threads = 128;
+  const size_t total = npoly * c->ht.N;
+  const unsigned grid = (unsigned)((total + threads - 1) / threads);
+  switch (wk_class((k + 63) / 64)) {
+#define X(WKC) case WKC: launch(c, "k_recon_add", hbdev::k_recon_add<WKC>, grid, threads, 0, 1, chat, D, out, Wout, k, c->dt, (unsigned)npoly, H, addw0, addw1, addw_stride, Waddw, adds0, adds1); break;
+    X(1) X(2) X(4) X(8) X(16)
+#undef X
+  }
+}
+
+extern "C" void hb_pk_upload(hb_ctx *ctx, hb_evk *pk, const uint64_t *p0_words, const uint64_t *p1_words) {
+  const hb::HostTables &h = ctx->ht;
+  const size_t polyw = (size_t)h.WC * h.N, half = (size_t)h.dim * h.N;
+  uint64_t *words = (uint64_t *)hb_dev_alloc(ctx, 2 * polyw * 8);
+  uint64_t *raw = (uint64_t *)hb_dev_alloc(ctx, 2 * half * 8);
+  pk->p = (uint64_t *)hb_dev_alloc(ctx, 2 * half * 16);
+  CUDA_OK(cudaMemcpyAsync(words, p0_words, polyw * 8, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_OK(cudaMemcpyAsync(words + polyw, p1_words, polyw * 8, cudaMemcpyHostToDevice, ctx->stream));
+  do_poly_ntt(ctx, words, polyw, (int)h.WC, raw, h.dim, 2);                          // ntt(pk.p_h mod p_d), d < hectx.dim
+  do_shoup_prep(ctx, raw, (ulonglong2 *)pk->p, h.dim, (size_t)2 * h.dim, 1, 0);     // times N^-1, like an evaluation key
+  hb_dev_free(ctx, words);
+  hb_dev_free(ctx, raw);
+}
+
+extern "C" void hb_sk_upload(hb_ctx *ctx, hb_sk *sk, const int64_t *s) {
+  const hb::HostTables &h = ctx->ht;
+  memset(sk, 0, sizeof *sk);
+  uint64_t *words = (uint64_t *)hb_dev_alloc(ctx, (size_t)h.N * 8);
+  sk->hat = (uint64_t *)hb_dev_alloc(ctx, (size_t)h.dimub * h.N * 8);
+  CUDA_OK(cudaMemcpyAsync(words, s, (size_t)h.N * 8, cudaMemcpyHostToDevice, ctx->stream));
+  do_poly_ntt(ctx, words, h.N, 1, sk->hat, h.dimub, 1);
+  hb_dev_free(ctx, words);
+}
+extern "C" void hb_sk_free(hb_ctx *ctx, hb_sk *sk) {
+  hb_dev_free(ctx, sk->hat);
+  for (uint64_t *&p : sk->scaled) { hb_dev_free(ctx, p); p = nullptr; }
+  sk->hat = nullptr;
+}
+
+extern "C" void hb_he_enc_pk(hb_ctx *ctx, hb_ct *ct, const uint64_t *pt_words, double pt_nu, const hb_evk *pk, const int64_t *v,
+                             const int64_t *e0, const int64_t *e1) {
+  need_ct(ct, "hb_he_enc_pk");
+  if (!pk || !pk->p) hb_die("hb_he_enc_pk: public key is not loaded");
+  const hb::HostTables &h = ctx->ht;
+  const unsigned batch = ct->batch, D = h.dim, L = h.L;
+  const size_t N = h.N, ptw = (size_t)h.WC * N;
+  // staging: v, e0, e1 [batch][N] and the plaintexts [batch][WC][N]
+  uint64_t *stage = ws_get(ctx, ctx->wsB, ctx->wsB_bytes, ((size_t)batch * (3 * N + ptw)) * 8);
+  int64_t *dv = (int64_t *)stage, *de0 = dv + (size_t)batch * N, *de1 = de0 + (size_t)batch * N;
+  uint64_t *dpt = (uint64_t *)(de1 + (size_t)batch * N);
+  CUDA_OK(cudaMemcpyAsync(dv, v, (size_t)batch * N * 8, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_OK(cudaMemcpyAsync(de0, e0, (size_t)batch * N * 8, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_OK(cudaMemcpyAsync(de1, e1, (size_t)batch * N * 8, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_OK(cudaMemcpyAsync(dpt, pt_words, (size_t)batch * ptw * 8, cudaMemcpyHostToDevice, ctx->stream));
+  uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, (size_t)batch * 2 * D * N * 8);
+  // both products v pk.p0, v pk.p1 share the transform of v: the key-switch limb kernel with the public key as "key"
+  do_ks_limb(ctx, (const uint64_t *)dv, N, 1, 1u, 1u, (const ulonglong2 *)pk->p, D, chat, D, batch);
+  ct->l = L;
+  const double Delta = std::ldexp(1.0, (int)h.logDelta);
+  ct->nu = pt_nu >= Delta ? pt_nu : Delta;
+  {
+    const double sigma = 3.1915382432114616, hw = 64, n = h.N;     // precomp.c:411-416
+    ct->B = 8 * std::sqrt(2.0) * sigma * n + 6 * sigma * std::sqrt(n) + 16 * sigma * std::sqrt(hw * n);
+  }
+  do_recon_add(ctx, chat, D, ct->words, (int)h.WC, (int)h.logq_l[L], (size_t)batch * 2, 2, dpt, nullptr, ptw, (int)h.WC, de0, de1);
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));      // the host arrays may be reused by the caller
+}
+
+extern "C" void hb_he_dec(hb_ctx *ctx, uint64_t *pt_words, const hb_ct *ct, const hb_sk *sk) {
+  need_ct(ct, "hb_he_dec");
+  if (!sk || !sk->hat) hb_die("hb_he_dec: secret key is not loaded");
+  const hb::HostTables &h = ctx->ht;
+  const unsigned batch = ct->batch, l = ct->l;
+  const unsigned D = (h.logq_l[l] + 1) / 59 + 1;                  // he-encrypt.c:115
+  if (D > h.dimub) hb_die("hb_he_dec: limb count %u outside the prime chain (%u)", D, h.dimub);
+  const int W = hb::words_of_level(h, l), k = h.logq_l[l];
+  const size_t N = h.N;
+  hb_sk *msk = const_cast<hb_sk *>(sk);
+  ulonglong2 *pthat;
+  uint64_t *tmp_scaled = nullptr;
+  if (D < 64 && msk->scaled[D]) pthat = (ulonglong2 *)msk->scaled[D];
+  else {
+    pthat = (ulonglong2 *)hb_dev_alloc(ctx, (size_t)D * N * 16);
+    do_shoup_prep(ctx, sk->hat, pthat, D, D, 2, D);
+    if (D < 64) msk->scaled[D] = (uint64_t *)pthat; else tmp_scaled = (uint64_t *)pthat;
+  }
+  uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, (size_t)batch * D * N * 8);
+  uint64_t *out = ws_get(ctx, ctx->wsB, ctx->wsB_bytes, (size_t)batch * W * N * 8);
+  do_mulpt_limb(ctx, ct->words + (size_t)W * N, (size_t)2 * W * N, W, pthat, chat, D, batch);      // c1 sk
+  do_recon_add(ctx, chat, D, out, W, k, batch, 1, ct->words, nullptr, (size_t)2 * W * N, W, nullptr, nullptr);   // + c0
+  CUDA_OK(cudaMemcpyAsync(pt_words, out, (size_t)batch * W * N * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  if (tmp_scaled) hb_dev_free(ctx, tmp_scaled);
 }
 
 // ---------------------------------------------------------------------------------------------------------

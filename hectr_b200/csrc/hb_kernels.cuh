@@ -205,7 +205,7 @@ k_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const __g
 // =========================================================================================================
 template <int LOGN>
 __global__ void __launch_bounds__(Cfg<LOGN>::THREADS, Cfg<LOGN>::MINBLOCKS)
-k_mulpt_limb(const uint64_t *__restrict__ ct, int W, const ulonglong2 *__restrict__ pthat,
+k_mulpt_limb(const uint64_t *__restrict__ ct, size_t poly_stride, int W, const ulonglong2 *__restrict__ pthat,
              uint64_t *__restrict__ chat, Tables T, unsigned D) {
   typedef Cfg<LOGN> G;
   extern __shared__ __align__(16) uint64_t smem[];
@@ -219,7 +219,7 @@ k_mulpt_limb(const uint64_t *__restrict__ ct, int W, const ulonglong2 *__restric
   const PrimeConsts pc = T.primes[d];
   const Mod m = make_mod(pc.p);
   const uint64_t negW = pc.p - T.pow64[(size_t)d * (T.WC + 1) + W];
-  const uint64_t *poly = ct + (size_t)q * W * G::N;
+  const uint64_t *poly = ct + (size_t)q * poly_stride;     // a ciphertext batch: W*N; one polynomial per instance (he_dec): 2*W*N
   poly_forward<LOGN>(smem, poly, W, 1u, 1u, pc, m, negW, make_tw(T, d, false));
   const ulonglong2 *pt = pthat + (size_t)d * G::N + (size_t)chunk * G::M;
 #pragma unroll 4
@@ -360,6 +360,59 @@ __global__ void k_recon_smod(const uint64_t *__restrict__ chat, unsigned D, uint
   const uint64_t *limbs = chat + (size_t)q * D * N + i;
   uint64_t acc[WK];
   crt_low<WK, PRE>([&](unsigned d) { return limbs[(size_t)d * N]; }, D, T, acc);
+  sext_bits<WK>(acc, k);
+  uint64_t *o = out + (size_t)q * Wout * N + i;
+#pragma unroll
+  for (int w = 0; w < WK; w++)
+    if (w < Wout) o[(size_t)w * N] = acc[w];
+}
+
+// Reconstruction plus addends, for the two client-side products:
+//   he_enc_pk (he-encrypt.c:37-74):  c0 = smod(v pk.p0 + m + e0, q_L),  c1 = smod(v pk.p1 + e1, q_L)     H = 2
+//   he_dec    (he-encrypt.c:107-123): m = smod(c1 sk + c0, q_l)                                           H = 1
+// chat[inst][H][D][N] pre-weighted limbs of the product(s); addw_h: optional multiword addend of half h (instance stride
+// given, Waddw words), adds_h: optional one-word signed addend [inst][N] (the sampled errors).  out[inst][H][Wout][N].
+template <int WK>
+__global__ void k_recon_add(const uint64_t *__restrict__ chat, unsigned D, uint64_t *__restrict__ out, int Wout, int k, Tables T,
+                            unsigned npoly, unsigned H, const uint64_t *__restrict__ addw0, const uint64_t *__restrict__ addw1,
+                            size_t addw_stride, int Waddw, const int64_t *__restrict__ adds0, const int64_t *__restrict__ adds1) {
+  const unsigned N = T.N;
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)npoly * N) return;
+  const unsigned q = gid / N, i = gid % N, inst = q / H, h = q % H;
+  const uint64_t *limbs = chat + (size_t)q * D * N + i;
+  uint64_t acc[WK];
+  crt_low<WK, true>([&](unsigned d) { return limbs[(size_t)d * N]; }, D, T, acc);
+  const uint64_t *aw = h ? addw1 : addw0;
+  const int64_t *as = h ? adds1 : adds0;
+  uint64_t carry = 0;
+  if (aw) {
+    const uint64_t *ap = aw + (size_t)inst * addw_stride + i;
+    uint64_t fill = 0;
+#pragma unroll
+    for (int w = 0; w < WK; w++) {
+      uint64_t a;
+      if (w < Waddw) { a = ap[(size_t)w * N]; fill = (uint64_t)((int64_t)a >> 63); }
+      else a = fill;
+      const uint64_t s1 = acc[w] + a, c1 = s1 < a;
+      const uint64_t s2 = s1 + carry, c2 = s2 < carry;
+      acc[w] = s2;
+      carry = c1 | c2;
+    }
+  }
+  if (as) {
+    const int64_t e = as[(size_t)inst * N + i];
+    const uint64_t fill = (uint64_t)(e >> 63);
+    carry = 0;
+#pragma unroll
+    for (int w = 0; w < WK; w++) {
+      const uint64_t a = w == 0 ? (uint64_t)e : fill;
+      const uint64_t s1 = acc[w] + a, c1 = s1 < a;
+      const uint64_t s2 = s1 + carry, c2 = s2 < carry;
+      acc[w] = s2;
+      carry = c1 | c2;
+    }
+  }
   sext_bits<WK>(acc, k);
   uint64_t *o = out + (size_t)q * Wout * N + i;
 #pragma unroll

@@ -10,7 +10,7 @@ import ctypes as C
 
 import numpy as np
 
-from ._lib import HbCt, HbEvk, HbInfo, HbPt, load_library
+from ._lib import HbCt, HbEvk, HbInfo, HbPt, HbSk, load_library
 
 
 def _ptr(a: np.ndarray):
@@ -245,6 +245,41 @@ class Engine:
             out = np.empty((batch, 2, self.words(l - 1), self.n), dtype=np.uint64)
         self.lib.hb_ctr_hempc_eval_host(self.ctx, batch, l, _ptr(Ka), _ptr(Kb), _ptr(xhat), _ptr(xr), _ptr(uhat),
                                         _ptr(ur), rk.arr, _ptr(out))
+        return out
+
+    # ---- client side on the device (he-encrypt.c) ---------------------------------------------------------
+    def pk(self, p0_words: np.ndarray, p1_words: np.ndarray) -> HbEvk:
+        """he_pk (gpqhe.h:72-76) as words[W_L][N] each -> device transform limbs."""
+        p0 = np.ascontiguousarray(p0_words, dtype=np.uint64)
+        p1 = np.ascontiguousarray(p1_words, dtype=np.uint64)
+        assert p0.shape == p1.shape == (self.info.words_top, self.n)
+        k = HbEvk()
+        self.lib.hb_pk_upload(self.ctx, C.byref(k), _ptr(p0), _ptr(p1))
+        return k
+
+    def sk(self, s: np.ndarray) -> HbSk:
+        s = np.ascontiguousarray(s, dtype=np.int64)
+        assert s.shape == (self.n,)
+        k = HbSk()
+        self.lib.hb_sk_upload(self.ctx, C.byref(k), _ptr(s))
+        return k
+
+    def he_enc_pk(self, pt_words: np.ndarray, pk: HbEvk, v: np.ndarray, e0: np.ndarray, e1: np.ndarray, pt_nu=None) -> Ciphertext:
+        """he_enc_pk with the caller's samples: pt_words[batch][W_L][N], v/e0/e1 int64[batch][N]."""
+        pt_words = np.ascontiguousarray(pt_words, dtype=np.uint64)
+        batch = pt_words.shape[0]
+        assert pt_words.shape == (batch, self.info.words_top, self.n)
+        arrs = [np.ascontiguousarray(a, dtype=np.int64) for a in (v, e0, e1)]
+        assert all(a.shape == (batch, self.n) for a in arrs)
+        ct = Ciphertext(self, batch)
+        self.lib.hb_he_enc_pk(self.ctx, C.byref(ct.h), _ptr(pt_words), float(pt_nu or 2.0 ** self.info.logDelta), C.byref(pk),
+                              _ptr(arrs[0]), _ptr(arrs[1]), _ptr(arrs[2]))
+        return ct
+
+    def he_dec(self, ct: Ciphertext, sk: HbSk) -> np.ndarray:
+        """he_dec -> plaintext words[batch][W_l][N] on the host."""
+        out = np.empty((ct.batch, self.words(ct.l), self.n), dtype=np.uint64)
+        self.lib.hb_he_dec(self.ctx, _ptr(out), C.byref(ct.h), C.byref(sk))
         return out
 
     # ---- limb level -----------------------------------------------------------------------------------------

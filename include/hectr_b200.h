@@ -57,6 +57,11 @@ typedef struct hb_evk {            /* he_evk_t (gpqhe.h:78-82) */
   uint64_t *p;                     /* DEVICE pointer [2][dimevk][N] pairs (key limb, its Shoup quotient) */
 } hb_evk;
 
+typedef struct hb_sk {             /* secret key, poly_mpi_t sk (he-kem.c:31-50), held as transform limbs */
+  uint64_t *hat;                   /* DEVICE [dimub][N]: ntt(sk mod p_d), canonical */
+  uint64_t *scaled[64];            /* DEVICE, built on first use: Shoup pairs of hat * N^-1 (P_D/p_d)^-1 for D limbs */
+} hb_sk;
+
 /* ---- context: hectx_init / hectx_exit (precomp.c:431-453,465-) --------------------------------- */
 hb_ctx *hb_ctx_create(unsigned logn, unsigned logq, unsigned slots, unsigned logDelta, int device);
 void hb_ctx_destroy(hb_ctx *ctx);
@@ -146,6 +151,17 @@ void hb_ctr_hempc_eval(hb_ctx *ctx, hb_ct *up, const double *Ka, const double *K
 void hb_ctr_hempc_eval_host(hb_ctx *ctx, unsigned batch, unsigned l, const double *Ka, const double *Kb,
                             const uint64_t *in_xhat, const uint64_t *in_xr, const uint64_t *in_uhat,
                             const uint64_t *in_ur, const hb_evk *rk, uint64_t *out_up);
+
+/* ---- client side on the device: he_enc_pk / he_dec, he-encrypt.c:37-74,107-123 ------------------ */
+/* Sampling stays with the caller (the reference's deterministic stream defines every ciphertext): v (sample_zo), e0, e1
+ * (sample_error) arrive as one signed word per coefficient, HOST [batch][N]; the plaintexts as HOST [batch][W_L][N]. */
+void hb_pk_upload(hb_ctx *ctx, hb_evk *pk, const uint64_t *p0_words, const uint64_t *p1_words);   /* he_pk: HOST [W_L][N] each */
+void hb_sk_upload(hb_ctx *ctx, hb_sk *sk, const int64_t *s);                                      /* HOST [N] */
+void hb_sk_free(hb_ctx *ctx, hb_sk *sk);
+void hb_he_enc_pk(hb_ctx *ctx, hb_ct *ct, const uint64_t *pt_words, double pt_nu, const hb_evk *pk, const int64_t *v,
+                  const int64_t *e0, const int64_t *e1);
+/* m = smod(c1 sk + c0, q_l): HOST pt_words[batch][W_l][N] (synchronises); the plaintext's nu is ct->nu */
+void hb_he_dec(hb_ctx *ctx, uint64_t *pt_words, const hb_ct *ct, const hb_sk *sk);
 
 /* ---- limb-level entry points (parity tests, NTT microbench) ---------------------------------------- */
 /* ntt / invntt (GPQHE/src/ntt.c:37-73) over nlimbs limbs in DEVICE memory; limb j uses prime d0 + j % D.

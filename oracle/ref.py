@@ -299,6 +299,35 @@ class Ref:
         self.lib.he_dec(C.byref(pt), C.byref(ct), C.byref(sk))
         return pt
 
+    # ---- samplers and the bare polynomial product (client-side parity: he-encrypt.c) -------------------------
+    def _sample(self, fn) -> np.ndarray:
+        p = self.alloc_poly()
+        fn(C.byref(p))
+        out = self.poly_to_words(p, 1)[0].view(np.int64).copy()
+        self.lib.poly_mpi_free(C.byref(p))
+        return out
+
+    def sample_zo(self) -> np.ndarray:
+        """sample_zo (sample.c:123-131) -> int64[N]; advances the deterministic stream like he_enc_pk's first draw."""
+        return self._sample(self.lib.sample_zo)
+
+    def sample_error(self) -> np.ndarray:
+        """sample_error (sample.c:74-82) -> int64[N]."""
+        return self._sample(self.lib.sample_error)
+
+    def poly_mul_words(self, a: PolyMpi, b_words: np.ndarray, dim: int, logm: int, W: int) -> np.ndarray:
+        """poly_mul(a, b, dim, 2^logm) (poly.c:84-107) -> words[W][N]."""
+        b = self.alloc_poly()
+        self.words_to_poly(b, b_words)
+        r = self.alloc_poly()
+        q = MPI(self.hlp.ref_pow2(C.c_uint(logm)))
+        self.lib.poly_mul(C.byref(r), C.byref(a), C.byref(b), C.c_uint(dim), q)
+        self.gcry.gcry_mpi_release(q)
+        out = self.poly_to_words(r, W)
+        self.lib.poly_mpi_free(C.byref(b))
+        self.lib.poly_mpi_free(C.byref(r))
+        return out
+
     # ---- evaluation (each returns / mutates reference structs) --------------------------------------
     def add(self, a, b):
         r = self.alloc_ct()

@@ -252,3 +252,48 @@ def test_mul_relin(cfgA):
             want = ref.mul(_ref_ct(ref, a[bi], l), _ref_ct(ref, b[bi], l), rlk)
             assert np.array_equal(got[bi], ref.ct_to_words(want)), (l, bi)
     ekeys.free()
+
+
+def test_enc_pk_and_dec_on_device(cfgA):
+    """he_enc_pk / he_dec on the device with the REFERENCE's samples (sampling order defines every
+    ciphertext, so the host draws v, e0, e1 in he_enc_pk's order: sample_zo, sample_error, sample_error)."""
+    from conftest import ints_to_words, words_to_ints
+    ref, eng, pk, sk = cfgA["ref"], cfgA["eng"], cfgA["pk"], cfgA["sk"]
+    rng = np.random.default_rng(61)
+    S, L, n = 16, ref.L, ref.n
+    W, k = eng.words(L), eng.logq(L)
+    q = 1 << k
+    B = 3
+    msgs = rng.standard_normal((B, S)) + 1j * rng.standard_normal((B, S))
+    pts = [ref.encode(m) for m in msgs]
+    pt_words = np.stack([ref.poly_to_words(p.m, W) for p in pts])
+    v = np.stack([ref.sample_zo() for _ in range(B)])          # the draws interleave per instance in the reference;
+    e0 = np.stack([ref.sample_error() for _ in range(B)])      # here any fixed order does: the arithmetic is what is compared
+    e1 = np.stack([ref.sample_error() for _ in range(B)])
+    assert set(np.unique(v)) <= {-1, 0, 1}
+    dpk = eng.pk(ref.poly_to_words(pk.p0, W), ref.poly_to_words(pk.p1, W))
+    got = eng.he_enc_pk(pt_words, dpk, v, e0, e1)
+    assert got.l == L
+    gw = got.download()
+    smod = lambda x: ((x + q // 2) % q) - q // 2
+    for b in range(B):
+        vw = v[b].view(np.uint64)[None]
+        prod0 = words_to_ints(ref.poly_mul_words(pk.p0, vw, ref.dim, k, W))          # poly_mul(pk.p0, v, hectx.dim, q)
+        prod1 = words_to_ints(ref.poly_mul_words(pk.p1, vw, ref.dim, k, W))
+        m = words_to_ints(pt_words[b])
+        c0 = [smod(prod0[i] + m[i] + int(e0[b, i])) for i in range(n)]
+        c1 = [smod(prod1[i] + int(e1[b, i])) for i in range(n)]
+        assert np.array_equal(gw[b, 0], ints_to_words(c0, W)), b
+        assert np.array_equal(gw[b, 1], ints_to_words(c1, W)), b
+    # he_dec: device against the reference on (a) the device-encrypted batch and (b) a reference-encrypted ciphertext
+    dsk = eng.sk(ref.poly_to_words(sk, 1)[0].view(np.int64))
+    dec = eng.he_dec(got, dsk)
+    for b in range(B):
+        want = ref.dec(ref.ct_from_words(gw[b], L, nu=got.nu, B=got.B), sk)
+        assert np.array_equal(dec[b], ref.poly_to_words(want.m, W)), b
+        assert np.abs(ref.decode(want) - msgs[b]).max() < 1e-9          # and it decrypts to the message
+    cref = ref.enc_pk(pts[0], pk)
+    for l in (L, L - 1):
+        wl = eng.words(l)
+        assert np.array_equal(eng.he_dec(eng.ct(ref.ct_to_words(cref), l), dsk)[0], ref.poly_to_words(ref.dec(cref, sk).m, wl)), l
+        ref.moddown(cref)
