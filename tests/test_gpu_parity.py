@@ -297,3 +297,66 @@ def test_enc_pk_and_dec_on_device(cfgA):
         wl = eng.words(l)
         assert np.array_equal(eng.he_dec(eng.ct(ref.ct_to_words(cref), l), dsk)[0], ref.poly_to_words(ref.dec(cref, sk).m, wl)), l
         ref.moddown(cref)
+
+
+def test_config_C_full_chain_ring(ref_available):
+    """BASELINE configs[2]: N = 2^15, q = 2^881 (the security-table maximum, precomp.c:63), Delta = 2^50: L = 17, key
+    switches over 47 limbs, 14-word coefficients -- the multiword reconstruction and key-switch tail, clusters of 4 CTAs
+    per limb.  he_mul + relinearise, he_rs and he_conj at the top level and at level 1 against the compiled reference."""
+    from oracle.ref import Ref
+    from hectr_b200 import Engine
+    P = (15, 881, 16, 50)
+    ref = Ref.get(*P)
+    eng = Engine(*P)
+    try:
+        i = eng.info
+        assert (i.L, i.dim, i.dimevk, i.dimub) == (ref.L, ref.dim, ref.dimevk, ref.dimub) == (17, 16, 47, 61)
+        pk, sk = ref.keypair()
+        rlk, ck = ref.genrlk(sk), ref.genck(sk)
+        erlk, eck = eng.keys(ref.evk_to_array(rlk)), eng.keys(ref.evk_to_array(ck))
+        rng = np.random.default_rng(71)
+        for l in (ref.L, 1):
+            W, k = eng.words(l), eng.logq(l)
+            w = random_ct_words(rng, 2, W, eng.n, k)
+            a, b = _ref_ct(ref, w[0], l), _ref_ct(ref, w[1], l)
+            want = ref.mul(a, b, rlk)
+            got = eng.he_mul(eng.ct(w[0], l), eng.ct(w[1], l), erlk)
+            assert np.array_equal(got.download()[0], ref.ct_to_words(want)), ("he_mul", l)
+            ref.rs(want)
+            eng.he_rs(got)
+            assert got.l == want.l == l - 1
+            assert np.array_equal(got.download()[0], ref.ct_to_words(want)), ("he_rs", l)
+            wantc = ref.conj(_ref_ct(ref, w[0], l), ck)
+            gotc = eng.he_conj(eng.ct(w[0], l), eck)
+            assert np.array_equal(gotc.download()[0], ref.ct_to_words(wantc)), ("he_conj", l)
+        erlk.free()
+        eck.free()
+    finally:
+        eng.close()
+
+
+def test_config_D_gemv_32_slots(ref_available):
+    """BASELINE configs[3] (horizon 10 -> slots = 32): n1 = 8 baby steps (two hoisted launches of four rotations), n2 = 4
+    giant steps, 32 rotation keys, dense complex matrix; he_gemv against the compiled reference."""
+    from oracle.ref import Ref
+    from hectr_b200 import Engine
+    P = (12, 109, 32, 50)
+    ref = Ref.get(*P)
+    eng = Engine(*P)
+    try:
+        pk, sk = ref.keypair()
+        rk = ref.genrk(sk)
+        keys = eng.keys(np.stack([ref.evk_to_array(rk[i]) for i in range(32)]))
+        rng = np.random.default_rng(73)
+        A = rng.standard_normal((32, 32)) + 1j * rng.standard_normal((32, 32))
+        v = rng.standard_normal(32) + 1j * rng.standard_normal(32)
+        ct = ref.enc_pk(ref.encode(v), pk)
+        want = ref.gemv(A, ct, rk)
+        got = eng.he_gemv(A, eng.ct(ref.ct_to_words(ct), ref.L, nu=ct.nu, B=ct.B), keys)
+        assert got.l == want.l
+        assert np.array_equal(got.download()[0], ref.ct_to_words(want))
+        dec = ref.decode(ref.dec(want, sk))
+        assert np.abs(dec - A @ v).max() < 1e-6
+        keys.free()
+    finally:
+        eng.close()
