@@ -177,6 +177,7 @@ def run_ours(args):
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG", "WARN")      # keeps NCCL's version banner off stdout (one JSON line only)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from hectr_b200.sharding import gather_results, shard_range
     total = args.instances
@@ -309,6 +310,14 @@ def run_ours(args):
         except Exception as ex:  # pragma: no cover
             ntt = {"error": str(ex)}
 
+    secondary = {}
+    if not args.no_ntt:
+        for nm, fn in (("config_C", config_c_bench), ("config_D", config_d_bench)):
+            try:
+                secondary[nm] = fn(local)
+            except Exception as ex:  # pragma: no cover
+                secondary[nm] = {"error": str(ex)}
+
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -324,6 +333,7 @@ def run_ours(args):
         "roofline": roofline,
         "cpu_baseline": cpu,
         "ntt": ntt,
+        **secondary,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
@@ -362,6 +372,74 @@ def ntt_microbench(device: int, peak: float, logn: int = 16, nlimbs: int = 1024,
     eng.close()
     return {"metric": "N=2^16 NTT limbs/s", "logn": logn, "limbs_per_launch": nlimbs, "primes": D,
             "algorithmic_bytes_per_limb": 16 * n, "l2": f"{host.nbytes >> 20} MiB in + out per launch (> L2)", **res}
+
+
+# ------------------------------------------------------------------------------------------------------
+# secondary: BASELINE configs[2] (ct x ct + relinearise + rescale, rotation at N=2^15, q=2^881) and configs[3]
+# (rotation-sum matvec at 32/64/128 slots).  Parity for both is in tests/test_gpu_parity.py; these are throughput only.
+# ------------------------------------------------------------------------------------------------------
+def _rand_ct(rng, batch, W, n, k):
+    buf = np.empty((batch, 2, W, n), dtype=np.uint64)
+    synth_ct_into(buf, rng, k)
+    return buf
+
+
+def _rand_keys(eng, rng, nkeys):
+    primes = eng.primes()
+    keys = np.empty((nkeys, 2, eng.info.dimevk, eng.n), dtype=np.uint64)
+    for d in range(eng.info.dimevk):
+        keys[:, :, d, :] = rng.integers(0, int(primes[d]), size=(nkeys, 2, eng.n), dtype=np.uint64)
+    return keys
+
+
+def config_c_bench(device: int, batch: int = 8, reps: int = 3):
+    from hectr_b200 import Engine
+    eng = Engine(15, 881, 16, 50, device=device)
+    lib, ctx = eng.lib, eng.ctx
+    rng = np.random.default_rng(5)
+    l = eng.L
+    W, k = eng.words(l), eng.logq(l)
+    keys = eng.keys(_rand_keys(eng, rng, 2))
+    x, y = eng.ct(_rand_ct(rng, batch, W, eng.n, k), l), eng.ct(_rand_ct(rng, batch, W, eng.n, k), l)
+    out = eng.ct(batch=batch)
+    res = {"logn": 15, "logq": 881, "level": l, "batch": batch, "limbs_keyswitch": int(lib.hb_dim_keyswitch(ctx, l)),
+           "limbs_mul": int(lib.hb_dim_mul(ctx, l))}
+    for name, fn in (("mul_relin_rs", lambda: (eng.he_mul(x, y, keys, out=out), eng.he_rs(out))),
+                     ("rot", lambda: eng.he_rot(x, 1, keys))):
+        fn()
+        eng.sync()
+        lib.hb_timer_start(ctx)
+        for _ in range(reps):
+            fn()
+        ms = float(lib.hb_timer_stop_ms(ctx)) / reps
+        res[name] = {"ms_per_batch": ms, "per_s": batch / (ms / 1e3)}
+    keys.free()
+    eng.close()
+    return res
+
+
+def config_d_bench(device: int, batch: int = 256, reps: int = 2):
+    from hectr_b200 import Engine
+    res = {"logn": 12, "logq": 109, "batch": batch}
+    for slots in (32, 64, 128):
+        eng = Engine(12, 109, slots, 50, device=device)
+        lib, ctx = eng.lib, eng.ctx
+        rng = np.random.default_rng(6)
+        l = eng.L
+        keys = eng.keys(_rand_keys(eng, rng, slots))
+        A = rng.standard_normal((slots, slots)) + 1j * rng.standard_normal((slots, slots))
+        x = eng.ct(_rand_ct(rng, batch, eng.words(l), eng.n, eng.logq(l)), l)
+        out = eng.ct(batch=batch)
+        eng.he_gemv(A, x, keys, out=out)          # builds the plan (host encode of the diagonals)
+        eng.sync()
+        lib.hb_timer_start(ctx)
+        for _ in range(reps):
+            eng.he_gemv(A, x, keys, out=out)
+        ms = float(lib.hb_timer_stop_ms(ctx)) / reps
+        res[f"slots{slots}"] = {"ms_per_batch": ms, "gemv_per_s": batch / (ms / 1e3)}
+        keys.free()
+        eng.close()
+    return res
 
 
 # ------------------------------------------------------------------------------------------------------
