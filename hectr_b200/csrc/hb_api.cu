@@ -293,6 +293,16 @@ static void do_ks_finish(hb_ctx *c, const uint64_t *chat, unsigned D, const uint
       for (unsigned w = 0; w < 2 && w < h.WP; w++) F.kphat[e][w] = h.ks_phat[(size_t)e * h.WP + w];
     }
     for (unsigned w = 0; w < 2 && w < h.WP; w++) F.kP[w] = h.ks_P[w];
+    {
+      // t = (x - R) P^-1 mod 2^128 is linear in every term of x and R: fold P^-1 into the constants once
+      typedef unsigned __int128 u128;
+      const u128 pinv = ((u128)F.Pinv[1] << 64) | F.Pinv[0];
+      auto fold = [&](uint64_t (&w)[2]) { const u128 v = ((((u128)w[1]) << 64) | w[0]) * pinv; w[0] = (uint64_t)v; w[1] = (uint64_t)(v >> 64); };
+      for (unsigned d = 0; d < D; d++) fold(F.phat[d]);
+      for (unsigned e = 0; e < h.dim; e++) fold(F.kphat[e]);
+      fold(F.PD);
+      fold(F.kP);
+    }
     bool done = true;
 #define KSF(DD, MM)                                                                                                             \
     if (D == DD && h.dim == MM) {                                                                                               \

@@ -647,17 +647,19 @@ __global__ void __launch_bounds__(128) k_ks_finish_fast(const uint64_t *__restri
 #pragma unroll
   for (int d = 0; d < D; d++) {
     const uint64_t y = a[d];                                     // already a_d (P_D/p_d)^-1, below 2p
-    Fx += __umul64hi(y, F.mu[d]);
+    Fx += (uint64_t)hi32(y) * hi32(F.mu[d]);
     mac_low<WK>(acc, y, F.phat[d]);
   }
 #pragma unroll
   for (int e = 0; e < DIM; e++) {
     const Mod m = make_mod(F.p[e]);
     const uint64_t z = shoup_lazy(a[e], F.kinv[e], F.kinvq[e], m);
-    Fr += __umul64hi(z, F.mu[e]);
+    Fr += (uint64_t)hi32(z) * hi32(F.mu[e]);
     mac_low<WK>(Rl, z, F.kphat[e]);
   }
-  const uint64_t ONE = 1ULL << 56, HALF = 1ULL << 55, MASK = ONE - 1, MARGIN = 64;
+  // The fractions come from the high halves only (one IMAD.WIDE per term): each term underestimates y mu / 2^64 by less
+  // than 2^33 + 3 units, at most 12 terms -> below 2^37; a sum within MARGIN of a decision boundary takes the exact tail.
+  const uint64_t ONE = 1ULL << 56, HALF = 1ULL << 55, MASK = ONE - 1, MARGIN = 1ULL << 38;
   const uint64_t fx = (Fx + HALF) & MASK, fr = Fr & MASK;
   const bool unsure = fx < MARGIN || fx > ONE - MARGIN || fr < MARGIN || fr > ONE - MARGIN ||
                       (fr > HALF - MARGIN && fr < HALF + MARGIN);
@@ -668,11 +670,10 @@ __global__ void __launch_bounds__(128) k_ks_finish_fast(const uint64_t *__restri
   }
   const uint64_t v = (Fx + HALF) >> 56, v2 = Fr >> 56;
   const bool roundup = fr > HALF;
-  // diff = (acc - v P_D) - (Rl - v2 P)  (mod 2^(64 WK));  t = diff * P^-1
+  // t = (acc - v P_D) - (Rl - v2 P)  (mod 2^(64 WK)), every constant already times P^-1 (do_ks_finish)
   uint64_t t[WK];
   if (WK == 1) {
-    const uint64_t diff = acc[0] - v * F.PD[0] - Rl[0] + v2 * F.kP[0];
-    t[0] = diff * F.Pinv[0];
+    t[0] = acc[0] - v * F.PD[0] - Rl[0] + v2 * F.kP[0];
   } else {
     uint64_t dlt[WK], sub[WK];
 #pragma unroll
@@ -683,9 +684,8 @@ __global__ void __launch_bounds__(128) k_ks_finish_fast(const uint64_t *__restri
     A -= ((unsigned __int128)dlt[WK - 1] << 64) | dlt[0];
     A -= ((unsigned __int128)Rl[WK - 1] << 64) | Rl[0];
     A += ((unsigned __int128)sub[WK - 1] << 64) | sub[0];
-    const uint64_t d0 = (uint64_t)A, d1 = (uint64_t)(A >> 64);
-    t[0] = d0 * F.Pinv[0];
-    t[WK - 1] = __umul64hi(d0, F.Pinv[0]) + d0 * F.Pinv[1] + d1 * F.Pinv[0];
+    t[0] = (uint64_t)A;
+    t[WK - 1] = (uint64_t)(A >> 64);
   }
   ks_tail<WK>(t, roundup, add, add_bstride, Wadd, ginv, N, b, h, i, out, Wout, k);
 }

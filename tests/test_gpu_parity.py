@@ -360,3 +360,26 @@ def test_config_D_gemv_32_slots(ref_available):
         keys.free()
     finally:
         eng.close()
+
+
+def test_fast_tail_equals_exact_tail(cfgA, monkeypatch):
+    """The fixed-point key-switch tail (fractions from the high halves, exact fallback near a decision boundary) against
+    the multiword tail on 2 x 256 x 4096 coefficients per level: enough for a few dozen threads to land inside the margin
+    (about 1e-5 per coefficient), so both branches and the hand-off between them are exercised."""
+    from hectr_b200 import Engine
+    eng, keys = cfgA["eng"], cfgA["keys"]
+    rng = np.random.default_rng(83)
+    S = 16
+    monkeypatch.setenv("HB_KS_EXACT", "1")
+    eng2 = Engine(*A_PARAMS)
+    try:
+        rk_arr = np.stack([cfgA["ref"].evk_to_array(cfgA["rk"][i]) for i in range(S)])
+        keys2 = eng2.keys(rk_arr)
+        for l in (2, 1):
+            a = random_ct_words(rng, 256, eng.words(l), eng.n, eng.logq(l))
+            fast = eng.he_rot(eng.ct(a, l), 5, keys).download()
+            exact = eng2.he_rot(eng2.ct(a, l), 5, keys2).download()
+            assert np.array_equal(fast, exact), l
+        keys2.free()
+    finally:
+        eng2.close()
