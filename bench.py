@@ -143,23 +143,25 @@ def pinned_array(eng, shape):
 
 
 # algorithmic bytes per launch, config A, batch B instances per launch
-def algorithmic_bytes(kernel: str, B: int, n: int, W: int, D_ks: int, D_pt: int):
+def algorithmic_bytes(kernel: str, B: int, n: int, W: int, D_ks: int, D_pt: int, n1: int = 4, n2: int = 4):
+    """SURVEY.md 8(d) per-unit figures x the units one launch processes.  The grouped he_gemv schedule puts the n1 baby
+    rotations (resp. the n2 giant steps) of one matvec into ONE launch, so a launch is n1 (n2) key switches / products."""
     ct_poly = n * W * 8
     hat = B * 2 * D_pt * n * 8
+    keyswitch = B * (2 * ct_poly + 2 * ct_poly) + 2 * D_ks * n * 8      # read d0,d1 + write c0,c1 + key shared by the batch
     table = {
-        # one key switch: read d0,d1 + write c0,c1 + keys shared over the batch (2*D*N*8 / B per unit)
-        "k_ks_limb": B * (2 * ct_poly + 2 * ct_poly) + 2 * D_ks * n * 8,
-        # the n1 = 4 baby rotations of one he_gemv in one launch (one shared forward transform): 4 key switches
-        "k_ks_baby": 4 * (B * (2 * ct_poly + 2 * ct_poly) + 2 * D_ks * n * 8),
-        "k_ks_finish": B * (2 * ct_poly + 2 * ct_poly) + 2 * D_ks * n * 8,
-        "k_ks_finish_fast": B * (2 * ct_poly + 2 * ct_poly) + 2 * D_ks * n * 8,
+        "k_ks_limb": n2 * keyswitch,                  # the n2 giant-step key switches
+        "k_ks_baby": n1 * keyswitch,                  # the n1 baby rotations (one shared forward transform)
+        "k_ks_finish": n1 * keyswitch,
+        "k_ks_finish_fast": n1 * keyswitch,           # second half of the same key switches (n1 == n2 at config A)
         # one ct x pt: ct in + ct out + plaintext (shared)
         "k_mulpt_limb": B * (2 * ct_poly + 2 * ct_poly) + D_pt * n * 8,
-        "k_recon_smod": B * (2 * ct_poly + 2 * ct_poly) + D_pt * n * 8,
-        # memoised gemv: rotated ct in -> NTT limbs out; n1 limb sets in -> one limb set out
-        "k_poly_ntt": 4 * (B * 2 * ct_poly + hat),        # the four rotated ciphertexts in one launch
-        "k_mulacc_intt": 4 * hat + hat,
+        "k_recon_smod": n2 * (B * 2 * ct_poly + hat),
+        # memoised gemv: rotated ct in -> NTT limbs out; n1 limb sets in -> n2 limb sets out
+        "k_poly_ntt": n1 * (B * 2 * ct_poly + hat),
+        "k_mulacc_intt": n1 * hat + n2 * hat,
         "k_ct_addsub": B * 3 * 2 * ct_poly,
+        "k_ct_sum": B * (n2 + 1) * 2 * ct_poly,
         "k_ct_rescale": B * 2 * 2 * ct_poly,
     }
     return table.get(kernel)

@@ -159,11 +159,11 @@ struct Launch {
     want_smem(hbdev::k_poly_ntt<LOGN>, G::SMEM_BYTES);
     launch(c, "k_poly_ntt", hbdev::k_poly_ntt<LOGN>, (unsigned)(npoly * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, src, stride, W, out, c->dt, D);
   }
-  static void ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, unsigned g, unsigned ginv, const ulonglong2 *evk,
+  static void ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hbdev::KsGroups &S,
                       unsigned key_limbs, uint64_t *chat, unsigned D, unsigned batch) {
     want_smem(hbdev::k_ks_limb<LOGN>, 2 * G::SMEM_BYTES);
     launch(c, "k_ks_limb", hbdev::k_ks_limb<LOGN>, (unsigned)((size_t)batch * D * G::C), G::THREADS, 2 * G::SMEM_BYTES, G::C, src, bstride, W,
-           g, ginv, evk, key_limbs, chat, c->dt, D);
+           S, key_limbs, chat, c->dt, D);
   }
   static void ks_baby(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hbdev::BabySet &S, uint64_t *chat, size_t jstride,
                       unsigned D, unsigned batch) {
@@ -177,11 +177,11 @@ struct Launch {
     launch(c, "k_mulpt_limb", hbdev::k_mulpt_limb<LOGN>, (unsigned)(npoly * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, ct, poly_stride, W, pthat,
            chat, c->dt, D);
   }
-  static void mulacc_intt(hb_ctx *c, const uint64_t *hat, size_t jstride, const ulonglong2 *pthat, unsigned n1, uint64_t *chat,
-                          unsigned D, unsigned batch) {
+  static void mulacc_intt(hb_ctx *c, const uint64_t *hat, size_t jstride, const ulonglong2 *pthat, size_t pthat_gstride, unsigned n1,
+                          unsigned ngroups, uint64_t *chat, unsigned D, unsigned batch) {
     want_smem(hbdev::k_mulacc_intt<LOGN>, G::SMEM_BYTES);
-    launch(c, "k_mulacc_intt", hbdev::k_mulacc_intt<LOGN>, (unsigned)((size_t)batch * 2 * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, hat, jstride,
-           pthat, n1, chat, c->dt, D);
+    launch(c, "k_mulacc_intt", hbdev::k_mulacc_intt<LOGN>, (unsigned)((size_t)ngroups * batch * 2 * D * G::C), G::THREADS, G::SMEM_BYTES, G::C,
+           hat, jstride, pthat, pthat_gstride, n1, batch * 2, chat, c->dt, D);
   }
   static void tensor_intt(hb_ctx *c, const uint64_t *hatA, const uint64_t *hatB, uint64_t *dhat, unsigned D, unsigned batch) {
     want_smem(hbdev::k_tensor_intt<LOGN>, G::SMEM_BYTES);
@@ -205,11 +205,19 @@ static void do_poly_ntt(hb_ctx *c, const uint64_t *src, size_t stride, int W, ui
 #undef X
 }
 // key_limbs: limbs per half of the key array (dimevk for evaluation keys, dim for an uploaded public key)
-static void do_ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, unsigned g, unsigned ginv, const ulonglong2 *evk,
-                       unsigned key_limbs, uint64_t *chat, unsigned D, unsigned batch) {
-#define X(L) case L: Launch<L>::ks_limb(c, src, bstride, W, g, ginv, evk, key_limbs, chat, D, batch); break;
+// batch = instances in the launch (all groups); S.gbatch instances per group
+static void do_ks_limb_g(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hbdev::KsGroups &S, unsigned key_limbs,
+                         uint64_t *chat, unsigned D, unsigned batch) {
+#define X(L) case L: Launch<L>::ks_limb(c, src, bstride, W, S, key_limbs, chat, D, batch); break;
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
+}
+static void do_ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, unsigned g, unsigned ginv, const ulonglong2 *evk,
+                       unsigned key_limbs, uint64_t *chat, unsigned D, unsigned batch) {
+  hbdev::KsGroups S;
+  memset(&S, 0, sizeof S);
+  S.evk[0] = evk; S.g[0] = g; S.ginv[0] = ginv; S.gbatch = batch;
+  do_ks_limb_g(c, src, bstride, W, S, key_limbs, chat, D, batch);
 }
 static void do_ks_baby(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hbdev::BabySet &S, uint64_t *chat, size_t jstride,
                        unsigned D, unsigned batch) {
@@ -223,9 +231,10 @@ static void do_mulpt_limb(hb_ctx *c, const uint64_t *ct, size_t poly_stride, int
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
 }
-static void do_mulacc_intt(hb_ctx *c, const uint64_t *hat, size_t jstride, const ulonglong2 *pthat, unsigned n1, uint64_t *chat,
-                           unsigned D, unsigned batch) {
-#define X(L) case L: Launch<L>::mulacc_intt(c, hat, jstride, pthat, n1, chat, D, batch); break;
+// ngroups giant steps in one launch: group i uses the diagonals pthat + i * pthat_gstride and writes chat[i][batch][2][D][N]
+static void do_mulacc_intt(hb_ctx *c, const uint64_t *hat, size_t jstride, const ulonglong2 *pthat, size_t pthat_gstride, unsigned n1,
+                           unsigned ngroups, uint64_t *chat, unsigned D, unsigned batch) {
+#define X(L) case L: Launch<L>::mulacc_intt(c, hat, jstride, pthat, pthat_gstride, n1, ngroups, chat, D, batch); break;
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
 }
@@ -263,17 +272,17 @@ static void do_recon_smod(hb_ctx *c, const uint64_t *chat, unsigned D, uint64_t 
 
 template <int WKC>
 static void ks_finish_wp(hb_ctx *c, unsigned grid, unsigned threads, const uint64_t *chat, unsigned D, const uint64_t *add0,
-                         const uint64_t *add1, size_t add_bstride, int Wadd, unsigned ginv, uint64_t *out, int Wout, int k,
+                         const uint64_t *add1, size_t add_bstride, int Wadd, const hbdev::TailGroups &TG, uint64_t *out, int Wout, int k,
                          unsigned batch) {
   switch (wp_class(c->ht.WP)) {
-#define X(WPC) case WPC: launch(c, "k_ks_finish", hbdev::k_ks_finish<WKC, WPC>, grid, threads, 0, 1, chat, D, add0, add1, add_bstride, Wadd, ginv, out, Wout, k, c->dt, batch); break;
+#define X(WPC) case WPC: launch(c, "k_ks_finish", hbdev::k_ks_finish<WKC, WPC>, grid, threads, 0, 1, chat, D, add0, add1, add_bstride, Wadd, TG, out, Wout, k, c->dt, batch); break;
     X(4) X(8) X(12) X(20)
 #undef X
   }
 }
 
-static void do_ks_finish(hb_ctx *c, const uint64_t *chat, unsigned D, const uint64_t *add0, const uint64_t *add1,
-                         size_t add_bstride, int Wadd, unsigned ginv, uint64_t *out, int Wout, int k, unsigned batch) {
+static void do_ks_finish_g(hb_ctx *c, const uint64_t *chat, unsigned D, const uint64_t *add0, const uint64_t *add1,
+                           size_t add_bstride, int Wadd, const hbdev::TailGroups &TG, uint64_t *out, int Wout, int k, unsigned batch) {
   const unsigned threads = 128;
   const size_t total = (size_t)batch * 2 * c->ht.N;
   const unsigned grid = (unsigned)((total + threads - 1) / threads);
@@ -306,18 +315,25 @@ static void do_ks_finish(hb_ctx *c, const uint64_t *chat, unsigned D, const uint
     bool done = true;
 #define KSF(DD, MM)                                                                                                             \
     if (D == DD && h.dim == MM) {                                                                                               \
-      if (wk == 1) launch(c, "k_ks_finish_fast", hbdev::k_ks_finish_fast<1, 4, DD, MM>, grid, threads, 0, 1, chat, F, add0, add1, add_bstride, Wadd, ginv, out, Wout, k, c->dt, batch); \
-      else launch(c, "k_ks_finish_fast", hbdev::k_ks_finish_fast<2, 4, DD, MM>, grid, threads, 0, 1, chat, F, add0, add1, add_bstride, Wadd, ginv, out, Wout, k, c->dt, batch);        \
+      if (wk == 1) launch(c, "k_ks_finish_fast", hbdev::k_ks_finish_fast<1, 4, DD, MM>, grid, threads, 0, 1, chat, F, add0, add1, add_bstride, Wadd, TG, out, Wout, k, c->dt, batch); \
+      else launch(c, "k_ks_finish_fast", hbdev::k_ks_finish_fast<2, 4, DD, MM>, grid, threads, 0, 1, chat, F, add0, add1, add_bstride, Wadd, TG, out, Wout, k, c->dt, batch);        \
     } else
     KSF(5, 2) KSF(6, 2) KSF(5, 3) KSF(6, 3) KSF(7, 3) KSF(8, 3) done = false;
 #undef KSF
     if (done) return;
   }
   switch (wk_class(wk)) {
-#define X(WKC) case WKC: ks_finish_wp<WKC>(c, grid, threads, chat, D, add0, add1, add_bstride, Wadd, ginv, out, Wout, k, batch); break;
+#define X(WKC) case WKC: ks_finish_wp<WKC>(c, grid, threads, chat, D, add0, add1, add_bstride, Wadd, TG, out, Wout, k, batch); break;
     X(1) X(2) X(4) X(8) X(16)
 #undef X
   }
+}
+static void do_ks_finish(hb_ctx *c, const uint64_t *chat, unsigned D, const uint64_t *add0, const uint64_t *add1,
+                         size_t add_bstride, int Wadd, unsigned ginv, uint64_t *out, int Wout, int k, unsigned batch) {
+  hbdev::TailGroups TG;
+  memset(&TG, 0, sizeof TG);
+  TG.ginv[0] = ginv; TG.gbatch = batch; TG.add_shared = 0;
+  do_ks_finish_g(c, chat, D, add0, add1, add_bstride, Wadd, TG, out, Wout, k, batch);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -987,63 +1003,114 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
   const double Delta = std::ldexp(1.0, (int)h.logDelta);
   const unsigned batch = ct->batch, D = plan.D, l = ct->l;
   const int W = hb::words_of_level(h, l), k = h.logq_l[l];
-  const size_t N = h.N, polyw = (size_t)W * N;
-  const size_t jstride = (size_t)batch * 2 * D * N;
+  const size_t N = h.N, polyw = (size_t)W * N, bstride = 2 * polyw;
+  const size_t jstride = (size_t)batch * 2 * D * N;                 // one rotated batch in transform form
+  const unsigned Dk = hb::dim_keyswitch(h, l);
+  if (Dk > h.dimevk || Dk > h.dimub) hb_die("hb_he_gemv: needs %u limbs but keys hold %u and the prime chain %u", Dk, h.dimevk, h.dimub);
+  const size_t cstride = (size_t)batch * 2 * Dk * N;                // one batch of key-switch limbs
+  const bool grouped = !ctx->no_hoist && N <= 65536 && n1 <= HB_MAX_GROUPS && n2 <= HB_MAX_GROUPS;
   uint64_t *hat = ws_get(ctx, ctx->wsC, ctx->wsC_bytes, (size_t)n1 * jstride * 8);
-  hb_ct inner, outer, rot;
-  ct_alloc_tmp(ctx, &inner, batch);
-  ct_alloc_tmp(ctx, &outer, batch);
-  ct_alloc_tmp(ctx, &rot, batch);
-  if (ctx->no_hoist || N > 65536) {
+  if (!grouped) {
+    // one launch per rotation and per giant step (A/B timing, very large rings)
+    hb_ct inner, outer, rot;
+    ct_alloc_tmp(ctx, &inner, batch);
+    ct_alloc_tmp(ctx, &outer, batch);
+    ct_alloc_tmp(ctx, &rot, batch);
     for (unsigned j = 0; j < n1; j++) {
       hb_ct_copy(ctx, &rot, ct);
       hb_he_rot(ctx, &rot, (int)j, rk);
       do_poly_ntt(ctx, rot.words, polyw, W, hat + (size_t)j * jstride, D, (size_t)batch * 2);
     }
-  } else {
-    const unsigned Dk = hb::dim_keyswitch(h, l);
-    if (Dk > h.dimevk || Dk > h.dimub) hb_die("hb_he_gemv: needs %u limbs but keys hold %u and the prime chain %u", Dk, h.dimevk, h.dimub);
-    const size_t bstride = (size_t)2 * polyw, cstride = (size_t)batch * 2 * Dk * N;
-    uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, (size_t)n1 * cstride * 8);
-    uint64_t *rots = ws_get(ctx, ctx->wsD, ctx->wsD_bytes, (size_t)n1 * batch * bstride * 8);
-    std::vector<unsigned> ginv(n1);
-    for (unsigned j0 = 0; j0 < n1; j0 += 4) {
-      hbdev::BabySet S;
-      memset(&S, 0, sizeof S);
-      S.nj = n1 - j0 < 4 ? n1 - j0 : 4;
-      for (unsigned t = 0; t < S.nj; t++) {
-        const unsigned j = j0 + t;
-        if (!rk[j].p) hb_die("hb_he_gemv: rotation key %u is not loaded", j);
-        ginv[j] = pow5_inv_mod_2n(ctx, j);
-        S.evk[t] = (const ulonglong2 *)rk[j].p;
-        S.perm[t] = perm_table(ctx, inv_odd_mod_2n(ctx, ginv[j]));
+    for (unsigned i = 0; i < n2; i++) {
+      const unsigned shift = i * n1;
+      uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, jstride * 8);
+      do_mulacc_intt(ctx, hat, jstride, plan.pthat + (size_t)shift * D * N, 0, n1, 1, chat, D, batch);
+      do_recon_smod(ctx, chat, D, inner.words, W, k, (size_t)batch * 2, true);
+      inner.l = l;
+      for (unsigned j = 0; j < n1; j++) {          // metadata exactly as he_mulpt / he_add update it
+        const double nu = ct->nu * Delta, B = ct->B * Delta;
+        if (!j) { inner.nu = nu; inner.B = B; }
+        else { inner.nu = inner.nu >= nu ? inner.nu : nu; inner.B = inner.B + B; }
       }
-      do_ks_baby(ctx, ct->words + polyw, bstride, W, S, chat + (size_t)j0 * cstride, cstride, Dk, batch);
+      hb_he_rot(ctx, &inner, (int)shift, rk);
+      if (!i) hb_ct_copy(ctx, &outer, &inner);
+      else hb_he_add(ctx, &outer, &outer, &inner);
     }
-    for (unsigned j = 0; j < n1; j++)     // tails: c0 = rdiv(.) + sigma_j(ct.c0), c1 = rdiv(.)   (he-automorphism.c:68-76)
-      do_ks_finish(ctx, chat + (size_t)j * cstride, Dk, ct->words, nullptr, bstride, W, ginv[j], rots + (size_t)j * batch * bstride, W, k, batch);
-    do_poly_ntt(ctx, rots, polyw, W, hat, D, (size_t)n1 * batch * 2);
+    hb_ct_copy(ctx, dst, &outer);
+    hb_he_rs(ctx, dst);
+    hb_ct_free(ctx, &inner);
+    hb_ct_free(ctx, &outer);
+    hb_ct_free(ctx, &rot);
+    return;
   }
+  // ---- grouped schedule: every phase of the matvec is ONE launch over (rotations or giant steps) x batch ----
+  const unsigned ng = n1 > n2 ? n1 : n2;
+  uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, (size_t)ng * cstride * 8);
+  uint64_t *cts = ws_get(ctx, ctx->wsD, ctx->wsD_bytes, (size_t)(ng + n2) * batch * bstride * 8);   // rots / inner sums, then switched sums
+  // 1. baby rotations: one decomposition + forward transform of ct.c1 per limb serves up to four key switches
+  hbdev::TailGroups TB;
+  memset(&TB, 0, sizeof TB);
+  TB.gbatch = batch; TB.add_shared = 1;
+  for (unsigned j0 = 0; j0 < n1; j0 += 4) {
+    hbdev::BabySet S;
+    memset(&S, 0, sizeof S);
+    S.nj = n1 - j0 < 4 ? n1 - j0 : 4;
+    for (unsigned t = 0; t < S.nj; t++) {
+      const unsigned j = j0 + t;
+      if (!rk[j].p) hb_die("hb_he_gemv: rotation key %u is not loaded", j);
+      TB.ginv[j] = pow5_inv_mod_2n(ctx, j);
+      S.evk[t] = (const ulonglong2 *)rk[j].p;
+      S.perm[t] = perm_table(ctx, inv_odd_mod_2n(ctx, TB.ginv[j]));
+    }
+    do_ks_baby(ctx, ct->words + polyw, bstride, W, S, chat + (size_t)j0 * cstride, cstride, Dk, batch);
+  }
+  //    tails of all n1 rotations: c0 = rdiv(.) + sigma_j(ct.c0), c1 = rdiv(.)   (he-automorphism.c:68-76)
+  do_ks_finish_g(ctx, chat, Dk, ct->words, nullptr, bstride, W, TB, cts, W, k, n1 * batch);
+  // 2. transform the rotated ciphertexts once
+  do_poly_ntt(ctx, cts, polyw, W, hat, D, (size_t)n1 * batch * 2);
+  // 3. all giant steps: inner_i = sum_j rot_j * diag_{i n1 + j}, summed in the transform domain
+  uint64_t *mchat = chat;                                          // [n2][batch][2][D][N], D <= Dk
+  do_mulacc_intt(ctx, hat, jstride, plan.pthat, (size_t)n1 * D * N, n1, n2, mchat, D, batch);
+  uint64_t *inner = cts;                                           // [n2][batch][2][W][N]
+  do_recon_smod(ctx, mchat, D, inner, W, k, (size_t)n2 * batch * 2, true);
+  // 4. key-switch every inner sum with its own rotation i n1
+  hbdev::KsGroups SG;
+  hbdev::TailGroups TG;
+  memset(&SG, 0, sizeof SG);
+  memset(&TG, 0, sizeof TG);
+  SG.gbatch = TG.gbatch = batch;
   for (unsigned i = 0; i < n2; i++) {
     const unsigned shift = i * n1;
-    uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, jstride * 8);
-    do_mulacc_intt(ctx, hat, jstride, plan.pthat + (size_t)shift * D * N, n1, chat, D, batch);
-    do_recon_smod(ctx, chat, D, inner.words, W, k, (size_t)batch * 2, true);
-    inner.l = l;
-    for (unsigned j = 0; j < n1; j++) {          // metadata exactly as he_mulpt / he_add update it
-      const double nu = ct->nu * Delta, B = ct->B * Delta;
-      if (!j) { inner.nu = nu; inner.B = B; }
-      else { inner.nu = inner.nu >= nu ? inner.nu : nu; inner.B = inner.B + B; }
-    }
-    hb_he_rot(ctx, &inner, (int)shift, rk);
-    if (!i) hb_ct_copy(ctx, &outer, &inner);
-    else hb_he_add(ctx, &outer, &outer, &inner);
+    if (shift >= h.slots) hb_die("hb_he_gemv: rotation %u outside [0,%u)", shift, h.slots);
+    if (!rk[shift].p) hb_die("hb_he_gemv: rotation key %u is not loaded", shift);
+    TG.ginv[i] = SG.ginv[i] = pow5_inv_mod_2n(ctx, shift);
+    SG.g[i] = inv_odd_mod_2n(ctx, SG.ginv[i]);
+    SG.evk[i] = (const ulonglong2 *)rk[shift].p;
   }
-  hb_ct_copy(ctx, dst, &outer);
+  do_ks_limb_g(ctx, inner + polyw, bstride, W, SG, h.dimevk, chat, Dk, n2 * batch);
+  uint64_t *switched = cts + (size_t)ng * batch * bstride;          // [n2][batch][2][W][N]
+  do_ks_finish_g(ctx, chat, Dk, inner, nullptr, bstride, W, TG, switched, W, k, n2 * batch);
+  // 5. outer = sum_i, then he_rs
+  {
+    const size_t npoly = (size_t)batch * 2, total = npoly * N;
+    launch(ctx, "k_ct_sum", hbdev::k_ct_sum, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint64_t *)switched, (size_t)batch * bstride, n2,
+           dst->words, W, k, (unsigned)N, npoly);
+  }
+  dst->l = l;
+  {                                                                 // metadata: the reference's own sequence of updates
+    double inu = 0, iB = 0, onu = 0, oB = 0;
+    for (unsigned i = 0; i < n2; i++) {
+      for (unsigned j = 0; j < n1; j++) {
+        const double nu = ct->nu * Delta, B = ct->B * Delta;
+        if (!j) { inu = nu; iB = B; }
+        else { inu = inu >= nu ? inu : nu; iB = iB + B; }
+      }
+      if (!i) { onu = inu; oB = iB; }
+      else { onu = onu >= inu ? onu : inu; oB = oB + iB; }
+    }
+    dst->nu = onu; dst->B = oB;
+  }
   hb_he_rs(ctx, dst);
-  hb_ct_free(ctx, &inner);
-  hb_ct_free(ctx, &outer);
-  hb_ct_free(ctx, &rot);
 }
 
 extern "C" void hb_he_gemv(hb_ctx *ctx, hb_ct *dst, const double *A, const hb_ct *ct, const hb_evk *rk) {

@@ -10,6 +10,20 @@
 
 namespace hbdev {
 
+// Several key switches in one launch ("groups": the n1 baby or the n2 giant rotations of one he_gemv).  Instance b of
+// the launch belongs to group b / gbatch; each group has its own automorphism and key.  Single key switch: one group.
+#define HB_MAX_GROUPS 16
+struct KsGroups {
+  const ulonglong2 *evk[HB_MAX_GROUPS];
+  unsigned g[HB_MAX_GROUPS], ginv[HB_MAX_GROUPS];
+  unsigned gbatch;
+};
+struct TailGroups {
+  unsigned ginv[HB_MAX_GROUPS];
+  unsigned gbatch;
+  unsigned add_shared;     // 1: every group adds sigma(add[b % gbatch]) (baby steps: the same source), 0: add[b]
+};
+
 // two shared-memory buffers per CTA: 3 x 74 KB fit one SM up to N = 2^12; from 2^13 (M = 8192, 147 KB) only one CTA does
 template <int LOGN>
 struct KsBlocks { static constexpr int value = (LOGN <= 12) ? HB_KS_MINB : 1; };
@@ -112,8 +126,8 @@ __global__ void k_shoup_prep(const uint64_t *__restrict__ in, ulonglong2 *__rest
 // =========================================================================================================
 template <int LOGN>
 __global__ void __launch_bounds__(Cfg<LOGN>::THREADS, KsBlocks<LOGN>::value)
-k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, unsigned g, unsigned ginv,
-          const ulonglong2 *__restrict__ evk, unsigned dimevk, uint64_t *__restrict__ chat, Tables T, unsigned D) {
+k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, const __grid_constant__ KsGroups S,
+          unsigned dimevk, uint64_t *__restrict__ chat, Tables T, unsigned D) {
   typedef Cfg<LOGN> G;
   extern __shared__ __align__(16) uint64_t smem[];
   uint64_t *smA = smem, *smB = smem + G::SMEM_WORDS;
@@ -129,7 +143,9 @@ k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, unsigned 
   const uint64_t negW = pc.p - T.pow64[(size_t)d * (T.WC + 1) + W];
   const uint64_t *poly = src + (size_t)b * src_bstride;
   const ulonglong2 *dc = T.dec_s + ((size_t)D * T.dimub + d) * (T.WC + 1);
-  poly_forward<LOGN, true>(smA, poly, W, g, ginv, pc, m, negW, make_tw(T, d, false), dc);
+  const unsigned grp = b / S.gbatch;
+  const ulonglong2 *evk = S.evk[grp];
+  poly_forward<LOGN, true>(smA, poly, W, S.g[grp], S.ginv[grp], pc, m, negW, make_tw(T, d, false), dc);
 #pragma unroll 1
   for (int h = 0; h < 2; h++) {
     const ulonglong2 *key = evk + ((size_t)h * dimevk + d) * G::N + (size_t)chunk * G::M;
@@ -242,12 +258,14 @@ k_mulpt_limb(const uint64_t *__restrict__ ct, size_t poly_stride, int W, const u
 // =========================================================================================================
 template <int LOGN>
 __global__ void __launch_bounds__(Cfg<LOGN>::THREADS, Cfg<LOGN>::MINBLOCKS)
-k_mulacc_intt(const uint64_t *__restrict__ hat, size_t hat_jstride, const ulonglong2 *__restrict__ pthat, unsigned n1,
-              uint64_t *__restrict__ chat, Tables T, unsigned D) {
+k_mulacc_intt(const uint64_t *__restrict__ hat, size_t hat_jstride, const ulonglong2 *__restrict__ pthat_all, size_t pthat_gstride,
+              unsigned n1, unsigned nq, uint64_t *__restrict__ chat, Tables T, unsigned D) {
   typedef Cfg<LOGN> G;
   extern __shared__ __align__(16) uint64_t smem[];
   const unsigned idx = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
-  const unsigned q = idx / D, d = idx % D;
+  // all giant steps in one launch: group i = qq / nq reads the SAME hat[j][q] with its own diagonals pthat_all + i * gstride
+  const unsigned qq = idx / D, d = idx % D, q = qq % nq;
+  const ulonglong2 *pthat = pthat_all + (size_t)(qq / nq) * pthat_gstride;
   const PrimeConsts pc = T.primes[d];
   const Mod m = make_mod(pc.p);
   const size_t off = (size_t)chunk * G::M;
@@ -264,7 +282,7 @@ k_mulacc_intt(const uint64_t *__restrict__ hat, size_t hat_jstride, const ulongl
     smem[pidx(i)] = fold(acc, m);
   }
   __syncthreads();
-  uint64_t *dst = chat + ((size_t)q * D + d) * G::N;
+  uint64_t *dst = chat + ((size_t)qq * D + d) * G::N;
   ntt_inverse<LOGN, INV_RAW>(smem, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
 }
 
@@ -551,7 +569,7 @@ __device__ __forceinline__ void ks_exact(const uint64_t *__restrict__ limbs, uns
 // t + roundup + sigma(add_h)[i], centred mod 2^k, stored as Wout words
 template <int WK>
 __device__ __forceinline__ void ks_tail(uint64_t (&t)[WK], bool roundup, const uint64_t *__restrict__ add, size_t add_bstride,
-                                        int Wadd, unsigned ginv, unsigned N, unsigned b, unsigned h, unsigned i,
+                                        int Wadd, unsigned ginv, unsigned N, unsigned b, unsigned badd, unsigned h, unsigned i,
                                         uint64_t *__restrict__ out, int Wout, int k) {
   uint64_t addw[WK];
 #pragma unroll
@@ -560,7 +578,7 @@ __device__ __forceinline__ void ks_tail(uint64_t (&t)[WK], bool roundup, const u
   if (add) {
     unsigned ip = (i * ginv) & (2 * N - 1);
     negate = ip >= N;
-    const uint64_t *ap = add + (size_t)b * add_bstride + (ip & (N - 1));
+    const uint64_t *ap = add + (size_t)badd * add_bstride + (ip & (N - 1));
     uint64_t fill = 0;
 #pragma unroll
     for (int w = 0; w < WK; w++) {
@@ -619,23 +637,25 @@ __device__ __forceinline__ void mac_low(uint64_t (&acc)[WK], uint64_t y, const u
 template <int WK, int WPK>
 __device__ __noinline__ void ks_slow(const uint64_t *__restrict__ limbs, unsigned D, const Tables &T,
                                      const uint64_t *__restrict__ add, size_t add_bstride, int Wadd, unsigned ginv, unsigned b,
-                                     unsigned h, unsigned i, uint64_t *__restrict__ out, int Wout, int k) {
+                                     unsigned badd, unsigned h, unsigned i, uint64_t *__restrict__ out, int Wout, int k) {
   uint64_t t[WK];
   bool roundup;
   ks_exact<WK, WPK>(limbs, D, T, t, roundup);
-  ks_tail<WK>(t, roundup, add, add_bstride, Wadd, ginv, T.N, b, h, i, out, Wout, k);
+  ks_tail<WK>(t, roundup, add, add_bstride, Wadd, ginv, T.N, b, badd, h, i, out, Wout, k);
 }
 
 template <int WK, int WPK, int D, int DIM>
 __global__ void __launch_bounds__(128) k_ks_finish_fast(const uint64_t *__restrict__ chat, const __grid_constant__ KsFast F,
                                                         const uint64_t *__restrict__ add0, const uint64_t *__restrict__ add1,
-                                                        size_t add_bstride, int Wadd, unsigned ginv, uint64_t *__restrict__ out,
-                                                        int Wout, int k, const __grid_constant__ Tables T, unsigned batch) {
+                                                        size_t add_bstride, int Wadd, const __grid_constant__ TailGroups TG,
+                                                        uint64_t *__restrict__ out, int Wout, int k,
+                                                        const __grid_constant__ Tables T, unsigned batch) {
   static_assert(WK <= 2 && D <= 8 && DIM <= 4 && DIM <= D, "fast key-switch tail: q_l <= 2^128, D <= 8, dim <= 4");
   const unsigned N = T.N;
   const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= (size_t)batch * 2 * N) return;
   const unsigned i = gid % N, h = (gid / N) & 1, b = gid / (2 * (size_t)N);
+  const unsigned grp = b / TG.gbatch, ginv = TG.ginv[grp], badd = TG.add_shared ? b - grp * TG.gbatch : b;
   const uint64_t *limbs = chat + ((size_t)b * 2 + h) * D * N + i;
   uint64_t a[D];
 #pragma unroll
@@ -665,7 +685,7 @@ __global__ void __launch_bounds__(128) k_ks_finish_fast(const uint64_t *__restri
                       (fr > HALF - MARGIN && fr < HALF + MARGIN);
   const uint64_t *add = h ? add1 : add0;
   if (unsure) {
-    ks_slow<WK, WPK>(limbs, D, T, add, add_bstride, Wadd, ginv, b, h, i, out, Wout, k);
+    ks_slow<WK, WPK>(limbs, D, T, add, add_bstride, Wadd, ginv, b, badd, h, i, out, Wout, k);
     return;
   }
   const uint64_t v = (Fx + HALF) >> 56, v2 = Fr >> 56;
@@ -687,22 +707,23 @@ __global__ void __launch_bounds__(128) k_ks_finish_fast(const uint64_t *__restri
     t[0] = (uint64_t)A;
     t[WK - 1] = (uint64_t)(A >> 64);
   }
-  ks_tail<WK>(t, roundup, add, add_bstride, Wadd, ginv, N, b, h, i, out, Wout, k);
+  ks_tail<WK>(t, roundup, add, add_bstride, Wadd, ginv, N, b, badd, h, i, out, Wout, k);
 }
 
 template <int WK, int WPK>
 __global__ void k_ks_finish(const uint64_t *__restrict__ chat, unsigned D, const uint64_t *__restrict__ add0,
-                            const uint64_t *__restrict__ add1, size_t add_bstride, int Wadd, unsigned ginv,
+                            const uint64_t *__restrict__ add1, size_t add_bstride, int Wadd, const __grid_constant__ TailGroups TG,
                             uint64_t *__restrict__ out, int Wout, int k, Tables T, unsigned batch) {
   const unsigned N = T.N;
   const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= (size_t)batch * 2 * N) return;
   const unsigned i = gid % N, h = (gid / N) & 1, b = gid / (2 * (size_t)N);
+  const unsigned grp = b / TG.gbatch, ginv = TG.ginv[grp], badd = TG.add_shared ? b - grp * TG.gbatch : b;
   const uint64_t *limbs = chat + ((size_t)b * 2 + h) * D * N + i;
   uint64_t t[WK];
   bool roundup;
   ks_exact<WK, WPK>(limbs, D, T, t, roundup);
-  ks_tail<WK>(t, roundup, h ? add1 : add0, add_bstride, Wadd, ginv, N, b, h, i, out, Wout, k);
+  ks_tail<WK>(t, roundup, h ? add1 : add0, add_bstride, Wadd, ginv, N, b, badd, h, i, out, Wout, k);
 }
 
 // =========================================================================================================
@@ -735,6 +756,37 @@ __global__ void k_ct_addsub(const uint64_t *__restrict__ a, const uint64_t *__re
       carry = c1 | c2;
       r = s2;
       int kk = k - 64 * w;
+      if (kk <= 64) {
+        if (kk < 64) r = (uint64_t)(((int64_t)(r << (64 - kk))) >> (64 - kk));
+        fill = (uint64_t)((int64_t)r >> 63);
+        done = true;
+      }
+    }
+    po[(size_t)w * N] = r;
+  }
+}
+
+// out = smod(sum_{g < G} a[g], 2^k): the he_add chain over the giant steps of he_gemv (he-algo.c:81-84).  Each he_add
+// centres its result; every representative is congruent mod 2^k, so one centring of the full sum gives the same words.
+__global__ void k_ct_sum(const uint64_t *__restrict__ a, size_t gstride, unsigned G, uint64_t *__restrict__ out, int W, int k,
+                         unsigned N, size_t npoly) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= npoly * N) return;
+  const size_t q = gid / N, i = gid % N;
+  const uint64_t *pa = a + q * W * N + i;
+  uint64_t *po = out + q * W * N + i;
+  uint64_t fill = 0;
+  unsigned carry = 0;           // at most G - 1 + previous carry: fits easily
+  bool done = false;
+  for (int w = 0; w < W; w++) {
+    uint64_t r;
+    if (done) r = fill;
+    else {
+      unsigned __int128 s = carry;
+      for (unsigned g = 0; g < G; g++) s += pa[(size_t)g * gstride + (size_t)w * N];
+      r = (uint64_t)s;
+      carry = (unsigned)(s >> 64);
+      const int kk = k - 64 * w;
       if (kk <= 64) {
         if (kk < 64) r = (uint64_t)(((int64_t)(r << (64 - kk))) >> (64 - kk));
         fill = (uint64_t)((int64_t)r >> 63);
