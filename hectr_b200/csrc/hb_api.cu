@@ -10,7 +10,9 @@
 #include <cuda_runtime.h>
 #include "../../include/hectr_b200.h"
 #include "hb_tables.hpp"
+#include "hb_tables32.hpp"
 #include "hb_kernels.cuh"
+#include "hb_dev32.cuh"
 
 extern "C" {
 struct hb_ring;
@@ -45,6 +47,10 @@ struct GemvPlan {
   unsigned l = 0, D = 0;
   bool fused = false;        // the n1 products of one giant step may be summed before the CRT (bound check below)
   ulonglong2 *pthat = nullptr; // device [slots][D][N] Shoup pairs: ntt of the encoded, pre-rotated diagonals
+  // the same diagonals on the internal 30-bit basis (hb_tables32.hpp), used when the fused bound holds
+  bool use32 = false;
+  unsigned D32 = 0;
+  uint32_t *pthat32 = nullptr; // device [slots][D32][2][N]: multiplicand plane, quotient plane
 };
 
 struct hb_ctx {
@@ -71,6 +77,9 @@ struct hb_ctx {
   std::multimap<size_t, uint64_t *> pool;
   std::map<uint64_t *, size_t> live;
   hb_ring *ring = nullptr;
+  bool have32 = false;              // the 30-bit plaintext-product path is built for this ring (2^10 <= N <= 2^13)
+  hb::HostTables32 ht32;
+  hb32::Tables32 dt32;
   std::map<unsigned, uint16_t *> perms;   // g -> device perm_g[N] (k_ks_baby)
   uint64_t *wsD = nullptr;
   size_t wsD_bytes = 0;
@@ -138,6 +147,50 @@ static void want_smem(K kernel, size_t bytes) {
 #else
 #define HB_LOGN_CASES(X) X(7) X(10) X(11) X(12) X(13) X(14) X(15) X(16)
 #endif
+
+#ifdef HB_DEV_FAST
+#define HB_LOGN32_CASES(X) X(12)
+#else
+#define HB_LOGN32_CASES(X) X(10) X(11) X(12) X(13)
+#endif
+
+// ---- 30-bit plaintext-product path (hb_dev32.cuh) -----------------------------------------------------------------
+template <int LOGN>
+struct Launch32 {
+  typedef hb32::Cfg32<LOGN> G;
+  static void poly_ntt(hb_ctx *c, const uint64_t *src, size_t stride, int W, uint32_t *out, unsigned D, size_t npoly, bool canon) {
+    if (!canon && (W == 1 || W == 2) && G::N >= 1024) {      // one CTA per polynomial, every limb from one read
+      if (W == 1) launch(c, "k32_poly_ntt_all", hb32::k32_poly_ntt_all<LOGN, 1>, (unsigned)npoly, G::THREADS, G::SMEM_BYTES, 1, src, stride, out, c->dt32, D);
+      else launch(c, "k32_poly_ntt_all", hb32::k32_poly_ntt_all<LOGN, 2>, (unsigned)npoly, G::THREADS, G::SMEM_BYTES, 1, src, stride, out, c->dt32, D);
+      return;
+    }
+    if (canon) launch(c, "k32_poly_ntt", hb32::k32_poly_ntt<LOGN, true>, (unsigned)(npoly * D), G::THREADS, G::SMEM_BYTES, 1, src, stride, W, out, c->dt32, D);
+    else launch(c, "k32_poly_ntt", hb32::k32_poly_ntt<LOGN, false>, (unsigned)(npoly * D), G::THREADS, G::SMEM_BYTES, 1, src, stride, W, out, c->dt32, D);
+  }
+  static void mulacc_intt(hb_ctx *c, const uint32_t *hat, size_t jstride, const uint32_t *pthat, size_t gstride, unsigned n1, unsigned ngroups,
+                          uint32_t *chat, unsigned D, unsigned batch) {
+    if (gstride == (size_t)n1 * D && (n1 == 2 || n1 == 4) && G::N >= 1024) {      // rotated transforms read once, in registers
+      const unsigned grid = (unsigned)((size_t)batch * 2 * D);
+      if (n1 == 4) launch(c, "k32_mulacc_intt_all", hb32::k32_mulacc_intt_all<LOGN, 4>, grid, G::THREADS, G::SMEM_BYTES, 1, hat, jstride, pthat, gstride, ngroups, batch * 2, chat, c->dt32, D);
+      else launch(c, "k32_mulacc_intt_all", hb32::k32_mulacc_intt_all<LOGN, 2>, grid, G::THREADS, G::SMEM_BYTES, 1, hat, jstride, pthat, gstride, ngroups, batch * 2, chat, c->dt32, D);
+      return;
+    }
+    launch(c, "k32_mulacc_intt", hb32::k32_mulacc_intt<LOGN>, (unsigned)((size_t)ngroups * batch * 2 * D), G::THREADS, G::SMEM_BYTES, 1, hat, jstride,
+           pthat, gstride, n1, batch * 2, chat, c->dt32, D);
+  }
+};
+static void do32_poly_ntt(hb_ctx *c, const uint64_t *src, size_t stride, int W, uint32_t *out, unsigned D, size_t npoly, bool canon) {
+#define X(L) case L: Launch32<L>::poly_ntt(c, src, stride, W, out, D, npoly, canon); break;
+  switch (c->ht.logn) { HB_LOGN32_CASES(X) default: hb_die("logn=%u has no 30-bit path", c->ht.logn); }
+#undef X
+}
+static void do32_mulacc_intt(hb_ctx *c, const uint32_t *hat, size_t jstride, const uint32_t *pthat, size_t gstride, unsigned n1, unsigned ngroups,
+                             uint32_t *chat, unsigned D, unsigned batch) {
+#define X(L) case L: Launch32<L>::mulacc_intt(c, hat, jstride, pthat, gstride, n1, ngroups, chat, D, batch); break;
+  switch (c->ht.logn) { HB_LOGN32_CASES(X) default: hb_die("logn=%u has no 30-bit path", c->ht.logn); }
+#undef X
+}
+static void do32_recon_smod(hb_ctx *c, const uint32_t *chat, unsigned D, uint64_t *out, int Wout, int k, size_t npoly);
 
 template <int LOGN>
 struct Launch {
@@ -265,6 +318,35 @@ static void do_recon_smod(hb_ctx *c, const uint64_t *chat, unsigned D, uint64_t 
     if (pre) launch(c, "k_recon_smod", hbdev::k_recon_smod<WKC, true>, grid, threads, 0, 1, chat, D, out, Wout, k, c->dt, (unsigned)npoly);  \
     else launch(c, "k_recon_smod", hbdev::k_recon_smod<WKC, false>, grid, threads, 0, 1, chat, D, out, Wout, k, c->dt, (unsigned)npoly);     \
     break;
+    X(1) X(2) X(4) X(8) X(16)
+#undef X
+  }
+}
+
+template <int WKC>
+static bool recon32_fixed(hb_ctx *c, const uint32_t *chat, unsigned D, uint64_t *out, int Wout, int k, size_t npoly) {
+  const unsigned threads = 128;
+  const unsigned grid = (unsigned)((npoly * (c->ht.N / 4) + threads - 1) / threads);
+  switch (D) {
+#define X(DD) case DD: launch(c, "k32_recon_smod4", hb32::k32_recon_smod4<WKC, DD>, grid, threads, 0, 1, chat, out, Wout, k, c->dt32, (unsigned)npoly); return true;
+    X(2) X(3) X(4) X(5) X(6) X(7) X(8)
+#undef X
+  }
+  return false;
+}
+
+static void do32_recon_smod(hb_ctx *c, const uint32_t *chat, unsigned D, uint64_t *out, int Wout, int k, size_t npoly) {
+  const int wkc = wk_class((k + 63) / 64);
+  if (c->ht.N >= 64 && wkc <= 4) {       // compile-time limb count, four coefficients per thread
+    if (wkc == 1 && recon32_fixed<1>(c, chat, D, out, Wout, k, npoly)) return;
+    if (wkc == 2 && recon32_fixed<2>(c, chat, D, out, Wout, k, npoly)) return;
+    if (wkc == 4 && recon32_fixed<4>(c, chat, D, out, Wout, k, npoly)) return;
+  }
+  const unsigned threads = 128;
+  const size_t total = npoly * c->ht.N;
+  const unsigned grid = (unsigned)((total + threads - 1) / threads);
+  switch (wkc) {
+#define X(WKC) case WKC: launch(c, "k32_recon_smod", hb32::k32_recon_smod<WKC>, grid, threads, 0, 1, chat, D, out, Wout, k, c->dt32, (unsigned)npoly); break;
     X(1) X(2) X(4) X(8) X(16)
 #undef X
   }
@@ -410,6 +492,29 @@ extern "C" hb_ctx *hb_ctx_create(unsigned logn, unsigned logq, unsigned slots, u
   }
   ctx->ring = hb_ring_create(logn);
   ctx->enc_host.assign((size_t)h.WC * h.N, 0);
+  {
+    bool ok32 = false;
+#define X(L) if (logn == L) ok32 = true;
+    HB_LOGN32_CASES(X)
+#undef X
+    const char *e = getenv("HB_NO_PT30");
+    if (ok32 && !(e && *e && *e != '0')) {
+      std::string err32 = hb::build_tables32(ctx->ht32, logn, h.WC, h.Pfull[h.dimub].bits());
+      if (!err32.empty()) hb_die("%s", err32.c_str());
+      static_assert(sizeof(hb::Prime32) == sizeof(hb32::Prime32), "Prime32 layout");
+      const hb::HostTables32 &g = ctx->ht32;
+      hb32::Tables32 &d = ctx->dt32;
+      d.primes = (const hb32::Prime32 *)upload_vec(ctx, g.primes);
+      d.tw = (const uint2 *)upload_vec(ctx, g.tw);
+      d.itw = (const uint2 *)upload_vec(ctx, g.itw);
+      d.pow32 = (const uint2 *)upload_vec(ctx, g.pow32);
+      d.crt_inv = (const uint2 *)upload_vec(ctx, g.crt_inv);
+      d.crt_qhat = upload_vec(ctx, g.crt_qhat);
+      d.crt_Q = upload_vec(ctx, g.crt_Q);
+      d.N = g.N; d.logn = g.logn; d.nprimes = g.nprimes; d.WC = g.WC; d.ndig = g.ndig;
+      ctx->have32 = true;
+    }
+  }
   return ctx;
 }
 
@@ -420,7 +525,7 @@ extern "C" void hb_ctx_destroy(hb_ctx *ctx) {
   for (void *p : ctx->table_allocs) cudaFree(p);
   for (auto &kv : ctx->pool) cudaFree(kv.second);
   for (auto &kv : ctx->live) cudaFree(kv.first);
-  for (auto &pl : ctx->plans) cudaFree(pl.pthat);
+  for (auto &pl : ctx->plans) { cudaFree(pl.pthat); cudaFree(pl.pthat32); }
   for (auto &kv : ctx->prof_recs)
     for (auto &pr : kv.second.pending) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   for (cudaEvent_t e : ctx->prof_free) cudaEventDestroy(e);
@@ -879,6 +984,7 @@ static const GemvPlan &gemv_plan(hb_ctx *ctx, const double *A, unsigned l) {
   if (ctx->plans.size() >= 8) {   // small LRU: drop the oldest
     CUDA_OK(cudaStreamSynchronize(ctx->stream));
     cudaFree(ctx->plans.front().pthat);
+    cudaFree(ctx->plans.front().pthat32);
     ctx->plans.erase(ctx->plans.begin());
   }
   GemvPlan plan;
@@ -940,9 +1046,24 @@ static const GemvPlan &gemv_plan(hb_ctx *ctx, const double *A, unsigned l) {
   plan.pthat = (ulonglong2 *)hb_dev_alloc(ctx, (size_t)S * plan.D * h.N * 16);
   do_poly_ntt(ctx, dpt, ptw, h.WC, raw, plan.D, S);
   do_shoup_prep(ctx, raw, plan.pthat, plan.D, (size_t)S * plan.D, 2, plan.D);
+  uint32_t *raw32 = nullptr;
+  if (ctx->have32 && plan.fused) {
+    // the exact product fits P_D (fused bound): any basis with Q >= P_D reconstructs the same integer
+    plan.D32 = hb::limbs32_for_bits(ctx->ht32, h.Pfull[plan.D].bits());
+    if (plan.D32) {
+      raw32 = (uint32_t *)hb_dev_alloc(ctx, (size_t)S * plan.D32 * h.N * 4);
+      plan.pthat32 = (uint32_t *)hb_dev_alloc(ctx, (size_t)S * plan.D32 * h.N * 8);
+      do32_poly_ntt(ctx, dpt, ptw, (int)h.WC, raw32, plan.D32, S, true);
+      const size_t total = (size_t)S * plan.D32 * h.N;
+      launch(ctx, "k32_shoup_prep", hb32::k32_shoup_prep, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint32_t *)raw32, plan.pthat32, ctx->dt32,
+             plan.D32, (size_t)S * plan.D32, plan.D32);
+      plan.use32 = true;
+    }
+  }
   CUDA_OK(cudaStreamSynchronize(ctx->stream));
   CUDA_OK(cudaFree(dpt));
   CUDA_OK(cudaFree(raw));
+  if (raw32) CUDA_OK(cudaFree(raw32));
   ctx->plans.push_back(std::move(plan));
   return ctx->plans.back();
 }
@@ -1066,13 +1187,23 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
   }
   //    tails of all n1 rotations: c0 = rdiv(.) + sigma_j(ct.c0), c1 = rdiv(.)   (he-automorphism.c:68-76)
   do_ks_finish_g(ctx, chat, Dk, ct->words, nullptr, bstride, W, TB, cts, W, k, n1 * batch);
-  // 2. transform the rotated ciphertexts once
-  do_poly_ntt(ctx, cts, polyw, W, hat, D, (size_t)n1 * batch * 2);
-  // 3. all giant steps: inner_i = sum_j rot_j * diag_{i n1 + j}, summed in the transform domain
-  uint64_t *mchat = chat;                                          // [n2][batch][2][D][N], D <= Dk
-  do_mulacc_intt(ctx, hat, jstride, plan.pthat, (size_t)n1 * D * N, n1, n2, mchat, D, batch);
   uint64_t *inner = cts;                                           // [n2][batch][2][W][N]
-  do_recon_smod(ctx, mchat, D, inner, W, k, (size_t)n2 * batch * 2, true);
+  if (plan.use32) {
+    // 2-3 on the internal 30-bit basis (twice the butterfly throughput per modulus bit; same integers, hb_tables32.hpp)
+    const unsigned D32 = plan.D32;
+    const size_t jstride32 = (size_t)batch * 2 * D32 * N;
+    uint32_t *hat32 = (uint32_t *)hat, *mchat32 = (uint32_t *)chat;       // 4 D32 <= 8 D bytes per coefficient: the buffers fit
+    do32_poly_ntt(ctx, cts, polyw, W, hat32, D32, (size_t)n1 * batch * 2, false);
+    do32_mulacc_intt(ctx, hat32, jstride32, plan.pthat32, (size_t)n1 * D32, n1, n2, mchat32, D32, batch);
+    do32_recon_smod(ctx, mchat32, D32, inner, W, k, (size_t)n2 * batch * 2);
+  } else {
+    // 2. transform the rotated ciphertexts once
+    do_poly_ntt(ctx, cts, polyw, W, hat, D, (size_t)n1 * batch * 2);
+    // 3. all giant steps: inner_i = sum_j rot_j * diag_{i n1 + j}, summed in the transform domain
+    uint64_t *mchat = chat;                                          // [n2][batch][2][D][N], D <= Dk
+    do_mulacc_intt(ctx, hat, jstride, plan.pthat, (size_t)n1 * D * N, n1, n2, mchat, D, batch);
+    do_recon_smod(ctx, mchat, D, inner, W, k, (size_t)n2 * batch * 2, true);
+  }
   // 4. key-switch every inner sum with its own rotation i n1
   hbdev::KsGroups SG;
   hbdev::TailGroups TG;

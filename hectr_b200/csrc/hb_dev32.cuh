@@ -1,0 +1,493 @@
+// 30-bit negacyclic NTT core and the plaintext-product kernels of he_gemv on the engine's internal 30-bit RNS basis
+// (hb_tables32.hpp explains why the integers are the same as the reference's, GPQHE/src/he-algo.c:64-79 + he-mult.c:159-196).
+//
+// Harvey lazy butterflies on 32-bit words: every prime is below 2^30, values live in [0, 4p) (forward) / [0, 2p) (inverse),
+// a Shoup product  a*w - umulhi(a, w')*p  is one IMAD.HI + two IMAD and accepts ANY 32-bit a.
+// One limb (N <= 2^13 coefficients, 4 bytes each) per CTA in padded shared memory (one pad word per 32), radix-2^R
+// register tiles with R <= 4 like the 59-bit core, same twiddle indexing (entry k of stage s at 2^s + k).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "hb_dev.cuh"
+
+namespace hb32 {
+
+struct Prime32 { uint32_t p, ninv, ninv_q, mu; };   // must match hb::Prime32
+
+struct Tables32 {                 // device pointers, by value
+  const Prime32 *primes;          // [nprimes]
+  const uint2 *tw, *itw;          // [nprimes][N] (w, floor(w 2^32 / p))
+  const uint2 *pow32;             // [nprimes][ndig + 1]
+  const uint2 *crt_inv;           // [nprimes + 1][nprimes]
+  const uint64_t *crt_qhat;       // [nprimes + 1][nprimes][WC]
+  const uint64_t *crt_Q;          // [nprimes + 1][WC]
+  unsigned N, logn, nprimes, WC, ndig;
+};
+
+__device__ __forceinline__ uint32_t shoup32(uint32_t a, uint32_t w, uint32_t wq, uint32_t p) {   // [0, 2p) for any a
+  return a * w - __umulhi(a, wq) * p;
+}
+__device__ __forceinline__ uint32_t csub32(uint32_t x, uint32_t m) { return min(x, x - m); }    // x < 2m -> x mod-ish m
+
+template <int LOGN>
+struct Cfg32 {
+  static constexpr int N = 1 << LOGN;
+  static constexpr int TILES16 = N / 16;
+  static constexpr int THREADS = TILES16 > 256 ? 256 : TILES16;
+  static constexpr int SMEM_WORDS = N + (N >> 5);
+  static constexpr int SMEM_BYTES = SMEM_WORDS * 4;
+};
+// one pad word per 32: a warp's 32 consecutive words, its 16-strided tiles and (with the lane swap in pass32) its two
+// 256-blocks of the middle pass all fall on 32 different banks
+__device__ __forceinline__ int pidx32(int i) { return i + (i >> 5); }
+
+// the 2^a consecutive twiddles of one stage of a tile, fetched 16 bytes at a time (the run starts at an even index)
+template <int CNT>
+__device__ __forceinline__ void load_tw32(uint2 (&w)[CNT], const uint2 *__restrict__ src) {
+  if constexpr (CNT == 1) {
+    w[0] = __ldg(src);
+  } else {
+    const uint4 *v = reinterpret_cast<const uint4 *>(src);
+#pragma unroll
+    for (int m = 0; m < CNT / 2; m++) {
+      const uint4 x = __ldg(&v[m]);
+      w[2 * m] = make_uint2(x.x, x.y);
+      w[2 * m + 1] = make_uint2(x.z, x.w);
+    }
+  }
+}
+
+template <int R, int A>
+__device__ __forceinline__ void stage_fwd32(uint32_t (&x)[1 << R], const uint2 *__restrict__ tw, unsigned K0, uint32_t p) {
+  constexpr int beta = R - 1 - A, half = 1 << beta;
+  const uint32_t p2 = 2 * p;
+  uint2 w[1 << A];
+  load_tw32<(1 << A)>(w, tw + ((size_t)K0 << A));
+#pragma unroll
+  for (int t = 0; t < (1 << R); t++) {
+    if ((t & half) == 0) {
+      const uint2 ww = w[t >> (beta + 1)];
+      const uint32_t u = csub32(x[t], p2);
+      const uint32_t v = shoup32(x[t + half], ww.x, ww.y, p);
+      x[t] = u + v;
+      x[t + half] = u - v + p2;
+    }
+  }
+}
+// forward tile: X' = X + wY, Y' = X - wY + 2p, X first brought below 2p; all values stay in [0, 4p)
+template <int R>
+__device__ __forceinline__ void tile_fwd32(uint32_t (&x)[1 << R], const uint2 *__restrict__ tw, unsigned K0, uint32_t p) {
+  stage_fwd32<R, 0>(x, tw, K0, p);
+  if constexpr (R > 1) stage_fwd32<R, 1>(x, tw, K0, p);
+  if constexpr (R > 2) stage_fwd32<R, 2>(x, tw, K0, p);
+  if constexpr (R > 3) stage_fwd32<R, 3>(x, tw, K0, p);
+}
+
+template <int R, int BETA>
+__device__ __forceinline__ void stage_inv32(uint32_t (&x)[1 << R], const uint2 *__restrict__ tw, unsigned K0, uint32_t p) {
+  constexpr int A = R - 1 - BETA, half = 1 << BETA;
+  const uint32_t p2 = 2 * p;
+  uint2 w[1 << A];
+  load_tw32<(1 << A)>(w, tw + ((size_t)K0 << A));
+#pragma unroll
+  for (int t = 0; t < (1 << R); t++) {
+    if ((t & half) == 0) {
+      const uint2 ww = w[t >> (BETA + 1)];
+      const uint32_t s = csub32(x[t] + x[t + half], p2);
+      const uint32_t d = x[t] - x[t + half] + p2;
+      x[t] = s;
+      x[t + half] = shoup32(d, ww.x, ww.y, p);
+    }
+  }
+}
+// inverse tile (Gentleman-Sande): inputs and outputs in [0, 2p)
+template <int R>
+__device__ __forceinline__ void tile_inv32(uint32_t (&x)[1 << R], const uint2 *__restrict__ tw, unsigned K0, uint32_t p) {
+  stage_inv32<R, 0>(x, tw, K0, p);
+  if constexpr (R > 1) stage_inv32<R, 1>(x, tw, K0, p);
+  if constexpr (R > 2) stage_inv32<R, 2>(x, tw, K0, p);
+  if constexpr (R > 3) stage_inv32<R, 3>(x, tw, K0, p);
+}
+
+// one pass over the limb in shared memory: stages [S, S+R) in forward numbering
+template <int LOGN, int S, int R, bool INV>
+__device__ __forceinline__ void pass32(uint32_t *sm, const uint2 *__restrict__ tw, uint32_t p) {
+  typedef Cfg32<LOGN> G;
+  constexpr int LOGST = LOGN - S - R, ST = 1 << LOGST, TILES = G::N >> R, LOGBLK = LOGN - S;
+  for (int t0 = threadIdx.x; t0 < TILES; t0 += G::THREADS) {
+    // 16-strided pass: the two half-warps take blocks two apart (bits 4 and 5 of the tile index swapped), whose padded
+    // offsets differ by 16 banks
+    const int tile = (LOGST == 4 && TILES >= 64) ? ((t0 & ~0x30) | ((t0 & 0x10) << 1) | ((t0 & 0x20) >> 1)) : t0;
+    const int b = tile >> LOGST, o = tile & (ST - 1), g = (b << LOGBLK) + o;
+    uint32_t x[1 << R];
+#pragma unroll
+    for (int t = 0; t < (1 << R); t++) x[t] = sm[pidx32(g + t * ST)];
+    if (INV) tile_inv32<R>(x, tw, (1u << S) + b, p);
+    else tile_fwd32<R>(x, tw, (1u << S) + b, p);
+#pragma unroll
+    for (int t = 0; t < (1 << R); t++) sm[pidx32(g + t * ST)] = x[t];
+  }
+}
+
+template <int LOGN, int S>
+__device__ __forceinline__ void fwd32(uint32_t *sm, const uint2 *__restrict__ tw, uint32_t p) {
+  if constexpr (S < LOGN) {
+    constexpr int R = hbdev::PassSize<LOGN - S>::R;
+    pass32<LOGN, S, R, false>(sm, tw, p);
+    __syncthreads();
+    fwd32<LOGN, S + R>(sm, tw, p);
+  }
+}
+template <int LOGN, int S>
+__device__ __forceinline__ void inv32(uint32_t *sm, const uint2 *__restrict__ itw, uint32_t p) {
+  if constexpr (S < LOGN) {
+    constexpr int R = hbdev::PassSize<LOGN - S>::R;
+    inv32<LOGN, S + R>(sm, itw, p);
+    pass32<LOGN, S, R, true>(sm, itw, p);
+    __syncthreads();
+  }
+}
+// natural order, values below 4p, visible after the barrier this starts with -> bit-reversed order, values below 4p
+template <int LOGN>
+__device__ __forceinline__ void ntt32_forward(uint32_t *sm, const uint2 *__restrict__ tw, uint32_t p) {
+  __syncthreads();
+  fwd32<LOGN, 0>(sm, tw, p);
+}
+// bit-reversed order, values below 2p -> natural order, NOT scaled by N^-1 (folded into the fixed multiplicand), below 2p
+template <int LOGN>
+__device__ __forceinline__ void ntt32_inverse(uint32_t *sm, const uint2 *__restrict__ itw, uint32_t p) {
+  __syncthreads();
+  inv32<LOGN, 0>(sm, itw, p);
+}
+
+}  // namespace hb32
+
+namespace hb32 {
+
+// ---------------------------------------------------------------------------------------------------------------
+// rns_decompose (GPQHE/src/rns.c:37-48) onto a 30-bit prime + forward transform.
+// src: npoly polynomials of W 64-bit words (planar, two's complement), polynomial q at src + q*poly_stride.
+// out[q][D][N] u32, bit-reversed order, lazily reduced (below 4p) -- or canonical [0,p) when CANON (fixed multiplicands).
+// ---------------------------------------------------------------------------------------------------------------
+template <int LOGN, bool CANON>
+__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS)
+k32_poly_ntt(const uint64_t *__restrict__ src, size_t poly_stride, int W, uint32_t *__restrict__ out, Tables32 T, unsigned D) {
+  typedef Cfg32<LOGN> G;
+  extern __shared__ __align__(16) uint32_t sm32[];
+  const unsigned q = blockIdx.x / D, d = blockIdx.x % D;
+  const uint32_t p = T.primes[d].p, p2 = 2 * p;
+  const uint2 *pw = T.pow32 + (size_t)d * (T.ndig + 1);
+  const uint32_t negW = p - __ldg(&pw[2 * W]).x;             // a negative coefficient subtracts 2^(64 W)
+  const uint64_t *poly = src + (size_t)q * poly_stride;
+  for (int i = threadIdx.x; i < G::N; i += G::THREADS) {
+    uint32_t acc = 0;
+    uint64_t top = 0;
+    for (int w = 0; w < W; w++) {
+      top = HB_LD(&poly[(size_t)w * G::N + i]);
+      const uint2 c0 = __ldg(&pw[2 * w]), c1 = __ldg(&pw[2 * w + 1]);
+      acc = csub32(acc + shoup32((uint32_t)top, c0.x, c0.y, p), p2);            // stays below 2p
+      acc = csub32(acc + shoup32((uint32_t)(top >> 32), c1.x, c1.y, p), p2);
+    }
+    acc += (negW & (uint32_t)((int64_t)top >> 63));                            // below 3p
+    sm32[pidx32(i)] = acc;
+  }
+  ntt32_forward<LOGN>(sm32, T.tw + (size_t)d * G::N, p);
+  uint32_t *dst = out + ((size_t)q * D + d) * G::N;
+  for (int i = threadIdx.x; i < G::N; i += G::THREADS) {
+    uint32_t v = sm32[pidx32(i)];
+    if (CANON) { v = csub32(v, p2); v = csub32(v, p); }
+    dst[i] = v;
+  }
+}
+
+// canonical residues -> Shoup pairs of  w * N^-1 * (Q_Dw/q_d)^-1  (the inverse transform then skips its scaling and the
+// reconstruction its per-limb multiply).  limbs[j][N] uses prime j % D.
+// Output is PLANAR per limb: out[limb][0][N] the multiplicands, out[limb][1][N] their quotients, so that a warp's 16-byte
+// loads of either plane are contiguous.
+__global__ void k32_shoup_prep(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, Tables32 T, unsigned D, size_t nlimbs, unsigned Dw) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= nlimbs * T.N) return;
+  const unsigned d = (unsigned)((gid / T.N) % D);
+  const Prime32 pc = T.primes[d];
+  const uint2 inv = T.crt_inv[(size_t)Dw * T.nprimes + d];
+  uint32_t w = in[gid];
+  w = csub32(shoup32(w, pc.ninv, pc.ninv_q, pc.p), pc.p);
+  w = csub32(shoup32(w, inv.x, inv.y, pc.p), pc.p);
+  const size_t limb = gid / T.N, i = gid % T.N;
+  out[(2 * limb) * T.N + i] = w;
+  out[(2 * limb + 1) * T.N + i] = (uint32_t)((((uint64_t)w) << 32) / pc.p);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// all giant steps of he_gemv in one launch (GPQHE/src/he-algo.c:64-79):
+//   chat[g][q][d] = y-weighted invntt( sum_j hat[j][q][d] o pthat[g*n1 + j][d] ),   g < ngroups, q < nq, j < n1
+// ---------------------------------------------------------------------------------------------------------------
+template <int LOGN>
+__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS)
+k32_mulacc_intt(const uint32_t *__restrict__ hat, size_t hat_jstride, const uint32_t *__restrict__ pthat_all, size_t pthat_gstride, unsigned n1,
+                unsigned nq, uint32_t *__restrict__ chat, Tables32 T, unsigned D) {
+  typedef Cfg32<LOGN> G;
+  extern __shared__ __align__(16) uint32_t sm32[];
+  const unsigned qq = blockIdx.x / D, d = blockIdx.x % D, q = qq % nq;
+  const uint32_t p = T.primes[d].p, p2 = 2 * p;
+  const uint32_t *a = hat + ((size_t)q * D + d) * G::N;
+  const uint32_t *w = pthat_all + ((size_t)(qq / nq) * pthat_gstride + d) * 2 * G::N;       // strides in limbs
+#pragma unroll 2
+  for (int i = threadIdx.x; i < G::N; i += G::THREADS) {
+    uint32_t acc = 0;
+    for (unsigned j = 0; j < n1; j++) {
+      const uint32_t *wj = w + (size_t)j * D * 2 * G::N;
+      acc = csub32(acc + shoup32(HB_LD(&a[(size_t)j * hat_jstride + i]), __ldg(&wj[i]), __ldg(&wj[G::N + i]), p), p2);
+    }
+    sm32[pidx32(i)] = acc;                                                       // below 2p
+  }
+  ntt32_inverse<LOGN>(sm32, T.itw + (size_t)d * G::N, p);
+  uint32_t *dst = chat + ((size_t)qq * D + d) * G::N;
+  for (int i = threadIdx.x; i < G::N; i += G::THREADS) dst[i] = sm32[pidx32(i)];
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// exact CRT over D 30-bit limbs, centred mod Q_D, then centred mod 2^k (poly_rns2mpi, poly.c:109-120, on this basis):
+//   x = sum_d y_d (Q_D/q_d) - v Q_D,  v = round(sum_d y_d / q_d);  |x| < Q_D/4 for every valid product, so a 56-bit
+//   fixed-point fraction (error below 2 D units) decides v.  Limbs arrive pre-weighted (y_d, below 2p).
+// ---------------------------------------------------------------------------------------------------------------
+template <int WK>
+__global__ void k32_recon_smod(const uint32_t *__restrict__ chat, unsigned D, uint64_t *__restrict__ out, int Wout, int k, Tables32 T,
+                               unsigned npoly) {
+  const unsigned N = T.N;
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)npoly * N) return;
+  const unsigned q = gid / N, i = gid % N;
+  const uint32_t *limbs = chat + (size_t)q * D * N + i;
+  const uint64_t *qhat = T.crt_qhat + (size_t)D * T.nprimes * T.WC;
+  uint64_t acc[WK];
+#pragma unroll
+  for (int w = 0; w < WK; w++) acc[w] = 0;
+  uint64_t F = 0;
+  for (unsigned d = 0; d < D; d++) {
+    const Prime32 pc = T.primes[d];
+    const uint32_t y = csub32(limbs[(size_t)d * N], pc.p);
+    F += ((uint64_t)y * pc.mu) >> 5;                       // y / q_d in units of 2^-56
+    uint64_t carry = 0;
+#pragma unroll
+    for (int w = 0; w < WK; w++) {
+      const uint64_t pw = (w < (int)T.WC) ? qhat[(size_t)d * T.WC + w] : 0;
+      const unsigned __int128 t = (unsigned __int128)y * pw + acc[w] + carry;
+      acc[w] = (uint64_t)t;
+      carry = (uint64_t)(t >> 64);
+    }
+  }
+  const uint64_t v = (F + (1ULL << 55)) >> 56;
+  const uint64_t *Q = T.crt_Q + (size_t)D * T.WC;
+  uint64_t borrow = 0;
+#pragma unroll
+  for (int w = 0; w < WK; w++) {
+    const uint64_t pw = (w < (int)T.WC) ? Q[w] : 0;
+    const unsigned __int128 t = (unsigned __int128)v * pw + borrow;
+    const uint64_t sub = (uint64_t)t;
+    borrow = (uint64_t)(t >> 64) + (acc[w] < sub);
+    acc[w] -= sub;
+  }
+  hbdev::sext_bits<WK>(acc, k);
+  uint64_t *o = out + (size_t)q * Wout * N + i;
+#pragma unroll
+  for (int w = 0; w < WK; w++)
+    if (w < Wout) o[(size_t)w * N] = acc[w];
+}
+
+}  // namespace hb32
+
+namespace hb32 {
+
+// ===============================================================================================================
+// Memory-lean variants.  On the 30-bit basis the butterflies are cheap enough that global-load latency and DRAM
+// traffic bind instead of the integer multiplier, so each CTA loads its inputs ONCE, 16 bytes per thread per load,
+// and loops over everything that reuses them.
+// ===============================================================================================================
+
+// One CTA per polynomial: the W words of 16 coefficients per thread are read once and decomposed onto every limb.
+template <int LOGN, int WT>
+__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, 2)
+k32_poly_ntt_all(const uint64_t *__restrict__ src, size_t poly_stride, uint32_t *__restrict__ out, Tables32 T, unsigned D) {
+  typedef Cfg32<LOGN> G;
+  constexpr int PER = G::N / G::THREADS;                      // coefficients per thread
+  extern __shared__ __align__(16) uint32_t sm32[];
+  const unsigned q = blockIdx.x;
+  const uint64_t *poly = src + (size_t)q * poly_stride;
+  uint32_t dig[PER][2 * WT];
+  uint32_t sign[PER];
+#pragma unroll
+  for (int k = 0; k < PER; k++) {
+    const int i = threadIdx.x + k * G::THREADS;
+    uint64_t top = 0;
+#pragma unroll
+    for (int w = 0; w < WT; w++) {
+      top = HB_LD(&poly[(size_t)w * G::N + i]);
+      dig[k][2 * w] = (uint32_t)top;
+      dig[k][2 * w + 1] = (uint32_t)(top >> 32);
+    }
+    sign[k] = (uint32_t)((int64_t)top >> 63);
+  }
+#pragma unroll 1
+  for (unsigned d = 0; d < D; d++) {
+    const uint32_t p = T.primes[d].p, p2 = 2 * p;
+    const uint2 *pw = T.pow32 + (size_t)d * (T.ndig + 1);
+    uint2 c[2 * WT];
+#pragma unroll
+    for (int w = 0; w < 2 * WT; w++) c[w] = __ldg(&pw[w]);
+    const uint32_t negW = p - __ldg(&pw[2 * WT]).x;
+#pragma unroll
+    for (int k = 0; k < PER; k++) {
+      uint32_t acc = shoup32(dig[k][0], c[0].x, c[0].y, p);
+#pragma unroll
+      for (int w = 1; w < 2 * WT; w++) acc = csub32(acc + shoup32(dig[k][w], c[w].x, c[w].y, p), p2);
+      sm32[pidx32(threadIdx.x + k * G::THREADS)] = acc + (negW & sign[k]);      // below 3p
+    }
+    ntt32_forward<LOGN>(sm32, T.tw + (size_t)d * G::N, p);
+    uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)q * D + d) * G::N);
+#pragma unroll
+    for (int k = 0; k < PER / 4; k++) {
+      const int i4 = threadIdx.x + k * G::THREADS;
+      uint4 v;
+      v.x = sm32[pidx32(4 * i4)]; v.y = sm32[pidx32(4 * i4 + 1)]; v.z = sm32[pidx32(4 * i4 + 2)]; v.w = sm32[pidx32(4 * i4 + 3)];
+      __stcs(&dst[i4], v);
+    }
+    __syncthreads();                                          // the buffer is refilled for the next limb
+  }
+}
+
+// One CTA per (polynomial q, limb d): the NJ rotated transforms hat[j][q][d] are read once into registers and serve every
+// giant step g < ngroups:  chat[g][q][d] = y-weighted invntt( sum_j hat[j][q][d] o pthat[g*NJ + j][d] ).
+template <int LOGN, int NJ>
+__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, 2)
+k32_mulacc_intt_all(const uint32_t *__restrict__ hat, size_t hat_jstride, const uint32_t *__restrict__ pthat_all, size_t pthat_gstride,
+                    unsigned ngroups, unsigned nq, uint32_t *__restrict__ chat, Tables32 T, unsigned D) {
+  typedef Cfg32<LOGN> G;
+  constexpr int V = G::N / 4 / G::THREADS;                    // uint4 per thread
+  extern __shared__ __align__(16) uint32_t sm32[];
+  const unsigned q = blockIdx.x / D, d = blockIdx.x % D;
+  const uint32_t p = T.primes[d].p, p2 = 2 * p;
+  uint4 h[NJ][V];
+#pragma unroll
+  for (int j = 0; j < NJ; j++) {
+    const uint4 *a = reinterpret_cast<const uint4 *>(hat + (size_t)j * hat_jstride + ((size_t)q * D + d) * G::N);
+#pragma unroll
+    for (int k = 0; k < V; k++) h[j][k] = __ldcs(&a[threadIdx.x + k * G::THREADS]);
+  }
+  const uint2 *itw = T.itw + (size_t)d * G::N;
+#pragma unroll 1
+  for (unsigned g = 0; g < ngroups; g++) {
+    const uint32_t *w = pthat_all + ((size_t)g * pthat_gstride + d) * 2 * G::N;               // strides in limbs
+#pragma unroll
+    for (int k = 0; k < V; k++) {
+      const int i4 = threadIdx.x + k * G::THREADS;
+      uint32_t acc[4] = {0, 0, 0, 0};
+#pragma unroll
+      for (int j = 0; j < NJ; j++) {
+        const uint4 *wp = reinterpret_cast<const uint4 *>(w + (size_t)j * D * 2 * G::N);
+        const uint4 kw = __ldg(&wp[i4]), kq = __ldg(&wp[G::N / 4 + i4]);    // elements 4 i4 .. 4 i4 + 3 of both planes
+        acc[0] = csub32(acc[0] + shoup32(h[j][k].x, kw.x, kq.x, p), p2);
+        acc[1] = csub32(acc[1] + shoup32(h[j][k].y, kw.y, kq.y, p), p2);
+        acc[2] = csub32(acc[2] + shoup32(h[j][k].z, kw.z, kq.z, p), p2);
+        acc[3] = csub32(acc[3] + shoup32(h[j][k].w, kw.w, kq.w, p), p2);
+      }
+#pragma unroll
+      for (int e = 0; e < 4; e++) sm32[pidx32(4 * i4 + e)] = acc[e];
+    }
+    ntt32_inverse<LOGN>(sm32, itw, p);
+    uint4 *dst = reinterpret_cast<uint4 *>(chat + (((size_t)g * nq + q) * D + d) * G::N);
+#pragma unroll
+    for (int k = 0; k < V; k++) {
+      const int i4 = threadIdx.x + k * G::THREADS;
+      uint4 v;
+      v.x = sm32[pidx32(4 * i4)]; v.y = sm32[pidx32(4 * i4 + 1)]; v.z = sm32[pidx32(4 * i4 + 2)]; v.w = sm32[pidx32(4 * i4 + 3)];
+      __stcs(&dst[i4], v);
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace hb32
+
+namespace hb32 {
+
+// k32_recon_smod with the limb count fixed at compile time and four consecutive coefficients per thread: one 16-byte
+// load per limb, 32-bit digit chains (one IMAD.WIDE per digit), 16-byte stores.  Same integers as k32_recon_smod.
+template <int WK, int DD>
+__global__ void __launch_bounds__(128)
+k32_recon_smod4(const uint32_t *__restrict__ chat, uint64_t *__restrict__ out, int Wout, int k, Tables32 T, unsigned npoly) {
+  const unsigned N = T.N, N4 = N >> 2;
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)npoly * N4) return;
+  const unsigned q = gid / N4, i4 = gid % N4;
+  const uint4 *limbs = reinterpret_cast<const uint4 *>(chat + (size_t)q * DD * N) + i4;
+  const uint64_t *qhat = T.crt_qhat + (size_t)DD * T.nprimes * T.WC;
+  uint32_t acc[4][2 * WK];
+  uint64_t F[4];
+#pragma unroll
+  for (int e = 0; e < 4; e++) {
+    F[e] = 0;
+#pragma unroll
+    for (int w = 0; w < 2 * WK; w++) acc[e][w] = 0;
+  }
+  uint4 yv[DD];
+#pragma unroll
+  for (int d = 0; d < DD; d++) yv[d] = __ldcs(&limbs[(size_t)d * N4]);
+#pragma unroll
+  for (int d = 0; d < DD; d++) {
+    const uint4 pcv = __ldg(reinterpret_cast<const uint4 *>(&T.primes[d]));     // p, ninv, ninv_q, mu
+    const uint32_t p = pcv.x, mu = pcv.w;
+    uint32_t qd[2 * WK];
+#pragma unroll
+    for (int w = 0; w < WK; w++) {
+      const uint64_t v = (w < (int)T.WC) ? __ldg(&qhat[(size_t)d * T.WC + w]) : 0;
+      qd[2 * w] = (uint32_t)v;
+      qd[2 * w + 1] = (uint32_t)(v >> 32);
+    }
+    const uint32_t y[4] = {csub32(yv[d].x, p), csub32(yv[d].y, p), csub32(yv[d].z, p), csub32(yv[d].w, p)};
+#pragma unroll
+    for (int e = 0; e < 4; e++) {
+      F[e] += ((uint64_t)y[e] * mu) >> 5;
+      uint32_t carry = 0;
+#pragma unroll
+      for (int w = 0; w < 2 * WK; w++) {
+        const uint64_t t = (uint64_t)y[e] * qd[w] + acc[e][w] + carry;
+        acc[e][w] = (uint32_t)t;
+        carry = (uint32_t)(t >> 32);
+      }
+    }
+  }
+  uint32_t Qd[2 * WK];
+#pragma unroll
+  for (int w = 0; w < WK; w++) {
+    const uint64_t v = (w < (int)T.WC) ? __ldg(&T.crt_Q[(size_t)DD * T.WC + w]) : 0;
+    Qd[2 * w] = (uint32_t)v;
+    Qd[2 * w + 1] = (uint32_t)(v >> 32);
+  }
+  uint64_t x[4][WK];
+#pragma unroll
+  for (int e = 0; e < 4; e++) {
+    const uint32_t v = (uint32_t)((F[e] + (1ULL << 55)) >> 56);
+    uint32_t borrow = 0;
+#pragma unroll
+    for (int w = 0; w < 2 * WK; w++) {
+      const uint64_t t = (uint64_t)v * Qd[w] + borrow;
+      const uint32_t sub = (uint32_t)t;
+      borrow = (uint32_t)(t >> 32) + (acc[e][w] < sub);
+      acc[e][w] -= sub;
+    }
+#pragma unroll
+    for (int w = 0; w < WK; w++) x[e][w] = (uint64_t)acc[e][2 * w] | ((uint64_t)acc[e][2 * w + 1] << 32);
+    hbdev::sext_bits<WK>(x[e], k);
+  }
+  uint64_t *o = out + (size_t)q * Wout * N + 4 * (size_t)i4;
+#pragma unroll
+  for (int w = 0; w < WK; w++)
+    if (w < Wout) {
+      ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(o + (size_t)w * N);
+      dst[0] = make_ulonglong2(x[0][w], x[1][w]);
+      dst[1] = make_ulonglong2(x[2][w], x[3][w]);
+    }
+}
+
+}  // namespace hb32
