@@ -20,7 +20,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-fil
     python profiles/prof_driver.py --case hempc --batch 4096 --reps 1 > "$O/ncu_launches.log" 2>&1
 echo "ncu launches rc=$?"
 python profiles/prof_driver.py --case hempc --batch 4096 --reps 1 > "$O/plain2.log" 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:'k_ks_limb|k_ks_baby|k_mulacc_intt|k_ks_finish|k_recon_smod|k_poly_ntt' -s 14 -c 14 \
+ncu --set full --clock-control none --import-source on -k regex:'k_ks_limb|k_ks_baby|k32_mulacc_intt_all|k_ks_finish|k32_recon_smod4|k32_poly_ntt_all' -s 14 -c 14 \
     -o "$O/prof_hempc" -f python profiles/prof_driver.py --case hempc --batch 4096 --reps 1 > "$O/ncu_full_hempc.log" 2>&1
 echo "ncu full hempc rc=$?"
 python profiles/prof_driver.py --case ntt --logn 16 --reps 1 > "$O/plain3.log" 2>&1 &&

@@ -54,7 +54,7 @@ def main():
         seen = set()
         for r in rows[2:]:
             name = re.sub(r"^void\s+", "", r[idx["Kernel Name"]])
-            name = re.sub(r"\(.*$", "", name).replace("hbdev::", "")
+            name = re.sub(r"\(.*$", "", name).replace("hbdev::", "").replace("hb32::", "")
             if name in seen:
                 continue
             seen.add(name)

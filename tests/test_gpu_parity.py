@@ -1,5 +1,8 @@
 """GPU parity: the CUDA path (through the C ABI) against the compiled, unmodified reference
 (oracle/_ref/libgpqhe.so) on the same seeded inputs.  Integer work: bit-exact."""
+import ctypes as C
+import json
+
 import numpy as np
 import pytest
 
@@ -383,3 +386,45 @@ def test_fast_tail_equals_exact_tail(cfgA, monkeypatch):
         keys2.free()
     finally:
         eng2.close()
+
+
+@pytest.mark.parametrize("slots,level", [(16, 2), (16, 1), (64, 2)])
+def test_pt30_basis_equals_59bit_basis(slots, level, monkeypatch):
+    """he_gemv's plaintext products run on the engine's internal 30-bit basis when the exact product fits P_D
+    (hb_tables32.hpp); HB_NO_PT30 keeps them on the reference's 59-bit primes.  Both must give the same words: 128
+    random ciphertexts at full size, dense random matrices (every diagonal non-zero), synthetic keys."""
+    from hectr_b200 import Engine
+    params = (12, 109, slots, 50)
+    rng = np.random.default_rng(97 + slots + level)
+    eng = Engine(*params)
+    monkeypatch.setenv("HB_NO_PT30", "1")
+    eng59 = Engine(*params)
+    monkeypatch.delenv("HB_NO_PT30")
+    try:
+        primes = eng.primes()
+        keys = np.empty((slots, 2, eng.info.dimevk, eng.n), dtype=np.uint64)
+        for d in range(eng.info.dimevk):
+            keys[:, :, d, :] = rng.integers(0, int(primes[d]), size=(slots, 2, eng.n), dtype=np.uint64)
+        rk, rk59 = eng.keys(keys), eng59.keys(keys)
+        K = rng.standard_normal((slots, slots)) + 1j * rng.standard_normal((slots, slots))
+        a = random_ct_words(rng, 128, eng.words(level), eng.n, eng.logq(level))
+        names = []
+        for e in (eng, eng59):
+            e.lib.hb_prof_reset(e.ctx)
+            e.lib.hb_prof_enable(e.ctx, 1)
+        got = eng.he_gemv(K, eng.ct(a, level), rk).download()
+        want = eng59.he_gemv(K, eng59.ct(a, level), rk59).download()
+        for e in (eng, eng59):
+            e.lib.hb_prof_enable(e.ctx, 0)
+            need = e.lib.hb_prof_report(e.ctx, None, 0)
+            buf = C.create_string_buffer(need + 1)
+            e.lib.hb_prof_report(e.ctx, buf, need + 1)
+            names.append(set(json.loads(buf.value.decode())))
+        assert any(n.startswith("k32_mulacc_intt") for n in names[0]), names[0]          # the 30-bit kernels really ran
+        assert not any(n.startswith("k32_") for n in names[1]) and "k_mulacc_intt" in names[1], names[1]
+        assert np.array_equal(got, want)
+        rk.free()
+        rk59.free()
+    finally:
+        eng.close()
+        eng59.close()
