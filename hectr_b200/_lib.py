@@ -93,6 +93,18 @@ PROTOTYPES = {
     "hb_he_add": (None, [ctx_p, ct_p, ct_p, ct_p]),
     "hb_he_sub": (None, [ctx_p, ct_p, ct_p, ct_p]),
     "hb_he_neg": (None, [ctx_p, ct_p]),
+    "hb_he_addpt": (None, [ctx_p, ct_p, ct_p, pt_p]),
+    "hb_he_subpt": (None, [ctx_p, ct_p, ct_p, pt_p]),
+    "hb_he_const_pt": (None, [ctx_p, pt_p, C.c_double, C.c_double]),
+    "hb_he_sum": (None, [ctx_p, ct_p, ct_p, evk_p]),
+    "hb_he_idx": (None, [ctx_p, ct_p, ct_p, C.c_uint, evk_p]),
+    "hb_he_nrm2": (None, [ctx_p, ct_p, ct_p, evk_p, evk_p, evk_p]),
+    "hb_he_inv": (None, [ctx_p, ct_p, ct_p, evk_p, C.c_uint]),
+    "hb_he_sqrt": (None, [ctx_p, ct_p, ct_p, evk_p, C.c_uint]),
+    "hb_he_sigmoid": (None, [ctx_p, ct_p, ct_p, evk_p]),
+    "hb_he_log": (None, [ctx_p, ct_p, ct_p, evk_p]),
+    "hb_he_exp": (None, [ctx_p, ct_p, C.c_double, C.c_double, ct_p, evk_p, C.c_uint]),
+    "hb_he_cmp": (None, [ctx_p, ct_p, ct_p, ct_p, evk_p, C.c_uint, C.c_uint]),
     "hb_he_rs": (None, [ctx_p, ct_p]),
     "hb_he_moddown": (None, [ctx_p, ct_p]),
     "hb_he_mulpt": (None, [ctx_p, ct_p, ct_p, pt_p]),

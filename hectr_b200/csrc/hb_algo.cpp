@@ -1,0 +1,263 @@
+// Compositions of GPQHE/src/he-algo.c:95-548 over the engine's C ABI.
+//
+// Nothing here touches device memory directly: every function is a fixed sequence of hb_he_* calls, in the order the
+// reference issues its he_* calls, because the order of multiplications, rescalings and level drops decides every bit of
+// the result.  All ciphertext handles carry the caller's batch, so one call evaluates the function on a whole batch.
+#include <cmath>
+#include <cstring>
+#include <vector>
+#include "../../include/hectr_b200.h"
+
+namespace {
+
+struct Ct {                                   // scoped he_alloc_ct / he_free_ct
+  hb_ctx *c;
+  hb_ct v;
+  Ct(hb_ctx *ctx, unsigned batch) : c(ctx) { std::memset(&v, 0, sizeof v); hb_ct_alloc(c, &v, batch); }
+  Ct(hb_ctx *ctx, const hb_ct *src) : Ct(ctx, src->batch) { hb_ct_copy(c, &v, src); }
+  ~Ct() { hb_ct_free(c, &v); }
+  Ct(const Ct &) = delete;
+  Ct &operator=(const Ct &) = delete;
+  operator hb_ct *() { return &v; }
+};
+
+struct Pt {                                   // scoped he_alloc_pt / he_free_pt, zero-filled like the reference's
+  hb_ctx *c;
+  hb_pt v;
+  explicit Pt(hb_ctx *ctx) : c(ctx) { std::memset(&v, 0, sizeof v); hb_pt_alloc(c, &v); }
+  Pt(hb_ctx *ctx, double value) : Pt(ctx) { hb_he_const_pt(c, &v, value, 0.0); }
+  ~Pt() { hb_pt_free(c, &v); }
+  Pt(const Pt &) = delete;
+  Pt &operator=(const Pt &) = delete;
+  Pt &set(double value) { hb_he_const_pt(c, &v, value, 0.0); return *this; }
+  operator hb_pt *() { return &v; }
+};
+
+struct Ops {                                  // the recurring pairs: product then rescale
+  hb_ctx *c;
+  const hb_evk *rlk;
+  void mul_rs(hb_ct *d, const hb_ct *a, const hb_ct *b) const { hb_he_mul(c, d, a, b, rlk); hb_he_rs(c, d); }
+  void mulpt_rs(hb_ct *d, const hb_ct *a, const hb_pt *p) const { hb_he_mulpt(c, d, a, p); hb_he_rs(c, d); }
+  void down(hb_ct *d, unsigned times) const { for (unsigned i = 0; i < times; i++) hb_he_moddown(c, d); }
+};
+
+unsigned slots_of(hb_ctx *ctx) {
+  hb_info info;
+  hb_ctx_info(ctx, &info);
+  return info.slots;
+}
+
+void gemv_into(hb_ctx *ctx, hb_ct *dst, const std::vector<double> &A, const hb_ct *ct, const hb_evk *rk) {
+  if (dst == ct) {                            // the matvec reads its input while it writes: go through a copy
+    Ct in(ctx, ct);
+    hb_he_gemv(ctx, dst, A.data(), in, rk);
+  } else {
+    hb_he_gemv(ctx, dst, A.data(), ct, rk);
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+// he_sum (he-algo.c:95-103): the matrix whose first row is all ones
+void hb_he_sum(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rk) {
+  const unsigned S = slots_of(ctx);
+  std::vector<double> A((size_t)S * S * 2, 0.0);
+  for (unsigned i = 0; i < S; i++) A[2 * (size_t)i] = 1.0;
+  gemv_into(ctx, dst, A, ct, rk);
+}
+
+// he_idx (he-algo.c:105-112): the matrix with a single one on the diagonal
+void hb_he_idx(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, unsigned idx, const hb_evk *rk) {
+  const unsigned S = slots_of(ctx);
+  std::vector<double> A((size_t)S * S * 2, 0.0);
+  A[2 * ((size_t)idx * S + idx)] = 1.0;
+  gemv_into(ctx, dst, A, ct, rk);
+}
+
+// he_nrm2 (he-algo.c:114-125): sum(ct * conj(ct))
+void hb_he_nrm2(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rlk, const hb_evk *ck, const hb_evk *rk) {
+  Ct conj(ctx, ct);
+  hb_he_conj(ctx, conj, ck);
+  Ct sq(ctx, ct->batch);
+  hb_he_mul(ctx, sq, ct, conj, rlk);
+  hb_he_rs(ctx, sq);
+  hb_he_sum(ctx, dst, sq, rk);
+}
+
+// he_inv (he-algo.c:131-164): Goldschmidt, a_0 = 2 - x, b_0 = 1 - x, b <- b^2, a <- a (1 + b); depth iter + 1
+void hb_he_inv(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rlk, unsigned iter) {
+  const Ops op{ctx, rlk};
+  Pt one(ctx, 1.0), two(ctx, 2.0);
+  Ct t(ctx, ct), a(ctx, ct->batch), b(ctx, ct->batch);
+  hb_he_neg(ctx, t);
+  hb_he_addpt(ctx, a, t, two);
+  hb_he_moddown(ctx, a);
+  hb_he_addpt(ctx, b, t, one);
+  for (unsigned n = 0; n < iter; n++) {
+    op.mul_rs(b, b, b);
+    hb_he_addpt(ctx, t, b, one);
+    op.mul_rs(a, a, t);
+  }
+  hb_ct_copy(ctx, dst, a);
+}
+
+// he_sqrt (he-algo.c:166-206): a_0 = x, b_0 = x - 1, a <- a (1 - b/2), b <- b^2 (b - 3)/4
+void hb_he_sqrt(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rlk, unsigned iter) {
+  const Ops op{ctx, rlk};
+  Pt one(ctx, 1.0), three(ctx, 3.0), half(ctx, 0.5), quarter(ctx, 0.25);
+  Ct a(ctx, ct), b(ctx, ct->batch), t(ctx, ct->batch);
+  hb_he_subpt(ctx, b, ct, one);
+  for (unsigned n = 0; n < iter; n++) {
+    op.mulpt_rs(t, b, half);
+    hb_he_subpt(ctx, t, t, one);
+    hb_he_neg(ctx, t);
+    hb_he_moddown(ctx, a);
+    op.mul_rs(a, a, t);
+    hb_he_subpt(ctx, t, b, three);
+    op.mulpt_rs(t, t, quarter);
+    op.mul_rs(b, b, b);
+    op.mul_rs(b, b, t);
+  }
+  hb_ct_copy(ctx, dst, a);
+}
+
+// he_sigmoid (he-algo.c:208-277): degree-9 Taylor polynomial 1/2 + x/4 - x^3/48 + x^5/480 - 17x^7/80640 + 31x^9/1451520,
+// grouped as (c3 x)(x^2 + c1/c3), (c7 x)(x^2 + c5/c7) x^4, (c9 x) x^8; result four levels down
+void hb_he_sigmoid(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rlk) {
+  const Ops op{ctx, rlk};
+  const unsigned B = ct->batch;
+  Ct x2(ctx, B), x4(ctx, B), x8(ctx, B), lo(ctx, B), g13(ctx, B), mid(ctx, B), g57(ctx, B), hi(ctx, B);
+  Pt k(ctx);
+  op.mul_rs(x2, ct, ct);
+  op.mul_rs(x4, x2, x2);
+  op.mul_rs(x8, x4, x4);
+  op.mulpt_rs(lo, ct, k.set(-1. / 48));
+  hb_he_addpt(ctx, g13, x2, k.set((1. / 4) / (-1. / 48)));
+  op.mul_rs(g13, lo, g13);
+  op.down(g13, 2);
+  op.mulpt_rs(mid, ct, k.set(-17. / 80640));
+  hb_he_addpt(ctx, g57, x2, k.set((1. / 480) / (-17. / 80640)));
+  op.mul_rs(g57, mid, g57);
+  op.mul_rs(g57, x4, g57);
+  op.down(g57, 1);
+  op.mulpt_rs(hi, ct, k.set(31. / 1451520));
+  op.down(hi, 2);
+  op.mul_rs(hi, hi, x8);
+  hb_he_add(ctx, dst, g13, g57);
+  hb_he_add(ctx, dst, dst, hi);
+  hb_he_addpt(ctx, dst, dst, k.set(1. / 2));
+}
+
+// he_log (he-algo.c:279-362): odd and even halves of a degree-10 polynomial in x, each (c x^j)(c0 + c2 x^2 + ... + x^8)
+void hb_he_log(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rlk) {
+  const Ops op{ctx, rlk};
+  const unsigned B = ct->batch;
+  Ct x2(ctx, B), x4(ctx, B), x8(ctx, B), t(ctx, B);
+  Pt k(ctx);
+  op.mul_rs(x2, ct, ct);
+  op.mul_rs(x4, x2, x2);
+  op.mul_rs(x8, x4, x4);
+  // inner(c6, c4, c2, c0) = c0 + c2 x^2 + c4 x^4 + c6 x^6 + x^8, three levels down
+  auto inner = [&](hb_ct *acc, double c6, double c4, double c2, double c0) {
+    hb_ct_copy(ctx, acc, x8);
+    op.mulpt_rs(t, x2, k.set(c6));
+    op.mul_rs(t, t, x4);
+    hb_he_add(ctx, acc, acc, t);
+    op.mulpt_rs(t, x4, k.set(c4));
+    hb_he_add(ctx, acc, acc, t);
+    op.mulpt_rs(t, x2, k.set(c2));
+    op.down(t, 1);
+    hb_he_add(ctx, acc, acc, t);
+    hb_he_addpt(ctx, acc, acc, k.set(c0));
+  };
+  Ct odd(ctx, B), even(ctx, B);
+  inner(odd, 9. / 7., 9. / 5., 9. / 3., 9);
+  op.mulpt_rs(t, ct, k.set(1. / 9.));
+  op.down(t, 2);
+  op.mul_rs(odd, t, odd);
+  inner(even, 10. / 8., 10. / 6., 10. / 4., 10. / 2);
+  op.mulpt_rs(t, x2, k.set(-1. / 10.));
+  op.down(t, 1);
+  op.mul_rs(even, t, even);
+  hb_he_add(ctx, dst, odd, even);
+}
+
+// he_exp_taylor (he-algo.c:364-433): degree-7 Taylor polynomial as ((x+1) + x^2 (x+3)/3!) + x^4 ((x+5)/5! + x^2 (x+7)/7!)
+static void exp_taylor(hb_ctx *ctx, hb_ct *dst, const hb_ct *x, const hb_evk *rlk) {
+  const Ops op{ctx, rlk};
+  const unsigned B = x->batch;
+  Ct x2(ctx, B), x4(ctx, B), p01(ctx, B), p23(ctx, B), low(ctx, B), p45(ctx, B), p67(ctx, B), high(ctx, B);
+  Pt k(ctx);
+  op.mul_rs(x2, x, x);
+  op.mul_rs(x4, x2, x2);
+  hb_he_addpt(ctx, p01, x, k.set(1.0));
+  op.mulpt_rs(p01, p01, k);                      // times the same constant 1
+  op.down(p01, 1);
+  hb_he_addpt(ctx, p23, x, k.set(3.0));
+  op.mulpt_rs(p23, p23, k.set(1.0 / 6));
+  op.mul_rs(p23, x2, p23);
+  hb_he_add(ctx, low, p01, p23);
+  op.down(low, 1);
+  hb_he_addpt(ctx, p45, x, k.set(5.0));
+  op.mulpt_rs(p45, p45, k.set(1.0 / 120));
+  op.down(p45, 1);
+  hb_he_addpt(ctx, p67, x, k.set(7.0));
+  op.mulpt_rs(p67, p67, k.set(1.0 / 5040));
+  op.mul_rs(p67, x2, p67);
+  hb_he_add(ctx, high, p45, p67);
+  op.mul_rs(high, x4, high);
+  hb_he_add(ctx, dst, low, high);
+}
+
+// he_exp (he-algo.c:435-458): exp(a x) = (taylor(a x / 2^iter))^(2^iter)
+void hb_he_exp(hb_ctx *ctx, hb_ct *dst, double a_re, double a_im, const hb_ct *ct, const hb_evk *rlk, unsigned iter) {
+  const Ops op{ctx, rlk};
+  const unsigned S = slots_of(ctx);
+  const double scale = (double)(1 << iter);
+  std::vector<double> coeff((size_t)S * 2);
+  for (unsigned i = 0; i < S; i++) { coeff[2 * i] = a_re / scale; coeff[2 * i + 1] = a_im / scale; }
+  Pt k(ctx);
+  hb_he_ecd(ctx, k, coeff.data());
+  Ct ax(ctx, ct->batch);
+  op.mulpt_rs(ax, ct, k);
+  exp_taylor(ctx, dst, ax, rlk);
+  for (unsigned n = 0; n < iter; n++) op.mul_rs(dst, dst, dst);
+}
+
+// he_cmp_core (he-algo.c:460-512): a <- x / (2 * (a/2)) then t rounds of a <- a^2 / (a^2 + (1-a)^2); `a` enters as x + y
+static void cmp_core(hb_ctx *ctx, hb_ct *a, const hb_ct *x, const hb_evk *rlk, unsigned iter, unsigned t) {
+  const Ops op{ctx, rlk};
+  Ct b(ctx, x->batch), inv(ctx, a);
+  Pt one(ctx, 1.0), half(ctx, 0.5);
+  op.mulpt_rs(inv, inv, half);
+  hb_he_inv(ctx, inv, inv, rlk, iter);
+  op.mulpt_rs(a, x, half);
+  op.down(a, iter + 1);
+  op.mul_rs(a, a, inv);
+  hb_he_subpt(ctx, b, a, one);
+  hb_he_neg(ctx, b);
+  for (unsigned n = 0; n < t; n++) {
+    op.mul_rs(a, a, a);
+    op.mul_rs(b, b, b);
+    hb_he_add(ctx, inv, a, b);
+    hb_he_inv(ctx, inv, inv, rlk, iter);
+    op.down(a, iter + 1);
+    op.mul_rs(a, a, inv);
+    hb_he_subpt(ctx, b, a, one);
+    hb_he_neg(ctx, b);
+  }
+}
+
+// he_cmp (he-algo.c:514-530): depth (3 + iter)(1 + t), t = log2(alpha / log2(1 + 2^-alpha))
+void hb_he_cmp(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct1, const hb_ct *ct2, const hb_evk *rlk, unsigned iter, unsigned alpha) {
+  const double c = 1 + std::pow(2, -(int)alpha);
+  const unsigned t = (unsigned)std::log2(alpha / std::log2(c));
+  Ct a(ctx, ct1->batch);
+  hb_he_add(ctx, a, ct1, ct2);
+  cmp_core(ctx, a, ct1, rlk, iter, t);
+  hb_ct_copy(ctx, dst, a);
+}
+
+}  // extern "C"

@@ -20,6 +20,7 @@ hb_ring *hb_ring_create(unsigned logn);
 void hb_ring_destroy(hb_ring *r);
 void hb_ring_encode(const hb_ring *r, unsigned slots, const double *m, double Delta, uint64_t *words, unsigned W);
 void hb_ring_decode(const hb_ring *r, unsigned slots, const uint64_t *words, unsigned W, double Delta, double *m);
+void hb_ring_const(const hb_ring *r, double re, double im, double Delta, uint64_t *words, unsigned W);
 }
 
 using hbdev::Tables;
@@ -814,6 +815,17 @@ extern "C" void hb_he_ecd(hb_ctx *ctx, hb_pt *pt, const double *m) {
   hb_pt_upload(ctx, pt, ctx->enc_host.data(), Delta);
 }
 
+extern "C" void hb_he_const_pt(hb_ctx *ctx, hb_pt *pt, double re, double im) {
+  if (!pt->words) hb_die("hb_he_const_pt: plaintext handle is not allocated");
+  // he_const_pt writes coefficients 0 and N/2 and keeps the rest (he-encode.c:119-125): read-modify-write like hb_he_ecd
+  const size_t bytes = (size_t)ctx->ht.WC * ctx->ht.N * 8;
+  CUDA_OK(cudaMemcpyAsync(ctx->enc_host.data(), pt->words, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  const double Delta = std::ldexp(1.0, (int)ctx->ht.logDelta);
+  hb_ring_const(ctx->ring, re, im, Delta, ctx->enc_host.data(), ctx->ht.WC);
+  hb_pt_upload(ctx, pt, ctx->enc_host.data(), Delta);
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // evaluation
 // ---------------------------------------------------------------------------------------------------------
@@ -834,6 +846,18 @@ static void addsub(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b, int o
 }
 extern "C" void hb_he_add(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b) { addsub(ctx, ct, a, b, 0, "hb_he_add"); }
 extern "C" void hb_he_sub(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b) { addsub(ctx, ct, a, b, 1, "hb_he_sub"); }
+static void addsub_pt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt, int op, const char *what) {
+  same_shape(dst, src, what);
+  if (!pt || !pt->words) hb_die("%s: plaintext handle is not allocated", what);
+  dst->l = src->l;
+  dst->nu = (src->nu >= pt->nu) ? src->nu : pt->nu;        // he-add.c:84
+  dst->B = src->B;
+  const int W = hb::words_of_level(ctx->ht, dst->l), k = ctx->ht.logq_l[dst->l];
+  const size_t npoly = (size_t)dst->batch * 2, total = npoly * ctx->ht.N;
+  launch(ctx, "k_ct_addpt", hbdev::k_ct_addpt, (unsigned)((total + 255) / 256), 256, 0, 1, src->words, pt->words, dst->words, W, k, op, ctx->ht.N, npoly);
+}
+extern "C" void hb_he_addpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt) { addsub_pt(ctx, dst, src, pt, 0, "hb_he_addpt"); }
+extern "C" void hb_he_subpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt) { addsub_pt(ctx, dst, src, pt, 1, "hb_he_subpt"); }
 extern "C" void hb_he_neg(hb_ctx *ctx, hb_ct *ct) {
   need_ct(ct, "hb_he_neg");
   const int W = hb::words_of_level(ctx->ht, ct->l), k = ctx->ht.logq_l[ct->l];

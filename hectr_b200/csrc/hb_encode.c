@@ -168,3 +168,9 @@ void hb_ring_decode(const hb_ring *r, unsigned slots, const uint64_t *words, uns
   for (unsigned i = 0; i < slots; i++) { m[2 * i] = re[i]; m[2 * i + 1] = im[i]; }
   free(re); free(im);
 }
+
+/* he_const_pt (he-encode.c:119-125): only coefficients 0 and n/2 are written */
+void hb_ring_const(const hb_ring *r, double re, double im, double Delta, uint64_t *words, unsigned W) {
+  store_rounded(words, r->n, W, 0, round((double)((long double)re * Delta)));
+  store_rounded(words, r->n, W, r->n / 2, round((double)((long double)im * Delta)));
+}

@@ -766,6 +766,41 @@ __global__ void k_ct_addsub(const uint64_t *__restrict__ a, const uint64_t *__re
   }
 }
 
+// he_addpt / he_subpt (he-add.c:80-123): c0 +- pt, c1 only re-centred; pt is one polynomial [WC][N] shared by the batch.
+__global__ void k_ct_addpt(const uint64_t *__restrict__ a, const uint64_t *__restrict__ pt, uint64_t *__restrict__ out, int W, int k,
+                           int op, unsigned N, size_t npoly) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= npoly * N) return;
+  const size_t q = gid / N, i = gid % N;
+  const uint64_t *pa = a + q * W * N + i;
+  const uint64_t *pb = (q & 1) ? nullptr : pt + i;
+  uint64_t *po = out + q * W * N + i;
+  uint64_t carry = op;                      // x - y = x + ~y + 1
+  uint64_t fill = 0;
+  bool done = false;
+  for (int w = 0; w < W; w++) {
+    uint64_t r;
+    if (done) r = fill;
+    else {
+      const uint64_t x = pa[(size_t)w * N], y = pb ? pb[(size_t)w * N] : 0;
+      const uint64_t rhs = op ? ~y : y;
+      const uint64_t s = x + rhs;
+      const uint64_t c1 = s < rhs;
+      const uint64_t s2 = s + carry;
+      const uint64_t c2 = s2 < carry;
+      carry = c1 | c2;
+      r = s2;
+      const int kk = k - 64 * w;
+      if (kk <= 64) {
+        if (kk < 64) r = (uint64_t)(((int64_t)(r << (64 - kk))) >> (64 - kk));
+        fill = (uint64_t)((int64_t)r >> 63);
+        done = true;
+      }
+    }
+    po[(size_t)w * N] = r;
+  }
+}
+
 // out = smod(sum_{g < G} a[g], 2^k): the he_add chain over the giant steps of he_gemv (he-algo.c:81-84).  Each he_add
 // centres its result; every representative is congruent mod 2^k, so one centring of the full sum gives the same words.
 __global__ void k_ct_sum(const uint64_t *__restrict__ a, size_t gstride, unsigned G, uint64_t *__restrict__ out, int W, int k,

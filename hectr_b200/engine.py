@@ -213,6 +213,72 @@ class Engine:
         self.lib.hb_he_mul(self.ctx, C.byref(r.h), C.byref(a.h), C.byref(b.h), rlk.arr)
         return r
 
+    def he_const_pt(self, num: complex, pt: HbPt | None = None) -> HbPt:
+        """he_const_pt: writes coefficients 0 and N/2 only; a fresh handle is zero-filled."""
+        if pt is None:
+            pt = HbPt()
+            self.lib.hb_pt_alloc(self.ctx, C.byref(pt))
+        num = complex(num)
+        self.lib.hb_he_const_pt(self.ctx, C.byref(pt), num.real, num.imag)
+        return pt
+
+    def he_addpt(self, a, pt: HbPt, out=None):
+        r = out or self._new_like(a)
+        self.lib.hb_he_addpt(self.ctx, C.byref(r.h), C.byref(a.h), C.byref(pt))
+        return r
+
+    def he_subpt(self, a, pt: HbPt, out=None):
+        r = out or self._new_like(a)
+        self.lib.hb_he_subpt(self.ctx, C.byref(r.h), C.byref(a.h), C.byref(pt))
+        return r
+
+    # ---- he-algo.c compositions (hb_algo.cpp) -------------------------------------------------------------
+    def he_sum(self, a, rk: EvalKeys):
+        r = self._new_like(a)
+        self.lib.hb_he_sum(self.ctx, C.byref(r.h), C.byref(a.h), rk.arr)
+        return r
+
+    def he_idx(self, a, idx: int, rk: EvalKeys):
+        r = self._new_like(a)
+        self.lib.hb_he_idx(self.ctx, C.byref(r.h), C.byref(a.h), idx, rk.arr)
+        return r
+
+    def he_nrm2(self, a, rlk: EvalKeys, ck: EvalKeys, rk: EvalKeys):
+        r = self._new_like(a)
+        self.lib.hb_he_nrm2(self.ctx, C.byref(r.h), C.byref(a.h), rlk.arr, ck.arr, rk.arr)
+        return r
+
+    def he_inv(self, a, rlk: EvalKeys, iters: int):
+        r = self._new_like(a)
+        self.lib.hb_he_inv(self.ctx, C.byref(r.h), C.byref(a.h), rlk.arr, iters)
+        return r
+
+    def he_sqrt(self, a, rlk: EvalKeys, iters: int):
+        r = self._new_like(a)
+        self.lib.hb_he_sqrt(self.ctx, C.byref(r.h), C.byref(a.h), rlk.arr, iters)
+        return r
+
+    def he_sigmoid(self, a, rlk: EvalKeys):
+        r = self._new_like(a)
+        self.lib.hb_he_sigmoid(self.ctx, C.byref(r.h), C.byref(a.h), rlk.arr)
+        return r
+
+    def he_log(self, a, rlk: EvalKeys):
+        r = self._new_like(a)
+        self.lib.hb_he_log(self.ctx, C.byref(r.h), C.byref(a.h), rlk.arr)
+        return r
+
+    def he_exp(self, coef: complex, a, rlk: EvalKeys, iters: int):
+        r = self._new_like(a)
+        coef = complex(coef)
+        self.lib.hb_he_exp(self.ctx, C.byref(r.h), coef.real, coef.imag, C.byref(a.h), rlk.arr, iters)
+        return r
+
+    def he_cmp(self, a, b, rlk: EvalKeys, iters: int, alpha: int):
+        r = self._new_like(a)
+        self.lib.hb_he_cmp(self.ctx, C.byref(r.h), C.byref(a.h), C.byref(b.h), rlk.arr, iters, alpha)
+        return r
+
     def he_rot(self, a, rot: int, rk: EvalKeys):
         self.lib.hb_he_rot(self.ctx, C.byref(a.h), rot, rk.arr)
         return a

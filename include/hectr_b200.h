@@ -129,11 +129,14 @@ void hb_evk_free(hb_ctx *ctx, hb_evk *evk);
 void hb_encode(const hb_ctx *ctx, const double *m, double Delta, uint64_t *words);
 void hb_decode(const hb_ctx *ctx, const uint64_t *words, unsigned W, double Delta, double *m);
 void hb_he_ecd(hb_ctx *ctx, hb_pt *pt, const double *m);       /* he_ecd: encode at Delta and upload */
+void hb_he_const_pt(hb_ctx *ctx, hb_pt *pt, double re, double im);   /* he_const_pt he-encode.c:119-125 */
 
 /* ---- evaluation ------------------------------------------------------------------------------------ */
 void hb_he_add(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b);        /* he_add   he-add.c:32-54 */
 void hb_he_sub(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b);        /* he_sub   he-add.c:57-79 */
 void hb_he_neg(hb_ctx *ctx, hb_ct *ct);                                        /* he_neg   he-add.c:124-142 */
+void hb_he_addpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt);  /* he_addpt he-add.c:80-100 */
+void hb_he_subpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt);  /* he_subpt he-add.c:103-123 */
 void hb_he_rs(hb_ctx *ctx, hb_ct *ct);                                         /* he_rs    he-rescale.c:33-54 */
 void hb_he_moddown(hb_ctx *ctx, hb_ct *ct);                                    /* he_moddown he-rescale.c:56-70 */
 void hb_he_mulpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt);  /* he_mulpt he-mult.c:159-196 */
@@ -151,6 +154,17 @@ void hb_ctr_hempc_eval(hb_ctx *ctx, hb_ct *up, const double *Ka, const double *K
 void hb_ctr_hempc_eval_host(hb_ctx *ctx, unsigned batch, unsigned l, const double *Ka, const double *Kb,
                             const uint64_t *in_xhat, const uint64_t *in_xr, const uint64_t *in_uhat,
                             const uint64_t *in_ur, const hb_evk *rk, uint64_t *out_up);
+
+/* ---- compositions of he-algo.c, built only from the entry points above: hb_algo.cpp -------------- */
+void hb_he_sum(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rk);                       /* he_sum  he-algo.c:95-103 */
+void hb_he_idx(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, unsigned idx, const hb_evk *rk);         /* he_idx  :105-112 */
+void hb_he_nrm2(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rlk, const hb_evk *ck, const hb_evk *rk); /* he_nrm2 :114-125 */
+void hb_he_inv(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rlk, unsigned iter);       /* he_inv  :131-164 */
+void hb_he_sqrt(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rlk, unsigned iter);      /* he_sqrt :166-206 */
+void hb_he_sigmoid(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rlk);                  /* he_sigmoid :208-277 */
+void hb_he_log(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rlk);                      /* he_log  :279-362 */
+void hb_he_exp(hb_ctx *ctx, hb_ct *dst, double a_re, double a_im, const hb_ct *ct, const hb_evk *rlk, unsigned iter); /* he_exp :364-458 */
+void hb_he_cmp(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct1, const hb_ct *ct2, const hb_evk *rlk, unsigned iter, unsigned alpha); /* he_cmp :460-530 */
 
 /* ---- client side on the device: he_enc_pk / he_dec, he-encrypt.c:37-74,107-123 ------------------ */
 /* Sampling stays with the caller (the reference's deterministic stream defines every ciphertext): v (sample_zo), e0, e1

@@ -376,6 +376,57 @@ class Ref:
         self.lib.he_gemv(C.byref(r), A.ctypes.data_as(C.c_void_p), C.byref(a), rk)
         return r
 
+    # ---- he-add.c:80-123, he-encode.c:119-125, he-algo.c:95-548 -----------------
+    def const_pt(self, num: complex, pt=None):
+        """he_const_pt takes a _Complex double by value: two SSE eightbytes, i.e. two double arguments (SysV x86-64)."""
+        pt = pt or self.alloc_pt()
+        num = complex(num)
+        self.lib.he_const_pt(C.byref(pt), C.c_double(num.real), C.c_double(num.imag))
+        return pt
+
+    def addpt(self, a, pt):
+        r = self.alloc_ct()
+        self.lib.he_addpt(C.byref(r), C.byref(a), C.byref(pt))
+        return r
+
+    def subpt(self, a, pt):
+        r = self.alloc_ct()
+        self.lib.he_subpt(C.byref(r), C.byref(a), C.byref(pt))
+        return r
+
+    def _algo(self, name, *args):
+        r = self.alloc_ct()
+        self._quiet(lambda: getattr(self.lib, name)(C.byref(r), *args))
+        return r
+
+    def he_sum(self, a, rk):
+        return self._algo("he_sum", C.byref(a), rk)
+
+    def he_idx(self, a, idx, rk):
+        return self._algo("he_idx", C.byref(a), C.c_uint(idx), rk)
+
+    def he_nrm2(self, a, rlk, ck, rk):
+        return self._algo("he_nrm2", C.byref(a), C.byref(rlk), C.byref(ck), rk)
+
+    def he_inv(self, a, rlk, iters):
+        return self._algo("he_inv", C.byref(a), C.byref(rlk), C.c_uint(iters))
+
+    def he_sqrt(self, a, rlk, iters):
+        return self._algo("he_sqrt", C.byref(a), C.byref(rlk), C.c_uint(iters))
+
+    def he_sigmoid(self, a, rlk):
+        return self._algo("he_sigmoid", C.byref(a), C.byref(rlk))
+
+    def he_log(self, a, rlk):
+        return self._algo("he_log", C.byref(a), C.byref(rlk))
+
+    def he_exp(self, coef: complex, a, rlk, iters):
+        coef = complex(coef)
+        return self._algo("he_exp", C.c_double(coef.real), C.c_double(coef.imag), C.byref(a), C.byref(rlk), C.c_uint(iters))
+
+    def he_cmp(self, a, b, rlk, iters, alpha):
+        return self._algo("he_cmp", C.byref(a), C.byref(b), C.byref(rlk), C.c_uint(iters), C.c_uint(alpha))
+
     # ---- limb-level internals ---------------------------------------------------------------------
     def ntt(self, a: np.ndarray, d: int, inverse=False) -> np.ndarray:
         a = np.ascontiguousarray(a, dtype=np.uint64).copy()
