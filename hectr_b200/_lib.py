@@ -105,6 +105,7 @@ PROTOTYPES = {
     "hb_he_log": (None, [ctx_p, ct_p, ct_p, evk_p]),
     "hb_he_exp": (None, [ctx_p, ct_p, C.c_double, C.c_double, ct_p, evk_p, C.c_uint]),
     "hb_he_cmp": (None, [ctx_p, ct_p, ct_p, ct_p, evk_p, C.c_uint, C.c_uint]),
+    "hb_he_cmppt": (None, [ctx_p, ct_p, ct_p, pt_p, evk_p, C.c_uint, C.c_uint]),
     "hb_he_rs": (None, [ctx_p, ct_p]),
     "hb_he_moddown": (None, [ctx_p, ct_p]),
     "hb_he_mulpt": (None, [ctx_p, ct_p, ct_p, pt_p]),
@@ -119,6 +120,8 @@ PROTOTYPES = {
     "hb_sk_free": (None, [ctx_p, C.POINTER(HbSk)]),
     "hb_he_enc_pk": (None, [ctx_p, ct_p, vp, C.c_double, evk_p, vp, vp, vp]),
     "hb_he_dec": (None, [ctx_p, vp, ct_p, C.POINTER(HbSk)]),
+    "hb_genswk_words": (C.c_uint, [ctx_p]),
+    "hb_he_genswk": (None, [ctx_p, C.c_uint, vp, vp, vp, C.POINTER(HbSk), vp, vp]),
     "hb_ntt_forward": (None, [ctx_p, vp, vp, C.c_size_t, C.c_uint, C.c_uint, C.c_int]),
     "hb_ntt_inverse": (None, [ctx_p, vp, vp, C.c_size_t, C.c_uint, C.c_uint]),
     "hb_ntt_forward_host": (None, [ctx_p, vp, vp, C.c_size_t, C.c_uint, C.c_uint, C.c_int]),

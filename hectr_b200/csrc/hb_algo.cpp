@@ -260,4 +260,17 @@ void hb_he_cmp(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct1, const hb_ct *ct2, cons
   hb_ct_copy(ctx, dst, a);
 }
 
+// he_cmppt (he-algo.c:532-548): the same with a plaintext second operand
+void hb_he_cmppt(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_pt *pt, const hb_evk *rlk, unsigned iter, unsigned alpha) {
+  // The reference negates the UNSIGNED alpha (he-algo.c:537): 2^(2^32 - alpha) overflows to infinity, alpha / log2(inf) = 0,
+  // and the conversion of log2(0) = -inf to unsigned yields 0 on x86-64 (cvttsd2si, low half).  So he_cmppt never runs the
+  // squaring rounds, whatever alpha; reproduced, and pinned by test_cmppt with alpha = 2.
+  (void)alpha;
+  const unsigned t = 0;
+  Ct a(ctx, ct->batch);
+  hb_he_addpt(ctx, a, ct, pt);
+  cmp_core(ctx, a, ct, rlk, iter, t);
+  hb_ct_copy(ctx, dst, a);
+}
+
 }  // extern "C"

@@ -13,6 +13,7 @@
 #include "hb_tables32.hpp"
 #include "hb_kernels.cuh"
 #include "hb_dev32.cuh"
+#include "hb_keygen.cuh"
 
 extern "C" {
 struct hb_ring;
@@ -1461,6 +1462,84 @@ extern "C" void hb_he_dec(hb_ctx *ctx, uint64_t *pt_words, const hb_ct *ct, cons
   CUDA_OK(cudaMemcpyAsync(pt_words, out, (size_t)batch * W * N * 8, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_OK(cudaStreamSynchronize(ctx->stream));
   if (tmp_scaled) hb_dev_free(ctx, tmp_scaled);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// he_genswk on the device: he-kem.c:74-119.  Sampling stays with the caller.
+// ---------------------------------------------------------------------------------------------------------
+extern "C" unsigned hb_genswk_words(const hb_ctx *ctx) { return (ctx->ht.nbitsPqL + 1 + 63) / 64; }
+
+extern "C" void hb_he_genswk(hb_ctx *ctx, unsigned nkeys, const uint64_t *a_words, const int64_t *e, const int64_t *sp, const hb_sk *sk,
+                             uint64_t *out_p0, uint64_t *out_p1) {
+  if (!sk || !sk->hat) hb_die("hb_he_genswk: secret key is not loaded");
+  if (!nkeys) return;
+  const hb::HostTables &h = ctx->ht;
+  const size_t N = h.N;
+  const hb::BigU &P = h.Pfull[h.dim];
+  const hb::BigU M = P.shl(h.logq_l[h.L]);                          // P q_L
+  const unsigned D = (M.bits() + h.logn) / 59 + 1;                  // he-kem.c:83
+  if (D > h.dimub) hb_die("hb_he_genswk: needs %u primes but the chain has %u", D, h.dimub);
+  const hb::BigU &PD = h.Pfull[D];
+  const unsigned WA = hb_genswk_words(ctx), WX = (PD.bits() + 72 + 63) / 64;
+  if (WX > (unsigned)hbkg::MAXW || WA > WX) hb_die("hb_he_genswk: %u-word intermediates exceed the built maximum %d", WX, hbkg::MAXW);
+  if (M.bits() + 64 * hbkg::TOPW < 64 * WX + 128) hb_die("hb_he_genswk: P q_L is too narrow for the quotient estimate window");
+  const unsigned Dmax = D > h.dimevk ? D : h.dimevk;
+  // ---- constants (host big integers), one upload ----
+  std::vector<uint64_t> hc;
+  auto put = [&](const std::vector<uint64_t> &v) { const size_t off = hc.size(); hc.insert(hc.end(), v.begin(), v.end()); return off; };
+  std::vector<uint64_t> primes(Dmax), inv(D), phat((size_t)D * WX);
+  for (unsigned d = 0; d < Dmax; d++) primes[d] = h.primes[d].p;
+  for (unsigned d = 0; d < D; d++) {
+    const hb::BigU ph = PD.divmod_u64(primes[d], nullptr);
+    inv[d] = hb::powmod(ph.mod_u64(primes[d]), primes[d] - 2, primes[d]);
+    const std::vector<uint64_t> lo = ph.low(WX);
+    std::copy(lo.begin(), lo.end(), phat.begin() + (size_t)d * WX);
+  }
+  const std::vector<uint64_t> Mw = M.low(WX), Mhw = M.shr1().low(WX);
+  std::vector<uint64_t> Mlo(WX);                                    // floor(M/2) - M in two's complement
+  {
+    uint64_t br = 0;
+    for (unsigned w = 0; w < WX; w++) {
+      const uint64_t x = Mhw[w], y = Mw[w];
+      Mlo[w] = x - y - br;
+      br = (x < y) || (x == y && br);
+    }
+  }
+  const size_t o_pr = put(primes), o_inv = put(inv), o_ph = put(phat), o_PD = put(PD.low(WX)), o_PDh = put(PD.shr1().low(WX)),
+               o_M = put(Mw), o_Mh = put(Mhw), o_Mlo = put(Mlo), o_P = put(P.low(WX));
+  uint64_t *dc = (uint64_t *)hb_dev_alloc(ctx, hc.size() * 8);
+  CUDA_OK(cudaMemcpyAsync(dc, hc.data(), hc.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+  hbkg::Consts C{dc + o_pr, dc + o_inv, dc + o_ph, dc + o_PD, dc + o_PDh, dc + o_M, dc + o_Mh, dc + o_Mlo, dc + o_P, D, WX, WA, (unsigned)N};
+  // ---- inputs ----
+  const size_t aw = (size_t)nkeys * WA * N, kn = (size_t)nkeys * N;
+  uint64_t *da = (uint64_t *)hb_dev_alloc(ctx, aw * 8);
+  int64_t *de = (int64_t *)hb_dev_alloc(ctx, kn * 8), *dsp = (int64_t *)hb_dev_alloc(ctx, kn * 8);
+  CUDA_OK(cudaMemcpyAsync(da, a_words, aw * 8, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_OK(cudaMemcpyAsync(de, e, kn * 8, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_OK(cudaMemcpyAsync(dsp, sp, kn * 8, cudaMemcpyHostToDevice, ctx->stream));
+  // ---- a*sk on D primes: decompose, transform, pointwise, inverse transform (poly_mul, poly.c:84-107) ----
+  const size_t limbsK = (size_t)nkeys * D * N;
+  uint64_t *t0 = (uint64_t *)hb_dev_alloc(ctx, limbsK * 8), *t1 = (uint64_t *)hb_dev_alloc(ctx, limbsK * 8);
+  launch(ctx, "k_decompose_wide", hbkg::k_decompose_wide, (unsigned)((limbsK + 255) / 256), 256, 0, 1, (const uint64_t *)da, (int)WA, (size_t)nkeys,
+         C.primes, D, t0, (unsigned)N);
+  do_ntt_fwd(ctx, t0, t1, (size_t)nkeys * D, 0, D, false);
+  launch(ctx, "k_pointmul", hbkg::k_pointmul, (unsigned)((limbsK + 255) / 256), 256, 0, 1, (const uint64_t *)t1, (const uint64_t *)sk->hat, C.primes, D, t0,
+         (unsigned)N, (size_t)nkeys);
+  do_ntt_inv(ctx, t0, t1, (size_t)nkeys * D, 0, D);
+  // ---- exact product, -x + e + P sp, centred mod P q_L; a centred mod P q_L ----
+  uint64_t *dv = (uint64_t *)hb_dev_alloc(ctx, 2 * aw * 8), *dac = dv + aw;
+  launch(ctx, "k_genswk_tail", hbkg::k_tail, (unsigned)((kn + 127) / 128), 128, 0, 1, (const uint64_t *)t1, C, (const int64_t *)de, (const int64_t *)dsp,
+         (const uint64_t *)da, dv, dac, nkeys);
+  // ---- both halves onto the dimevk key primes, transformed in the reference's [0,p] representation (he-kem.c:103-110) ----
+  const size_t limbsE = (size_t)2 * nkeys * h.dimevk * N;
+  uint64_t *r0 = (uint64_t *)hb_dev_alloc(ctx, limbsE * 8), *r1 = (uint64_t *)hb_dev_alloc(ctx, limbsE * 8);
+  launch(ctx, "k_decompose_wide", hbkg::k_decompose_wide, (unsigned)((limbsE + 255) / 256), 256, 0, 1, (const uint64_t *)dv, (int)WA, (size_t)2 * nkeys,
+         C.primes, h.dimevk, r0, (unsigned)N);
+  do_ntt_fwd(ctx, r0, r1, (size_t)2 * nkeys * h.dimevk, 0, h.dimevk, true);
+  CUDA_OK(cudaMemcpyAsync(out_p0, r1, limbsE * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_OK(cudaMemcpyAsync(out_p1, r1 + limbsE / 2, limbsE * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  for (void *q : {(void *)dc, (void *)da, (void *)de, (void *)dsp, (void *)t0, (void *)t1, (void *)dv, (void *)r0, (void *)r1}) hb_dev_free(ctx, q);
 }
 
 // ---------------------------------------------------------------------------------------------------------

@@ -279,6 +279,11 @@ class Engine:
         self.lib.hb_he_cmp(self.ctx, C.byref(r.h), C.byref(a.h), C.byref(b.h), rlk.arr, iters, alpha)
         return r
 
+    def he_cmppt(self, a, pt: HbPt, rlk: EvalKeys, iters: int, alpha: int):
+        r = self._new_like(a)
+        self.lib.hb_he_cmppt(self.ctx, C.byref(r.h), C.byref(a.h), C.byref(pt), rlk.arr, iters, alpha)
+        return r
+
     def he_rot(self, a, rot: int, rk: EvalKeys):
         self.lib.hb_he_rot(self.ctx, C.byref(a.h), rot, rk.arr)
         return a
@@ -329,6 +334,23 @@ class Engine:
         k = HbSk()
         self.lib.hb_sk_upload(self.ctx, C.byref(k), _ptr(s))
         return k
+
+    def genswk_words(self) -> int:
+        return int(self.lib.hb_genswk_words(self.ctx))
+
+    def he_genswk(self, a_words: np.ndarray, e: np.ndarray, sp: np.ndarray, sk: HbSk) -> np.ndarray:
+        """he_genswk with the caller's samples, nkeys keys at once: a_words[nkeys][genswk_words][N] (sample_uniform),
+        e, sp int64[nkeys][N] -> uint64[nkeys][2][dimevk][N], the layout ``Engine.keys`` takes."""
+        a_words = np.ascontiguousarray(a_words, dtype=np.uint64)
+        nkeys = a_words.shape[0]
+        assert a_words.shape == (nkeys, self.genswk_words(), self.n)
+        e = np.ascontiguousarray(e, dtype=np.int64)
+        sp = np.ascontiguousarray(sp, dtype=np.int64)
+        assert e.shape == sp.shape == (nkeys, self.n)
+        p0 = np.empty((nkeys, self.info.dimevk, self.n), dtype=np.uint64)
+        p1 = np.empty_like(p0)
+        self.lib.hb_he_genswk(self.ctx, nkeys, _ptr(a_words), _ptr(e), _ptr(sp), C.byref(sk), _ptr(p0), _ptr(p1))
+        return np.stack([p0, p1], axis=1)
 
     def he_enc_pk(self, pt_words: np.ndarray, pk: HbEvk, v: np.ndarray, e0: np.ndarray, e1: np.ndarray, pt_nu=None) -> Ciphertext:
         """he_enc_pk with the caller's samples: pt_words[batch][W_L][N], v/e0/e1 int64[batch][N]."""

@@ -165,6 +165,7 @@ void hb_he_sigmoid(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rlk);
 void hb_he_log(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rlk);                      /* he_log  :279-362 */
 void hb_he_exp(hb_ctx *ctx, hb_ct *dst, double a_re, double a_im, const hb_ct *ct, const hb_evk *rlk, unsigned iter); /* he_exp :364-458 */
 void hb_he_cmp(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct1, const hb_ct *ct2, const hb_evk *rlk, unsigned iter, unsigned alpha); /* he_cmp :460-530 */
+void hb_he_cmppt(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_pt *pt, const hb_evk *rlk, unsigned iter, unsigned alpha); /* he_cmppt :532-548 */
 
 /* ---- client side on the device: he_enc_pk / he_dec, he-encrypt.c:37-74,107-123 ------------------ */
 /* Sampling stays with the caller (the reference's deterministic stream defines every ciphertext): v (sample_zo), e0, e1
@@ -176,6 +177,16 @@ void hb_he_enc_pk(hb_ctx *ctx, hb_ct *ct, const uint64_t *pt_words, double pt_nu
                   const int64_t *e0, const int64_t *e1);
 /* m = smod(c1 sk + c0, q_l): HOST pt_words[batch][W_l][N] (synchronises); the plaintext's nu is ct->nu */
 void hb_he_dec(hb_ctx *ctx, uint64_t *pt_words, const hb_ct *ct, const hb_sk *sk);
+
+/* ---- key generation on the device: he_genswk, he-kem.c:74-119 ------------------------------------- */
+/* For nkeys keys at once:  p1 = smod(a, P q_L),  p0 = smod(-a sk + e + P sp, P q_L),  both as dimevk transform limbs in the
+ * reference's [0,p] representation -- what hb_evk_upload takes.  Sampling stays with the caller: a (sample_uniform below
+ * 2^nbits(P q_L)) as HOST words [nkeys][hb_genswk_words][N], e (sample_error) and sp -- the polynomial switched from:
+ * poly_rot / poly_conj of sk (he_genrk, he_genck) or sk^2 mod q_L (he_genrlk) -- as HOST int64 [nkeys][N].
+ * out_p0, out_p1: HOST [nkeys][dimevk][N].  Synchronises. */
+unsigned hb_genswk_words(const hb_ctx *ctx);
+void hb_he_genswk(hb_ctx *ctx, unsigned nkeys, const uint64_t *a_words, const int64_t *e, const int64_t *sp, const hb_sk *sk,
+                  uint64_t *out_p0, uint64_t *out_p1);
 
 /* ---- limb-level entry points (parity tests, NTT microbench) ---------------------------------------- */
 /* ntt / invntt (GPQHE/src/ntt.c:37-73) over nlimbs limbs in DEVICE memory; limb j uses prime d0 + j % D.

@@ -315,6 +315,20 @@ class Ref:
         """sample_error (sample.c:74-82) -> int64[N]."""
         return self._sample(self.lib.sample_error)
 
+    def sample_uniform_PqL(self) -> PolyMpi:
+        """sample_uniform(., P q_L) (sample.c:133-141), he_genswk's draw of swk.p1 (he-kem.c:94)."""
+        p = self.alloc_poly()
+        self.lib.sample_uniform(C.byref(p), self.hectx.PqL)
+        return p
+
+    def poly_mul_PqL(self, a: PolyMpi, b: PolyMpi, dim: int) -> list:
+        """poly_mul(a, b, dim, P q_L) (poly.c:84-107) -> python ints (centred mod P q_L)."""
+        r = self.alloc_poly()
+        self.lib.poly_mul(C.byref(r), C.byref(a), C.byref(b), C.c_uint(dim), self.hectx.PqL)
+        out = [self.mpi_int(r.coeffs[i]) for i in range(self.n)]
+        self.lib.poly_mpi_free(C.byref(r))
+        return out
+
     def poly_mul_words(self, a: PolyMpi, b_words: np.ndarray, dim: int, logm: int, W: int) -> np.ndarray:
         """poly_mul(a, b, dim, 2^logm) (poly.c:84-107) -> words[W][N]."""
         b = self.alloc_poly()
@@ -426,6 +440,9 @@ class Ref:
 
     def he_cmp(self, a, b, rlk, iters, alpha):
         return self._algo("he_cmp", C.byref(a), C.byref(b), C.byref(rlk), C.c_uint(iters), C.c_uint(alpha))
+
+    def he_cmppt(self, a, pt, rlk, iters, alpha):
+        return self._algo("he_cmppt", C.byref(a), C.byref(pt), C.byref(rlk), C.c_uint(iters), C.c_uint(alpha))
 
     # ---- limb-level internals ---------------------------------------------------------------------
     def ntt(self, a: np.ndarray, d: int, inverse=False) -> np.ndarray:

