@@ -79,7 +79,7 @@ struct hb_ctx {
   std::multimap<size_t, uint64_t *> pool;
   std::map<uint64_t *, size_t> live;
   hb_ring *ring = nullptr;
-  bool have32 = false;              // the 30-bit plaintext-product path is built for this ring (2^10 <= N <= 2^13)
+  bool have32 = false;              // the 30-bit plaintext-product path is built for this ring (2^11 <= N <= 2^13)
   hb::HostTables32 ht32;
   hb32::Tables32 dt32;
   std::map<unsigned, uint16_t *> perms;   // g -> device perm_g[N] (k_ks_baby)
@@ -153,7 +153,8 @@ static void want_smem(K kernel, size_t bytes) {
 #ifdef HB_DEV_FAST
 #define HB_LOGN32_CASES(X) X(12)
 #else
-#define HB_LOGN32_CASES(X) X(10) X(11) X(12) X(13)
+// N = 2^10 admits q <= 2^27 only (precomp.c:338-350): no matvec fits, so the 30-bit kernels start at 2^11
+#define HB_LOGN32_CASES(X) X(11) X(12) X(13)
 #endif
 
 // ---- 30-bit plaintext-product path (hb_dev32.cuh) -----------------------------------------------------------------

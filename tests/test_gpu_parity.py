@@ -388,14 +388,16 @@ def test_fast_tail_equals_exact_tail(cfgA, monkeypatch):
         eng2.close()
 
 
-@pytest.mark.parametrize("slots,level", [(16, 2), (16, 1), (64, 2)])
-def test_pt30_basis_equals_59bit_basis(slots, level, monkeypatch):
+@pytest.mark.parametrize("logn,logq,logDelta,slots,level", [(12, 109, 50, 16, 2), (12, 109, 50, 16, 1), (12, 109, 50, 64, 2),
+                                                             (11, 50, 24, 32, 2), (13, 218, 50, 16, 4)])
+def test_pt30_basis_equals_59bit_basis(logn, logq, logDelta, slots, level, monkeypatch):
     """he_gemv's plaintext products run on the engine's internal 30-bit basis when the exact product fits P_D
     (hb_tables32.hpp); HB_NO_PT30 keeps them on the reference's 59-bit primes.  Both must give the same words: 128
-    random ciphertexts at full size, dense random matrices (every diagonal non-zero), synthetic keys."""
+    random ciphertexts at full size, dense random matrices (every diagonal non-zero), synthetic keys; every ring size the
+    30-bit kernels are built for (their pass structure and bank-conflict lane swap depend on N)."""
     from hectr_b200 import Engine
-    params = (12, 109, slots, 50)
-    rng = np.random.default_rng(97 + slots + level)
+    params = (logn, logq, slots, logDelta)       # q at most the reference's bound for the ring (precomp.c:338-350)
+    rng = np.random.default_rng(97 + slots + level + logn)
     eng = Engine(*params)
     monkeypatch.setenv("HB_NO_PT30", "1")
     eng59 = Engine(*params)
