@@ -120,6 +120,12 @@ PROTOTYPES = {
     "hb_sk_free": (None, [ctx_p, C.POINTER(HbSk)]),
     "hb_he_enc_pk": (None, [ctx_p, ct_p, vp, C.c_double, evk_p, vp, vp, vp]),
     "hb_he_dec": (None, [ctx_p, vp, ct_p, C.POINTER(HbSk)]),
+    "hb_wire_ct_bytes": (C.c_size_t, [ctx_p, C.c_uint, C.c_uint]),
+    "hb_wire_evk_bytes": (C.c_size_t, [ctx_p]),
+    "hb_ct_serialize": (C.c_size_t, [ctx_p, ct_p, vp, C.c_size_t]),
+    "hb_ct_deserialize": (None, [ctx_p, ct_p, vp, C.c_size_t]),
+    "hb_evk_serialize": (C.c_size_t, [ctx_p, vp, vp, vp, C.c_size_t]),
+    "hb_evk_deserialize": (None, [ctx_p, evk_p, vp, C.c_size_t]),
     "hb_genswk_words": (C.c_uint, [ctx_p]),
     "hb_he_genswk": (None, [ctx_p, C.c_uint, vp, vp, vp, C.POINTER(HbSk), vp, vp]),
     "hb_ntt_forward": (None, [ctx_p, vp, vp, C.c_size_t, C.c_uint, C.c_uint, C.c_int]),

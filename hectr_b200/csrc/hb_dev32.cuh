@@ -306,8 +306,14 @@ namespace hb32 {
 // ===============================================================================================================
 
 // One CTA per polynomial: the W words of 16 coefficients per thread are read once and decomposed onto every limb.
+#ifndef HB32_PN_MINB
+#define HB32_PN_MINB 2
+#endif
+#ifndef HB32_MA_MINB
+#define HB32_MA_MINB 2
+#endif
 template <int LOGN, int WT>
-__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, 2)
+__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_PN_MINB)
 k32_poly_ntt_all(const uint64_t *__restrict__ src, size_t poly_stride, uint32_t *__restrict__ out, Tables32 T, unsigned D) {
   typedef Cfg32<LOGN> G;
   constexpr int PER = G::N / G::THREADS;                      // coefficients per thread
@@ -359,7 +365,7 @@ k32_poly_ntt_all(const uint64_t *__restrict__ src, size_t poly_stride, uint32_t 
 // One CTA per (polynomial q, limb d): the NJ rotated transforms hat[j][q][d] are read once into registers and serve every
 // giant step g < ngroups:  chat[g][q][d] = y-weighted invntt( sum_j hat[j][q][d] o pthat[g*NJ + j][d] ).
 template <int LOGN, int NJ>
-__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, 2)
+__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_MA_MINB)
 k32_mulacc_intt_all(const uint32_t *__restrict__ hat, size_t hat_jstride, const uint32_t *__restrict__ pthat_all, size_t pthat_gstride,
                     unsigned ngroups, unsigned nq, uint32_t *__restrict__ chat, Tables32 T, unsigned D) {
   typedef Cfg32<LOGN> G;

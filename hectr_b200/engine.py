@@ -335,6 +335,32 @@ class Engine:
         self.lib.hb_sk_upload(self.ctx, C.byref(k), _ptr(s))
         return k
 
+    # ---- wire format (hb_wire.cpp) -----------------------------------------------------------------------------
+    def ct_serialize(self, a: Ciphertext) -> bytes:
+        n = int(self.lib.hb_wire_ct_bytes(self.ctx, a.l, a.batch))
+        buf = C.create_string_buffer(n)
+        got = int(self.lib.hb_ct_serialize(self.ctx, C.byref(a.h), buf, n))
+        assert got == n
+        return buf.raw
+
+    def ct_deserialize(self, msg: bytes, batch: int) -> Ciphertext:
+        r = Ciphertext(self, batch)
+        self.lib.hb_ct_deserialize(self.ctx, C.byref(r.h), msg, len(msg))
+        return r
+
+    def evk_serialize(self, key: np.ndarray) -> bytes:
+        key = np.ascontiguousarray(key, dtype=np.uint64)
+        assert key.shape == (2, self.info.dimevk, self.n)
+        n = int(self.lib.hb_wire_evk_bytes(self.ctx))
+        buf = C.create_string_buffer(n)
+        assert int(self.lib.hb_evk_serialize(self.ctx, _ptr(key[0]), _ptr(key[1]), buf, n)) == n
+        return buf.raw
+
+    def evk_deserialize(self, msg: bytes) -> HbEvk:
+        k = HbEvk()
+        self.lib.hb_evk_deserialize(self.ctx, C.byref(k), msg, len(msg))
+        return k
+
     def genswk_words(self) -> int:
         return int(self.lib.hb_genswk_words(self.ctx))
 

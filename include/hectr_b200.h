@@ -188,6 +188,14 @@ unsigned hb_genswk_words(const hb_ctx *ctx);
 void hb_he_genswk(hb_ctx *ctx, unsigned nkeys, const uint64_t *a_words, const int64_t *e, const int64_t *sp, const hb_sk *sk,
                   uint64_t *out_p0, uint64_t *out_p1);
 
+/* ---- wire format (additive: the reference has none).  Layout in hb_wire.cpp. ---------------------------- */
+size_t hb_wire_ct_bytes(const hb_ctx *ctx, unsigned l, unsigned batch);
+size_t hb_wire_evk_bytes(const hb_ctx *ctx);
+size_t hb_ct_serialize(hb_ctx *ctx, const hb_ct *ct, void *buf, size_t cap);          /* bytes written, 0 if cap is too small */
+void hb_ct_deserialize(hb_ctx *ctx, hb_ct *ct, const void *buf, size_t len);          /* ct allocated with the message's batch */
+size_t hb_evk_serialize(const hb_ctx *ctx, const uint64_t *p0, const uint64_t *p1, void *buf, size_t cap);   /* HOST limbs [dimevk][N] */
+void hb_evk_deserialize(hb_ctx *ctx, hb_evk *evk, const void *buf, size_t len);       /* checks, then hb_evk_upload */
+
 /* ---- limb-level entry points (parity tests, NTT microbench) ---------------------------------------- */
 /* ntt / invntt (GPQHE/src/ntt.c:37-73) over nlimbs limbs in DEVICE memory; limb j uses prime d0 + j % D.
  * strict != 0 reproduces the reference's [0,p] forward representation bit for bit; strict == 0 returns
