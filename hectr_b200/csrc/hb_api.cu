@@ -1247,12 +1247,7 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
   do_ks_limb_g(ctx, inner + polyw, bstride, W, SG, h.dimevk, chat, Dk, n2 * batch);
   uint64_t *switched = cts + (size_t)ng * batch * bstride;          // [n2][batch][2][W][N]
   do_ks_finish_g(ctx, chat, Dk, inner, nullptr, bstride, W, TG, switched, W, k, n2 * batch);
-  // 5. outer = sum_i, then he_rs
-  {
-    const size_t npoly = (size_t)batch * 2, total = npoly * N;
-    launch(ctx, "k_ct_sum", hbdev::k_ct_sum, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint64_t *)switched, (size_t)batch * bstride, n2,
-           dst->words, W, k, (unsigned)N, npoly);
-  }
+  // 5. outer = sum_i, then he_rs: one pass (the centred sum never leaves the registers)
   dst->l = l;
   {                                                                 // metadata: the reference's own sequence of updates
     double inu = 0, iB = 0, onu = 0, oB = 0;
@@ -1267,7 +1262,24 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
     }
     dst->nu = onu; dst->B = oB;
   }
-  hb_he_rs(ctx, dst);
+  if (l == 0) hb_die("hb_he_rs: ciphertext is already at level 0");
+  if (W > 16) {                                                    // wider than the fused kernel's registers: two passes
+    const size_t npoly = (size_t)batch * 2, total = npoly * N;
+    launch(ctx, "k_ct_sum", hbdev::k_ct_sum, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint64_t *)switched, (size_t)batch * bstride, n2,
+           dst->words, W, k, (unsigned)N, npoly);
+    hb_he_rs(ctx, dst);
+    return;
+  }
+  {
+    const double n = h.N, Brs = std::sqrt(n / 3.) * (3 + 8 * std::sqrt(64.0));   // precomp.c:417, as hb_he_rs
+    dst->nu /= Delta;
+    dst->B = dst->B / Delta + Brs;
+    dst->l = l - 1;
+    const int Wout = hb::words_of_level(h, l - 1), kout = h.logq_l[l - 1];
+    const size_t npoly = (size_t)batch * 2, total = npoly * N;
+    launch(ctx, "k_ct_sum_rs", hbdev::k_ct_sum_rs, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint64_t *)switched, (size_t)batch * bstride, n2,
+           dst->words, W, k, Wout, (int)h.logDelta, kout, (unsigned)N, npoly);
+  }
 }
 
 extern "C" void hb_he_gemv(hb_ctx *ctx, hb_ct *dst, const double *A, const hb_ct *ct, const hb_evk *rk) {
@@ -1293,11 +1305,21 @@ extern "C" void hb_ctr_hempc_eval(hb_ctx *ctx, hb_ct *up, const double *Ka, cons
   hb_he_sub(ctx, &udiff, uhat, ur);              // hempc.c:255
   hb_he_gemv(ctx, &KaX, Ka, &xdiff, rk);         // hempc.c:257
   hb_he_gemv(ctx, &KbU, Kb, &udiff, rk);         // hempc.c:259
-  hb_he_add(ctx, &du, &KaX, &KbU);               // hempc.c:261
-  hb_he_neg(ctx, &du);                           // hempc.c:262
-  hb_ct_copy(ctx, &ucopy, uhat);                 // hempc.c:264
-  hb_he_moddown(ctx, &ucopy);                    // hempc.c:265
-  hb_he_add(ctx, up, &ucopy, &du);               // hempc.c:266
+  // hempc.c:261-266: he_add(du, KaX, KbU); he_neg(du); he_copy_ct(ucopy, uhat); he_moddown(ucopy); he_add(up, ucopy, du) -- all
+  // of it arithmetic mod q_{l-1} followed by centring, so one pass computes smod(uhat - KaX - KbU, q_{l-1}); the bookkeeping
+  // fields follow the five calls
+  if (KaX.l != KbU.l || uhat->l == 0 || KaX.l != uhat->l - 1) hb_die("hb_ctr_hempc_eval: operands are at different levels");
+  {
+    const hb::HostTables &h = ctx->ht;
+    const double du_nu = KaX.nu >= KbU.nu ? KaX.nu : KbU.nu, du_B = KaX.B + KbU.B;
+    up->l = KaX.l;
+    up->nu = uhat->nu >= du_nu ? uhat->nu : du_nu;
+    up->B = uhat->B + du_B;
+    const int Wu = hb::words_of_level(h, uhat->l), Wout = hb::words_of_level(h, up->l), kout = h.logq_l[up->l];
+    const size_t npoly = (size_t)batch * 2, total = npoly * h.N;
+    launch(ctx, "k_ct_combine", hbdev::k_ct_combine, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint64_t *)uhat->words, Wu,
+           (const uint64_t *)KaX.words, (const uint64_t *)KbU.words, up->words, Wout, kout, h.N, npoly);
+  }
   hb_ct_free(ctx, &xdiff); hb_ct_free(ctx, &udiff); hb_ct_free(ctx, &KaX);
   hb_ct_free(ctx, &KbU); hb_ct_free(ctx, &du); hb_ct_free(ctx, &ucopy);
 }

@@ -766,6 +766,103 @@ __global__ void k_ct_addsub(const uint64_t *__restrict__ a, const uint64_t *__re
   }
 }
 
+// k_ct_sum followed by he_rs (he-rescale.c:33-54) in one pass: the centred sum stays in registers, then the rounded shift by
+// `shift` bits and the centring mod 2^kout -- the end of he_gemv (he-algo.c:81-90).  Win <= 16 words.
+__global__ void k_ct_sum_rs(const uint64_t *__restrict__ a, size_t gstride, unsigned G, uint64_t *__restrict__ out, int Win, int k,
+                            int Wout, int shift, int kout, unsigned N, size_t npoly) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= npoly * N) return;
+  const size_t q = gid / N, i = gid % N;
+  const uint64_t *pa = a + q * Win * N + i;
+  uint64_t s[16];
+  {
+    uint64_t fill = 0;
+    unsigned carry = 0;
+    bool done = false;
+    for (int w = 0; w < Win; w++) {
+      uint64_t r;
+      if (done) r = fill;
+      else {
+        unsigned __int128 t = carry;
+        for (unsigned g = 0; g < G; g++) t += pa[(size_t)g * gstride + (size_t)w * N];
+        r = (uint64_t)t;
+        carry = (unsigned)(t >> 64);
+        const int kk = k - 64 * w;
+        if (kk <= 64) {
+          if (kk < 64) r = (uint64_t)(((int64_t)(r << (64 - kk))) >> (64 - kk));
+          fill = (uint64_t)((int64_t)r >> 63);
+          done = true;
+        }
+      }
+      s[w] = r;
+    }
+  }
+  const uint64_t sign = (uint64_t)((int64_t)s[Win - 1] >> 63);
+  auto word = [&](int w) -> uint64_t { return w < Win ? s[w] : sign; };
+  uint64_t roundup = 0;                          // round up iff (x mod 2^shift) > 2^(shift-1): ties toward -infinity (types.c:123)
+  if (shift > 0) {
+    const int hb = shift - 1, hw = hb / 64, hbit = hb % 64;
+    const uint64_t wv = word(hw);
+    if ((wv >> hbit) & 1) {
+      bool lower = (hbit > 0) && ((wv & ((1ULL << hbit) - 1)) != 0);
+      for (int w = 0; w < hw && !lower; w++) lower = word(w) != 0;
+      roundup = lower ? 1 : 0;
+    }
+  }
+  const int ws = shift / 64, bs = shift % 64;
+  uint64_t *po = out + q * Wout * N + i;
+  uint64_t carry = roundup, fill = 0;
+  bool done = false;
+  for (int w = 0; w < Wout; w++) {
+    uint64_t r;
+    if (done) r = fill;
+    else {
+      const uint64_t lo = word(w + ws), hi = word(w + ws + 1);
+      const uint64_t v = bs ? ((lo >> bs) | (hi << (64 - bs))) : lo;
+      const uint64_t t = v + carry;
+      carry = (t < carry);
+      r = t;
+      const int kk = kout - 64 * w;
+      if (kk <= 64) {
+        if (kk < 64) r = (uint64_t)(((int64_t)(r << (64 - kk))) >> (64 - kk));
+        fill = (uint64_t)((int64_t)r >> 63);
+        done = true;
+      }
+    }
+    po[(size_t)w * N] = r;
+  }
+}
+
+// The last four calls of ctr_hempc (src/hempc.c:261-266) in one pass: he_add, he_neg, he_moddown of a copy of u, he_add.
+// Every step is arithmetic mod 2^kout followed by centring, so  out = smod(u - a - b, 2^kout)  on the low words of u.
+__global__ void k_ct_combine(const uint64_t *__restrict__ u, int Wu, const uint64_t *__restrict__ a, const uint64_t *__restrict__ b,
+                             uint64_t *__restrict__ out, int Wout, int kout, unsigned N, size_t npoly) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= npoly * N) return;
+  const size_t q = gid / N, i = gid % N;
+  const uint64_t *pu = u + q * Wu * N + i, *pa = a + q * Wout * N + i, *pb = b + q * Wout * N + i;
+  uint64_t *po = out + q * Wout * N + i;
+  uint64_t br = 0, fill = 0;
+  bool done = false;
+  for (int w = 0; w < Wout; w++) {
+    uint64_t r;
+    if (done) r = fill;
+    else {
+      const unsigned __int128 sub = (unsigned __int128)pa[(size_t)w * N] + pb[(size_t)w * N] + br;     // below 2^65 + small
+      const uint64_t x = pu[(size_t)w * N], y = (uint64_t)sub;
+      r = x - y;
+      br = (uint64_t)(sub >> 64) + (x < y);
+      const int kk = kout - 64 * w;
+      if (kk <= 64) {
+        if (kk < 64) r = (uint64_t)(((int64_t)(r << (64 - kk))) >> (64 - kk));
+        fill = (uint64_t)((int64_t)r >> 63);
+        done = true;
+      }
+    }
+    po[(size_t)w * N] = r;
+  }
+}
+
 // he_addpt / he_subpt (he-add.c:80-123): c0 +- pt, c1 only re-centred; pt is one polynomial [WC][N] shared by the batch.
 __global__ void k_ct_addpt(const uint64_t *__restrict__ a, const uint64_t *__restrict__ pt, uint64_t *__restrict__ out, int W, int k,
                            int op, unsigned N, size_t npoly) {
