@@ -51,17 +51,50 @@ def load_peaks():
 # clocks sampler
 # ------------------------------------------------------------------------------------------------------
 class ClockSampler:
+    """SM clock and throttle reasons DURING the timed region.  NVML (the library nvidia-smi prints from) polled every few
+    milliseconds from a thread, so that even a 50 ms region (8 GPUs) gets samples; `nvidia-smi -lms` when pynvml is missing."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
     NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    MASKS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}   # nvml.h
 
     def __init__(self, index: int):
         self.index = index
         self.samples = []
         self.proc = None
         self.thread = None
+        self.nvml = None
+        self.stop_flag = False
+
+    def _start_nvml(self) -> bool:
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            smax = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            reasons_fn = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+            reasons_fn(h)
+        except Exception:
+            return False
+        self.nvml = pynvml
+
+        def run():
+            while not self.stop_flag:
+                try:
+                    sm = float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+                    mask = int(reasons_fn(h))
+                except Exception:
+                    break
+                f = [str(sm), str(smax)] + ["Active" if mask & self.MASKS[n] else "Not Active" for n in self.NAMES]
+                self.samples.append(", ".join(f))
+                time.sleep(0.004)
+        self.thread = threading.Thread(target=run, daemon=True)
+        self.thread.start()
+        return True
 
     def start(self):
+        if self._start_nvml():
+            return
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index), "-lms", "100"],
@@ -76,13 +109,17 @@ class ClockSampler:
         self.thread.start()
 
     def stop(self):
-        if not self.proc:
+        if self.nvml is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=2)
+        elif not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
+        else:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
         sm, smax, reasons = [], None, set()
         for s in self.samples:
             f = [x.strip() for x in s.split(",")]
@@ -97,7 +134,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "source": "nvml (the library behind nvidia-smi), 4 ms period" if self.nvml is not None else "nvidia-smi -lms 100"}
 
 
 # ------------------------------------------------------------------------------------------------------

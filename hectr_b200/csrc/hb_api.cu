@@ -1335,6 +1335,7 @@ extern "C" void hb_ctr_hempc_eval_host(hb_ctx *ctx, unsigned batch, unsigned l, 
   if (batch == 0) return;
   const double Delta = std::ldexp(1.0, (int)ctx->ht.logDelta);
   unsigned chunk = 512;
+  if (batch < 4 * chunk) chunk = (batch + 7) / 8 > 64 ? (batch + 7) / 8 : 64;     // small batches (a shard of 8 GPUs) still pipeline
   if (const char *e = getenv("HB_E2E_CHUNK")) { const long v = atol(e); if (v > 0) chunk = (unsigned)v; }
   if (chunk > batch) chunk = batch;
   const uint64_t *host_in[4] = {in_xhat, in_xr, in_uhat, in_ur};
