@@ -87,7 +87,7 @@ class ClockSampler:
                     break
                 f = [str(sm), str(smax)] + ["Active" if mask & self.MASKS[n] else "Not Active" for n in self.NAMES]
                 self.samples.append(", ".join(f))
-                time.sleep(0.004)
+                time.sleep(0.010)
         self.thread = threading.Thread(target=run, daemon=True)
         self.thread.start()
         return True
@@ -134,7 +134,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
-                "samples": len(sm), "source": "nvml (the library behind nvidia-smi), 4 ms period" if self.nvml is not None else "nvidia-smi -lms 100"}
+                "samples": len(sm), "source": "nvml (the library behind nvidia-smi), 10 ms period" if self.nvml is not None else "nvidia-smi -lms 100"}
 
 
 # ------------------------------------------------------------------------------------------------------
@@ -246,15 +246,37 @@ def run_ours(args):
     for nm in names:
         lib.hb_ct_upload(ctx, C.byref(dev[nm].h), host[nm].ctypes.data_as(C.c_void_p), l, Delta, 1.0)
     up = eng.ct(batch=per)
-    gather_in = torch.empty((per, 2 * Wout * n), dtype=torch.int64, device="cuda")
+    # result gather (the only collective, north_star): two buffer sets, asynchronous, so that the gather of step k overlaps
+    # the evaluation of step k+1; every gather is waited for before the timed region closes
+    equal = total % world == 0
+    nbuf = 2 if (world > 1 and equal) else 1
+    gather_in = [torch.empty((per, 2 * Wout * n), dtype=torch.int64, device="cuda") for _ in range(nbuf)]
+    gather_out = [torch.empty((total, 2 * Wout * n), dtype=torch.int64, device="cuda") for _ in range(nbuf)] if (world > 1 and equal) else []
+    works = [None] * nbuf
+    counter = [0]
+
+    def drain():
+        for i, w in enumerate(works):
+            if w is not None:
+                w.wait()          # the current stream waits for the collective; the host does not block
+                works[i] = None
 
     def step():
         eng.ctr_hempc_eval(Ka, Kb, dev["xhat"], dev["xr"], dev["uhat"], dev["ur"], keys, out=up)
-        if world > 1:      # the only collective: gather the result ciphertexts (north_star)
-            lib.hb_ct_export(ctx, C.byref(up.h), C.c_void_p(gather_in.data_ptr()))
-            gather_results(gather_in, total)
+        if world > 1:
+            b = counter[0] % nbuf
+            counter[0] += 1
+            if works[b] is not None:
+                works[b].wait()
+                works[b] = None
+            lib.hb_ct_export(ctx, C.byref(up.h), C.c_void_p(gather_in[b].data_ptr()))
+            if equal:
+                _, works[b] = gather_results(gather_in[b], total, out=gather_out[b], async_op=True)
+            else:
+                gather_results(gather_in[b], total)
 
     def barrier():
+        drain()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
@@ -272,6 +294,7 @@ def run_ours(args):
     lib.hb_timer_start(ctx)
     for _ in range(args.steps):
         step()
+    drain()                                   # the last gathers end inside the timed region
     ms = float(lib.hb_timer_stop_ms(ctx))
     barrier()
     launches = eng.launches() - launches0

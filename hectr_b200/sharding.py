@@ -23,11 +23,15 @@ def shard_sizes(total: int, world: int) -> list[int]:
     return [hi - lo for lo, hi in (shard_range(total, r, world) for r in range(world))]
 
 
-def gather_results(local, total: int, group=None):
+def gather_results(local, total: int, group=None, out=None, async_op: bool = False):
     """All-gather the per-rank result words (a tensor whose dim 0 is this rank's instances) into batch order.
 
     Equal shards use one ``all_gather_into_tensor`` (NCCL: a single NVLink/NVSwitch collective); ragged shards pad to
-    the largest shard first.  Returns a tensor with ``total`` instances on every rank."""
+    the largest shard first.  Returns a tensor with ``total`` instances on every rank.
+
+    ``out``: preallocated destination (equal shards only).  ``async_op=True`` (equal shards only) returns ``(out, work)``
+    without making the calling stream wait: the gather of step k then overlaps the evaluation of step k+1, and the caller
+    calls ``work.wait()`` before it reads ``out`` or reuses ``local``."""
     import torch
     import torch.distributed as dist
 
@@ -36,12 +40,15 @@ def gather_results(local, total: int, group=None):
     if local.shape[0] != sizes[dist.get_rank(group)]:
         raise ValueError(f"rank holds {local.shape[0]} instances, expected {sizes[dist.get_rank(group)]}")
     if world == 1:
-        return local
+        return (local, None) if async_op else local
     big = max(sizes)
     if min(sizes) == big:
-        out = torch.empty((total,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
-        dist.all_gather_into_tensor(out, local.contiguous(), group=group)
-        return out
+        if out is None:
+            out = torch.empty((total,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+        work = dist.all_gather_into_tensor(out, local.contiguous(), group=group, async_op=async_op)
+        return (out, work) if async_op else out
+    if async_op or out is not None:
+        raise ValueError("ragged shards: only the blocking gather into a fresh tensor is implemented")
     pad = torch.zeros((big,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
     pad[: local.shape[0]] = local
     out = torch.empty((world * big,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)

@@ -42,6 +42,23 @@ def _worker(rank, world, port, total, q):
         idx = torch.arange(lo, hi, dtype=torch.int64)
         local = (idx[:, None, None] * 1000003 + torch.arange(6, dtype=torch.int64).reshape(2, 3)[None]) ^ 0x5555
         out = gather_results(local, total)
+        if total % world == 0:
+            # the overlapped form the bench uses: preallocated destinations, two gathers in flight, waited for afterwards
+            outs = [torch.zeros_like(out) for _ in range(2)]
+            works = []
+            for b in range(2):
+                o, w = gather_results(local + b, total, out=outs[b], async_op=True)
+                assert o is outs[b]
+                works.append(w)
+            for w in works:
+                w.wait()
+            assert torch.equal(outs[0], out) and torch.equal(outs[1], out + 1)
+        else:
+            try:
+                gather_results(local, total, async_op=True)
+                raise AssertionError("ragged asynchronous gather must be refused")
+            except ValueError:
+                pass
         q.put((rank, out.numpy().copy()))
         dist.barrier()
     finally:
