@@ -115,6 +115,8 @@ PROTOTYPES = {
     "hb_he_gemv": (None, [ctx_p, ct_p, vp, ct_p, evk_p]),
     "hb_ctr_hempc_eval": (None, [ctx_p, ct_p, vp, vp, ct_p, ct_p, ct_p, ct_p, evk_p]),
     "hb_ctr_hempc_eval_host": (None, [ctx_p, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp, evk_p, vp]),
+    "hb_ctr_hempc_submit_host": (C.c_uint64, [ctx_p, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp, evk_p, vp]),
+    "hb_ctr_hempc_wait": (None, [ctx_p, C.c_uint64]),
     "hb_pk_upload": (None, [ctx_p, evk_p, vp, vp]),
     "hb_sk_upload": (None, [ctx_p, C.POINTER(HbSk), vp]),
     "hb_sk_free": (None, [ctx_p, C.POINTER(HbSk)]),

@@ -1,4 +1,5 @@
 // C ABI of the engine (include/hectr_b200.h): context, containers, launch orchestration.
+#include <algorithm>
 #include <cstdio>
 #include <cstdarg>
 #include <cstdlib>
@@ -44,6 +45,9 @@ using hbdev::Tables;
     if (e_ != cudaSuccess) hb_die("CUDA failure %s at %s:%d (%s)", cudaGetErrorString(e_), __FILE__, __LINE__, #expr); \
   } while (0)
 
+struct hb_ctx;
+static void use_device(const hb_ctx *ctx);      // every entry point that touches the GPU selects the context's device first
+
 struct GemvPlan {
   std::vector<double> A;     // the matrix the plan was built from
   unsigned l = 0, D = 0;
@@ -53,6 +57,10 @@ struct GemvPlan {
   bool use32 = false;
   unsigned D32 = 0;
   uint32_t *pthat32 = nullptr; // device [slots][D32][2][N]: multiplicand plane, quotient plane
+  // giant steps i (of n2) with at least one non-zero encoded diagonal.  A giant step whose n1 diagonals all encode to the zero
+  // polynomial (the hempc gain matrices are 8x3 / 8x2 blocks in a 16x16 frame: src/hempc.c:232-238) has the zero ciphertext
+  // as inner sum, and he_rot of the zero ciphertext is the zero ciphertext: skipping it changes no word of the result.
+  std::vector<unsigned> giant_nz;
 };
 
 struct hb_ctx {
@@ -87,10 +95,28 @@ struct hb_ctx {
   size_t wsD_bytes = 0;
   bool no_hoist = false;            // HB_GEMV_NOHOIST=1: one key-switch launch per baby rotation (A/B timing, tests)
   std::vector<GemvPlan> plans;
+  // bit length of the largest |coefficient| of each uploaded evaluation key, as an integer (k_lift_bits): a key made by
+  // he_genswk stays below P q_L / 2, which is what lets the summed giant steps (and any other exact-product shortcut) be used
+  std::map<const void *, unsigned> evk_bits;
+  uint64_t *keycheck_consts = nullptr;
+  hbkg::Consts keycheck;
+  bool no_sum = false;              // HB_GEMV_NOSUM=1: one tail per giant step (A/B timing, tests)
+  bool no_skip = false;             // HB_GEMV_NOSKIP=1: evaluate identically zero giant steps too
   std::vector<uint64_t> enc_host;   // [WC][N] scratch for hb_he_ecd / gemv plans
+  // streaming host interface (hb_ctr_hempc_submit_host / hb_ctr_hempc_wait): two persistent device buffer sets
+  hb_ct job_in[2][4], job_up[2];
+  unsigned job_cap = 0;             // instances each set holds
+  uint64_t job_next = 0;            // ticket of the next submission
+  bool job_busy[2] = {false, false};
+  cudaEvent_t job_done[2] = {nullptr, nullptr};
 };
 
+static void use_device(const hb_ctx *ctx) {
+  if (ctx) CUDA_OK(cudaSetDevice(ctx->device));   // a no-op in the driver when the device is already current
+}
+
 static void need_ct(const hb_ct *ct, const char *what);
+static void pipeline_streams(hb_ctx *ctx);
 static size_t ct_words(const hb_ctx *ctx, const hb_ct *ct);
 static void check_level(const hb_ctx *ctx, unsigned l);
 
@@ -109,6 +135,7 @@ static void launch(hb_ctx *ctx, const char *name, void (*kernel)(KArgs...), unsi
                    int cluster, Args... args) {
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof cfg);
+  if (grid == 0) return;
   cfg.gridDim = dim3(grid, 1, 1);
   cfg.blockDim = dim3(threads, 1, 1);
   cfg.dynamicSmemBytes = smem;
@@ -134,10 +161,13 @@ static void launch(hb_ctx *ctx, const char *name, void (*kernel)(KArgs...), unsi
   ctx->launches++;
 }
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute: the cache is keyed by (current device, kernel)
 template <class K>
 static void want_smem(K kernel, size_t bytes) {
-  static std::map<void *, size_t> done;
-  void *key = (void *)kernel;
+  static std::map<std::pair<int, void *>, size_t> done;
+  int dev = 0;
+  CUDA_OK(cudaGetDevice(&dev));
+  const std::pair<int, void *> key(dev, (void *)kernel);
   auto it = done.find(key);
   if (it != done.end() && it->second >= bytes) return;
   CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
@@ -170,16 +200,16 @@ struct Launch32 {
     if (canon) launch(c, "k32_poly_ntt", hb32::k32_poly_ntt<LOGN, true>, (unsigned)(npoly * D), G::THREADS, G::SMEM_BYTES, 1, src, stride, W, out, c->dt32, D);
     else launch(c, "k32_poly_ntt", hb32::k32_poly_ntt<LOGN, false>, (unsigned)(npoly * D), G::THREADS, G::SMEM_BYTES, 1, src, stride, W, out, c->dt32, D);
   }
-  static void mulacc_intt(hb_ctx *c, const uint32_t *hat, size_t jstride, const uint32_t *pthat, size_t gstride, unsigned n1, unsigned ngroups,
-                          uint32_t *chat, unsigned D, unsigned batch) {
+  static void mulacc_intt(hb_ctx *c, const uint32_t *hat, size_t jstride, const uint32_t *pthat, size_t gstride, const hbdev::GroupMap &GM,
+                          unsigned n1, unsigned ngroups, uint32_t *chat, unsigned D, unsigned batch) {
     if (gstride == (size_t)n1 * D && (n1 == 2 || n1 == 4) && G::N >= 1024) {      // rotated transforms read once, in registers
       const unsigned grid = (unsigned)((size_t)batch * 2 * D);
-      if (n1 == 4) launch(c, "k32_mulacc_intt_all", hb32::k32_mulacc_intt_all<LOGN, 4>, grid, G::THREADS, G::SMEM_BYTES, 1, hat, jstride, pthat, gstride, ngroups, batch * 2, chat, c->dt32, D);
-      else launch(c, "k32_mulacc_intt_all", hb32::k32_mulacc_intt_all<LOGN, 2>, grid, G::THREADS, G::SMEM_BYTES, 1, hat, jstride, pthat, gstride, ngroups, batch * 2, chat, c->dt32, D);
+      if (n1 == 4) launch(c, "k32_mulacc_intt_all", hb32::k32_mulacc_intt_all<LOGN, 4>, grid, G::THREADS, G::SMEM_BYTES, 1, hat, jstride, pthat, gstride, GM, ngroups, batch * 2, chat, c->dt32, D);
+      else launch(c, "k32_mulacc_intt_all", hb32::k32_mulacc_intt_all<LOGN, 2>, grid, G::THREADS, G::SMEM_BYTES, 1, hat, jstride, pthat, gstride, GM, ngroups, batch * 2, chat, c->dt32, D);
       return;
     }
     launch(c, "k32_mulacc_intt", hb32::k32_mulacc_intt<LOGN>, (unsigned)((size_t)ngroups * batch * 2 * D), G::THREADS, G::SMEM_BYTES, 1, hat, jstride,
-           pthat, gstride, n1, batch * 2, chat, c->dt32, D);
+           pthat, gstride, GM, n1, batch * 2, chat, c->dt32, D);
   }
 };
 static void do32_poly_ntt(hb_ctx *c, const uint64_t *src, size_t stride, int W, uint32_t *out, unsigned D, size_t npoly, bool canon) {
@@ -187,9 +217,9 @@ static void do32_poly_ntt(hb_ctx *c, const uint64_t *src, size_t stride, int W, 
   switch (c->ht.logn) { HB_LOGN32_CASES(X) default: hb_die("logn=%u has no 30-bit path", c->ht.logn); }
 #undef X
 }
-static void do32_mulacc_intt(hb_ctx *c, const uint32_t *hat, size_t jstride, const uint32_t *pthat, size_t gstride, unsigned n1, unsigned ngroups,
-                             uint32_t *chat, unsigned D, unsigned batch) {
-#define X(L) case L: Launch32<L>::mulacc_intt(c, hat, jstride, pthat, gstride, n1, ngroups, chat, D, batch); break;
+static void do32_mulacc_intt(hb_ctx *c, const uint32_t *hat, size_t jstride, const uint32_t *pthat, size_t gstride, const hbdev::GroupMap &GM,
+                             unsigned n1, unsigned ngroups, uint32_t *chat, unsigned D, unsigned batch) {
+#define X(L) case L: Launch32<L>::mulacc_intt(c, hat, jstride, pthat, gstride, GM, n1, ngroups, chat, D, batch); break;
   switch (c->ht.logn) { HB_LOGN32_CASES(X) default: hb_die("logn=%u has no 30-bit path", c->ht.logn); }
 #undef X
 }
@@ -216,10 +246,20 @@ struct Launch {
     launch(c, "k_poly_ntt", hbdev::k_poly_ntt<LOGN>, (unsigned)(npoly * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, src, stride, W, out, c->dt, D);
   }
   static void ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hbdev::KsGroups &S,
-                      unsigned key_limbs, uint64_t *chat, unsigned D, unsigned batch) {
+                      unsigned key_limbs, uint64_t *chat, unsigned D, unsigned batch, unsigned d0, unsigned Dn) {
     want_smem(hbdev::k_ks_limb<LOGN>, 2 * G::SMEM_BYTES);
-    launch(c, "k_ks_limb", hbdev::k_ks_limb<LOGN>, (unsigned)((size_t)batch * D * G::C), G::THREADS, 2 * G::SMEM_BYTES, G::C, src, bstride, W,
-           S, key_limbs, chat, c->dt, D);
+    launch(c, "k_ks_limb", hbdev::k_ks_limb<LOGN>, (unsigned)((size_t)batch * Dn * G::C), G::THREADS, 2 * G::SMEM_BYTES, G::C, src, bstride, W,
+           S, key_limbs, chat, c->dt, D, d0, Dn);
+  }
+  static void ks_limb_sum(hb_ctx *c, const uint64_t *src, size_t bstride, size_t gstride, int W, const hbdev::KsGroups &S, unsigned ng,
+                          unsigned key_limbs, uint64_t *chatX, unsigned D, unsigned batch, unsigned d0, unsigned Dn) {
+    if constexpr (G::C == 1) {
+      want_smem(hbdev::k_ks_limb_sum<LOGN>, 3 * G::SMEM_BYTES);
+      launch(c, "k_ks_limb_sum", hbdev::k_ks_limb_sum<LOGN>, (unsigned)((size_t)batch * Dn), G::THREADS, 3 * G::SMEM_BYTES, 1, src, bstride, gstride,
+             W, S, ng, key_limbs, chatX, c->dt, D, d0, Dn);
+    } else {
+      hb_die("summed giant steps are built for N <= 2^13 only");
+    }
   }
   static void ks_baby(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hbdev::BabySet &S, uint64_t *chat, size_t jstride,
                       unsigned D, unsigned batch) {
@@ -233,11 +273,11 @@ struct Launch {
     launch(c, "k_mulpt_limb", hbdev::k_mulpt_limb<LOGN>, (unsigned)(npoly * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, ct, poly_stride, W, pthat,
            chat, c->dt, D);
   }
-  static void mulacc_intt(hb_ctx *c, const uint64_t *hat, size_t jstride, const ulonglong2 *pthat, size_t pthat_gstride, unsigned n1,
-                          unsigned ngroups, uint64_t *chat, unsigned D, unsigned batch) {
+  static void mulacc_intt(hb_ctx *c, const uint64_t *hat, size_t jstride, const ulonglong2 *pthat, size_t pthat_gstride,
+                          const hbdev::GroupMap &GM, unsigned n1, unsigned ngroups, uint64_t *chat, unsigned D, unsigned batch) {
     want_smem(hbdev::k_mulacc_intt<LOGN>, G::SMEM_BYTES);
     launch(c, "k_mulacc_intt", hbdev::k_mulacc_intt<LOGN>, (unsigned)((size_t)ngroups * batch * 2 * D * G::C), G::THREADS, G::SMEM_BYTES, G::C,
-           hat, jstride, pthat, pthat_gstride, n1, batch * 2, chat, c->dt, D);
+           hat, jstride, pthat, pthat_gstride, GM, n1, batch * 2, chat, c->dt, D);
   }
   static void tensor_intt(hb_ctx *c, const uint64_t *hatA, const uint64_t *hatB, uint64_t *dhat, unsigned D, unsigned batch) {
     want_smem(hbdev::k_tensor_intt<LOGN>, G::SMEM_BYTES);
@@ -262,9 +302,17 @@ static void do_poly_ntt(hb_ctx *c, const uint64_t *src, size_t stride, int W, ui
 }
 // key_limbs: limbs per half of the key array (dimevk for evaluation keys, dim for an uploaded public key)
 // batch = instances in the launch (all groups); S.gbatch instances per group
+// limbs [d0, d0 + Dn) of a D-limb key switch (Dn = 0: all of them), written compactly as chat[b][h][Dn][N]
 static void do_ks_limb_g(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hbdev::KsGroups &S, unsigned key_limbs,
-                         uint64_t *chat, unsigned D, unsigned batch) {
-#define X(L) case L: Launch<L>::ks_limb(c, src, bstride, W, S, key_limbs, chat, D, batch); break;
+                         uint64_t *chat, unsigned D, unsigned batch, unsigned d0 = 0, unsigned Dn = 0) {
+  if (!Dn) Dn = D;
+#define X(L) case L: Launch<L>::ks_limb(c, src, bstride, W, S, key_limbs, chat, D, batch, d0, Dn); break;
+  switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
+#undef X
+}
+static void do_ks_limb_sum(hb_ctx *c, const uint64_t *src, size_t bstride, size_t gstride, int W, const hbdev::KsGroups &S, unsigned ng,
+                           unsigned key_limbs, uint64_t *chatX, unsigned D, unsigned batch, unsigned d0, unsigned Dn) {
+#define X(L) case L: Launch<L>::ks_limb_sum(c, src, bstride, gstride, W, S, ng, key_limbs, chatX, D, batch, d0, Dn); break;
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
 }
@@ -288,9 +336,9 @@ static void do_mulpt_limb(hb_ctx *c, const uint64_t *ct, size_t poly_stride, int
 #undef X
 }
 // ngroups giant steps in one launch: group i uses the diagonals pthat + i * pthat_gstride and writes chat[i][batch][2][D][N]
-static void do_mulacc_intt(hb_ctx *c, const uint64_t *hat, size_t jstride, const ulonglong2 *pthat, size_t pthat_gstride, unsigned n1,
-                           unsigned ngroups, uint64_t *chat, unsigned D, unsigned batch) {
-#define X(L) case L: Launch<L>::mulacc_intt(c, hat, jstride, pthat, pthat_gstride, n1, ngroups, chat, D, batch); break;
+static void do_mulacc_intt(hb_ctx *c, const uint64_t *hat, size_t jstride, const ulonglong2 *pthat, size_t pthat_gstride,
+                           const hbdev::GroupMap &GM, unsigned n1, unsigned ngroups, uint64_t *chat, unsigned D, unsigned batch) {
+#define X(L) case L: Launch<L>::mulacc_intt(c, hat, jstride, pthat, pthat_gstride, GM, n1, ngroups, chat, D, batch); break;
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
 }
@@ -366,6 +414,56 @@ static void ks_finish_wp(hb_ctx *c, unsigned grid, unsigned threads, const uint6
   }
 }
 
+// the fixed-point tails (k_ks_finish_fast, k_ks_finish_sum) cover D <= 8 limbs, dim <= 4, q_l <= 2^128
+static bool ks_fast_ok(const hb_ctx *c, unsigned D, unsigned wk) {
+  const hb::HostTables &h = c->ht;
+  return D <= 8 && h.dim <= 4 && h.dim <= D && wk <= 2 && h.WP <= 4 && !c->exact_tail;
+}
+static void ks_fast_consts(const hb_ctx *c, unsigned D, hbdev::KsFast &F) {
+  const hb::HostTables &h = c->ht;
+  memset(&F, 0, sizeof F);
+  F.D = D; F.dim = h.dim;
+  for (unsigned d = 0; d < D; d++) {
+    F.p[d] = h.primes[d].p; F.mu[d] = h.primes[d].mu;
+    for (unsigned w = 0; w < 2 && w < h.WC; w++) F.phat[d][w] = h.crt_phat[((size_t)D * h.dimub + d) * h.WC + w];
+  }
+  for (unsigned w = 0; w < 2 && w < h.WC; w++) { F.PD[w] = h.crt_P[(size_t)D * h.WC + w]; F.Pinv[w] = h.ks_Pinv[w]; }
+  for (unsigned e = 0; e < h.dim; e++) {
+    F.kinv[e] = h.ks_z[((size_t)D * h.dim + e) * 2]; F.kinvq[e] = h.ks_z[((size_t)D * h.dim + e) * 2 + 1];
+    for (unsigned w = 0; w < 2 && w < h.WP; w++) F.kphat[e][w] = h.ks_phat[(size_t)e * h.WP + w];
+  }
+  for (unsigned w = 0; w < 2 && w < h.WP; w++) F.kP[w] = h.ks_P[w];
+  // t = (x - R) P^-1 mod 2^128 is linear in every term of x and R: fold P^-1 into the constants once
+  typedef unsigned __int128 u128;
+  const u128 pinv = ((u128)F.Pinv[1] << 64) | F.Pinv[0];
+  auto fold = [&](uint64_t (&w)[2]) { const u128 v = ((((u128)w[1]) << 64) | w[0]) * pinv; w[0] = (uint64_t)v; w[1] = (uint64_t)(v >> 64); };
+  for (unsigned d = 0; d < D; d++) fold(F.phat[d]);
+  for (unsigned e = 0; e < h.dim; e++) fold(F.kphat[e]);
+  fold(F.PD);
+  fold(F.kP);
+}
+
+// tail of ng summed giant-step key switches + he_rs (k_ks_finish_sum); false when this (D, dim) pair is not instantiated
+static bool do_ks_finish_sum(hb_ctx *c, const uint64_t *chatP, size_t chatP_gstride, const uint64_t *chatX, unsigned D, const uint64_t *add0,
+                             size_t add_gstride, size_t add_bstride, int Wadd, const hbdev::SumGroups &SG, uint64_t *out, int Wout, int k,
+                             int shift, int kout, unsigned batch, bool probe) {
+  const hb::HostTables &h = c->ht;
+  const unsigned threads = 128;
+  const size_t total = (size_t)batch * 2 * h.N;
+  const unsigned grid = (unsigned)((total + threads - 1) / threads);
+  hbdev::KsFast F;
+  if (!probe) ks_fast_consts(c, D, F);
+#define KSS(DD, MM)                                                                                                              \
+  if (D == DD && h.dim == MM) {                                                                                                  \
+    if (!probe) launch(c, "k_ks_finish_sum", hbdev::k_ks_finish_sum<4, DD, MM>, grid, threads, 0, 1, chatP, chatP_gstride, chatX, F, add0, \
+                       add_gstride, add_bstride, Wadd, SG, out, Wout, k, shift, kout, c->dt, batch);                             \
+    return true;                                                                                                                 \
+  }
+  KSS(5, 2) KSS(6, 2) KSS(5, 3) KSS(6, 3) KSS(7, 3) KSS(8, 3)
+#undef KSS
+  return false;
+}
+
 static void do_ks_finish_g(hb_ctx *c, const uint64_t *chat, unsigned D, const uint64_t *add0, const uint64_t *add1,
                            size_t add_bstride, int Wadd, const hbdev::TailGroups &TG, uint64_t *out, int Wout, int k, unsigned batch) {
   const unsigned threads = 128;
@@ -373,30 +471,9 @@ static void do_ks_finish_g(hb_ctx *c, const uint64_t *chat, unsigned D, const ui
   const unsigned grid = (unsigned)((total + threads - 1) / threads);
   const unsigned wk = (k + 63) / 64;
   const hb::HostTables &h = c->ht;
-  if (D <= 8 && h.dim <= 4 && h.dim <= D && wk <= 2 && h.WP <= 4 && !c->exact_tail) {
+  if (ks_fast_ok(c, D, wk)) {
     hbdev::KsFast F;
-    memset(&F, 0, sizeof F);
-    F.D = D; F.dim = h.dim;
-    for (unsigned d = 0; d < D; d++) {
-      F.p[d] = h.primes[d].p; F.mu[d] = h.primes[d].mu;
-      for (unsigned w = 0; w < 2 && w < h.WC; w++) F.phat[d][w] = h.crt_phat[((size_t)D * h.dimub + d) * h.WC + w];
-    }
-    for (unsigned w = 0; w < 2 && w < h.WC; w++) { F.PD[w] = h.crt_P[(size_t)D * h.WC + w]; F.Pinv[w] = h.ks_Pinv[w]; }
-    for (unsigned e = 0; e < h.dim; e++) {
-      F.kinv[e] = h.ks_z[((size_t)D * h.dim + e) * 2]; F.kinvq[e] = h.ks_z[((size_t)D * h.dim + e) * 2 + 1];
-      for (unsigned w = 0; w < 2 && w < h.WP; w++) F.kphat[e][w] = h.ks_phat[(size_t)e * h.WP + w];
-    }
-    for (unsigned w = 0; w < 2 && w < h.WP; w++) F.kP[w] = h.ks_P[w];
-    {
-      // t = (x - R) P^-1 mod 2^128 is linear in every term of x and R: fold P^-1 into the constants once
-      typedef unsigned __int128 u128;
-      const u128 pinv = ((u128)F.Pinv[1] << 64) | F.Pinv[0];
-      auto fold = [&](uint64_t (&w)[2]) { const u128 v = ((((u128)w[1]) << 64) | w[0]) * pinv; w[0] = (uint64_t)v; w[1] = (uint64_t)(v >> 64); };
-      for (unsigned d = 0; d < D; d++) fold(F.phat[d]);
-      for (unsigned e = 0; e < h.dim; e++) fold(F.kphat[e]);
-      fold(F.PD);
-      fold(F.kP);
-    }
+    ks_fast_consts(c, D, F);
     bool done = true;
 #define KSF(DD, MM)                                                                                                             \
     if (D == DD && h.dim == MM) {                                                                                               \
@@ -492,6 +569,10 @@ extern "C" hb_ctx *hb_ctx_create(unsigned logn, unsigned logq, unsigned slots, u
     ctx->exact_tail = e && *e && *e != '0';
     e = getenv("HB_GEMV_NOHOIST");
     ctx->no_hoist = e && *e && *e != '0';
+    e = getenv("HB_GEMV_NOSUM");
+    ctx->no_sum = e && *e && *e != '0';
+    e = getenv("HB_GEMV_NOSKIP");
+    ctx->no_skip = e && *e && *e != '0';
   }
   ctx->ring = hb_ring_create(logn);
   ctx->enc_host.assign((size_t)h.WC * h.N, 0);
@@ -521,7 +602,7 @@ extern "C" hb_ctx *hb_ctx_create(unsigned logn, unsigned logq, unsigned slots, u
   return ctx;
 }
 
-extern "C" void hb_ctx_destroy(hb_ctx *ctx) {
+extern "C" void hb_ctx_destroy(hb_ctx *ctx) { use_device(ctx);
   if (!ctx) return;
   CUDA_OK(cudaSetDevice(ctx->device));
   cudaStreamSynchronize(ctx->stream);
@@ -536,12 +617,15 @@ extern "C" void hb_ctx_destroy(hb_ctx *ctx) {
   cudaFree(ctx->wsB);
   cudaFree(ctx->wsC);
   cudaFree(ctx->wsD);
+  cudaFree(ctx->keycheck_consts);
   for (auto &kv : ctx->perms) cudaFree(kv.second);
   if (ctx->up_stream) {
     cudaStreamDestroy(ctx->up_stream);
     cudaStreamDestroy(ctx->down_stream);
     for (int s2 = 0; s2 < 2; s2++) { cudaEventDestroy(ctx->ev_up[s2]); cudaEventDestroy(ctx->ev_comp[s2]); cudaEventDestroy(ctx->ev_down[s2]); }
   }
+  for (int q = 0; q < 2; q++)
+    if (ctx->job_done[q]) cudaEventDestroy(ctx->job_done[q]);
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->own_stream);
@@ -570,10 +654,10 @@ extern "C" void hb_ctx_twiddles(const hb_ctx *ctx, unsigned d, int inverse, uint
 extern "C" unsigned hb_dim_keyswitch(const hb_ctx *ctx, unsigned l) { check_level(ctx, l); return hb::dim_keyswitch(ctx->ht, l); }
 extern "C" unsigned hb_dim_mul(const hb_ctx *ctx, unsigned l) { check_level(ctx, l); return hb::dim_mul(ctx->ht, l); }
 extern "C" unsigned hb_dim_mulpt(const hb_ctx *ctx, unsigned l, double nu) { check_level(ctx, l); return hb::dim_mulpt(ctx->ht, l, nu); }
-extern "C" void hb_ctx_set_stream(hb_ctx *ctx, void *s) { ctx->stream = s ? (cudaStream_t)s : ctx->own_stream; }
-extern "C" void hb_sync(hb_ctx *ctx) { CUDA_OK(cudaStreamSynchronize(ctx->stream)); }
-extern "C" void hb_timer_start(hb_ctx *ctx) { CUDA_OK(cudaEventRecord(ctx->ev0, ctx->stream)); }
-extern "C" float hb_timer_stop_ms(hb_ctx *ctx) {
+extern "C" void hb_ctx_set_stream(hb_ctx *ctx, void *s) { use_device(ctx); ctx->stream = s ? (cudaStream_t)s : ctx->own_stream; }
+extern "C" void hb_sync(hb_ctx *ctx) { use_device(ctx); CUDA_OK(cudaStreamSynchronize(ctx->stream)); }
+extern "C" void hb_timer_start(hb_ctx *ctx) { use_device(ctx); CUDA_OK(cudaEventRecord(ctx->ev0, ctx->stream)); }
+extern "C" float hb_timer_stop_ms(hb_ctx *ctx) { use_device(ctx);
   CUDA_OK(cudaEventRecord(ctx->ev1, ctx->stream));
   CUDA_OK(cudaEventSynchronize(ctx->ev1));
   float ms = 0;
@@ -581,14 +665,14 @@ extern "C" float hb_timer_stop_ms(hb_ctx *ctx) {
   return ms;
 }
 extern "C" uint64_t hb_launch_count(const hb_ctx *ctx) { return ctx->launches; }
-extern "C" void hb_prof_enable(hb_ctx *ctx, int on) { ctx->prof = on != 0; }
-extern "C" void hb_prof_reset(hb_ctx *ctx) {
+extern "C" void hb_prof_enable(hb_ctx *ctx, int on) { use_device(ctx); ctx->prof = on != 0; }
+extern "C" void hb_prof_reset(hb_ctx *ctx) { use_device(ctx);
   CUDA_OK(cudaStreamSynchronize(ctx->stream));
   for (auto &kv : ctx->prof_recs)
     for (auto &pr : kv.second.pending) { ctx->prof_free.push_back(pr.first); ctx->prof_free.push_back(pr.second); }
   ctx->prof_recs.clear();
 }
-extern "C" size_t hb_prof_report(hb_ctx *ctx, char *buf, size_t cap) {
+extern "C" size_t hb_prof_report(hb_ctx *ctx, char *buf, size_t cap) { use_device(ctx);
   CUDA_OK(cudaStreamSynchronize(ctx->stream));
   std::string out = "{";
   bool first = true;
@@ -610,11 +694,11 @@ extern "C" size_t hb_prof_report(hb_ctx *ctx, char *buf, size_t cap) {
   if (buf && cap) { size_t n = out.size() < cap - 1 ? out.size() : cap - 1; memcpy(buf, out.data(), n); buf[n] = 0; }
   return out.size();
 }
-extern "C" void hb_ct_export(hb_ctx *ctx, const hb_ct *ct, void *dst_device) {
+extern "C" void hb_ct_export(hb_ctx *ctx, const hb_ct *ct, void *dst_device) { use_device(ctx);
   need_ct(ct, "hb_ct_export");
   CUDA_OK(cudaMemcpyAsync(dst_device, ct->words, ct_words(ctx, ct) * 8, cudaMemcpyDeviceToDevice, ctx->stream));
 }
-extern "C" void hb_ct_import(hb_ctx *ctx, hb_ct *ct, const void *src_device, unsigned l, double nu, double B) {
+extern "C" void hb_ct_import(hb_ctx *ctx, hb_ct *ct, const void *src_device, unsigned l, double nu, double B) { use_device(ctx);
   need_ct(ct, "hb_ct_import"); check_level(ctx, l);
   ct->l = l; ct->nu = nu; ct->B = B;
   CUDA_OK(cudaMemcpyAsync(ct->words, src_device, ct_words(ctx, ct) * 8, cudaMemcpyDeviceToDevice, ctx->stream));
@@ -676,40 +760,43 @@ extern "C" void hb_tables_decode(const hb_tables *t, const uint64_t *words, unsi
 // ---------------------------------------------------------------------------------------------------------
 // raw memory
 // ---------------------------------------------------------------------------------------------------------
-extern "C" void *hb_dev_alloc(hb_ctx *ctx, size_t bytes) {
+extern "C" void *hb_dev_alloc(hb_ctx *ctx, size_t bytes) { use_device(ctx);
   CUDA_OK(cudaSetDevice(ctx->device));
   void *p = nullptr;
   CUDA_OK(cudaMalloc(&p, bytes ? bytes : 8));
   return p;
 }
-extern "C" void hb_dev_free(hb_ctx *ctx, void *p) {
+extern "C" void hb_dev_free(hb_ctx *ctx, void *p) { use_device(ctx);
   if (!p) return;
   CUDA_OK(cudaStreamSynchronize(ctx->stream));
   CUDA_OK(cudaFree(p));
 }
-extern "C" void *hb_host_alloc(hb_ctx *ctx, size_t bytes) {
+extern "C" void *hb_host_alloc(hb_ctx *ctx, size_t bytes) { use_device(ctx);
   (void)ctx;
   void *p = nullptr;
   CUDA_OK(cudaMallocHost(&p, bytes ? bytes : 8));
   return p;
 }
-extern "C" void hb_host_free(hb_ctx *ctx, void *p) { (void)ctx; if (p) CUDA_OK(cudaFreeHost(p)); }
-extern "C" void hb_h2d(hb_ctx *ctx, void *dst, const void *src, size_t bytes) {
+extern "C" void hb_host_free(hb_ctx *ctx, void *p) { use_device(ctx); (void)ctx; if (p) CUDA_OK(cudaFreeHost(p)); }
+extern "C" void hb_h2d(hb_ctx *ctx, void *dst, const void *src, size_t bytes) { use_device(ctx);
   CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
 }
-extern "C" void hb_d2h(hb_ctx *ctx, void *dst, const void *src, size_t bytes) {
+extern "C" void hb_d2h(hb_ctx *ctx, void *dst, const void *src, size_t bytes) { use_device(ctx);
   CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
 }
-extern "C" void hb_dev_fill(hb_ctx *ctx, void *dst, int byte, size_t bytes) {
+extern "C" void hb_dev_fill(hb_ctx *ctx, void *dst, int byte, size_t bytes) { use_device(ctx);
   CUDA_OK(cudaMemsetAsync(dst, byte, bytes, ctx->stream));
 }
 
+// the smallest pooled buffer of sufficient capacity (at most twice the request, so a small handle never pins a large
+// buffer); a ragged last chunk of the host pipeline reuses the full-size buffers instead of a synchronising cudaMalloc
 static uint64_t *pool_get(hb_ctx *ctx, size_t bytes) {
-  auto it = ctx->pool.find(bytes);
+  auto it = ctx->pool.lower_bound(bytes);
   uint64_t *p;
-  if (it != ctx->pool.end()) { p = it->second; ctx->pool.erase(it); }
+  size_t cap = bytes;
+  if (it != ctx->pool.end() && it->first <= 2 * bytes) { p = it->second; cap = it->first; ctx->pool.erase(it); }
   else { void *q = nullptr; CUDA_OK(cudaMalloc(&q, bytes)); p = (uint64_t *)q; }
-  ctx->live[p] = bytes;
+  ctx->live[p] = cap;
   return p;
 }
 static void pool_put(hb_ctx *ctx, uint64_t *p) {
@@ -736,7 +823,7 @@ static uint64_t *ws_get(hb_ctx *ctx, uint64_t *&ws, size_t &cur, size_t bytes) {
 static size_t ct_capacity(const hb_ctx *ctx, unsigned batch) { return (size_t)batch * 2 * ctx->ht.WC * ctx->ht.N * 8; }
 static size_t ct_words(const hb_ctx *ctx, const hb_ct *ct) { return (size_t)ct->batch * 2 * hb::words_of_level(ctx->ht, ct->l) * ctx->ht.N; }
 
-extern "C" void hb_ct_alloc(hb_ctx *ctx, hb_ct *ct, unsigned batch) {
+extern "C" void hb_ct_alloc(hb_ctx *ctx, hb_ct *ct, unsigned batch) { use_device(ctx);
   if (batch == 0) hb_die("a ciphertext handle must hold at least one instance");
   CUDA_OK(cudaSetDevice(ctx->device));
   ct->l = ctx->ht.L; ct->nu = 0; ct->B = 0; ct->batch = batch;
@@ -748,43 +835,82 @@ static void ct_alloc_tmp(hb_ctx *ctx, hb_ct *ct, unsigned batch) {
   ct->l = ctx->ht.L; ct->nu = 0; ct->B = 0; ct->batch = batch;
   ct->words = pool_get(ctx, ct_capacity(ctx, batch));
 }
-extern "C" void hb_ct_free(hb_ctx *ctx, hb_ct *ct) {
+extern "C" void hb_ct_free(hb_ctx *ctx, hb_ct *ct) { use_device(ctx);
   pool_put(ctx, ct->words);
   ct->words = nullptr; ct->batch = 0;
 }
 static void need_ct(const hb_ct *ct, const char *what) {
   if (!ct || !ct->words) hb_die("%s: ciphertext handle is not allocated", what);
 }
-extern "C" void hb_ct_copy(hb_ctx *ctx, hb_ct *dst, const hb_ct *src) {
+extern "C" void hb_ct_copy(hb_ctx *ctx, hb_ct *dst, const hb_ct *src) { use_device(ctx);
   need_ct(dst, "hb_ct_copy"); need_ct(src, "hb_ct_copy");
   if (dst->batch != src->batch) hb_die("hb_ct_copy: batch mismatch (%u vs %u)", dst->batch, src->batch);
   dst->l = src->l; dst->nu = src->nu; dst->B = src->B;
   if (dst->words != src->words)
     CUDA_OK(cudaMemcpyAsync(dst->words, src->words, ct_words(ctx, src) * 8, cudaMemcpyDeviceToDevice, ctx->stream));
 }
-extern "C" void hb_ct_upload(hb_ctx *ctx, hb_ct *ct, const uint64_t *host, unsigned l, double nu, double B) {
+extern "C" void hb_ct_upload(hb_ctx *ctx, hb_ct *ct, const uint64_t *host, unsigned l, double nu, double B) { use_device(ctx);
   need_ct(ct, "hb_ct_upload"); check_level(ctx, l);
   ct->l = l; ct->nu = nu; ct->B = B;
   CUDA_OK(cudaMemcpyAsync(ct->words, host, ct_words(ctx, ct) * 8, cudaMemcpyHostToDevice, ctx->stream));
 }
-extern "C" void hb_ct_download(hb_ctx *ctx, const hb_ct *ct, uint64_t *host) {
+extern "C" void hb_ct_download(hb_ctx *ctx, const hb_ct *ct, uint64_t *host) { use_device(ctx);
   need_ct(ct, "hb_ct_download");
   CUDA_OK(cudaMemcpyAsync(host, ct->words, ct_words(ctx, ct) * 8, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_OK(cudaStreamSynchronize(ctx->stream));
 }
-extern "C" void hb_pt_alloc(hb_ctx *ctx, hb_pt *pt) {
+extern "C" void hb_pt_alloc(hb_ctx *ctx, hb_pt *pt) { use_device(ctx);
   pt->nu = 0;
   pt->words = (uint64_t *)hb_dev_alloc(ctx, (size_t)ctx->ht.WC * ctx->ht.N * 8);
   CUDA_OK(cudaMemsetAsync(pt->words, 0, (size_t)ctx->ht.WC * ctx->ht.N * 8, ctx->stream));
 }
-extern "C" void hb_pt_free(hb_ctx *ctx, hb_pt *pt) { hb_dev_free(ctx, pt->words); pt->words = nullptr; }
-extern "C" void hb_pt_upload(hb_ctx *ctx, hb_pt *pt, const uint64_t *host, double nu) {
+extern "C" void hb_pt_free(hb_ctx *ctx, hb_pt *pt) { use_device(ctx); hb_dev_free(ctx, pt->words); pt->words = nullptr; }
+extern "C" void hb_pt_upload(hb_ctx *ctx, hb_pt *pt, const uint64_t *host, double nu) { use_device(ctx);
   if (!pt->words) hb_die("hb_pt_upload: plaintext handle is not allocated");
   pt->nu = nu;
   CUDA_OK(cudaMemcpyAsync(pt->words, host, (size_t)ctx->ht.WC * ctx->ht.N * 8, cudaMemcpyHostToDevice, ctx->stream));
   CUDA_OK(cudaStreamSynchronize(ctx->stream));
 }
-extern "C" void hb_evk_upload(hb_ctx *ctx, hb_evk *evk, const uint64_t *p0, const uint64_t *p1) {
+// largest |coefficient| (bit length) of a key given as canonical-or-[0,p] transform limbs raw[2][dimevk][N] on the device
+static unsigned key_lift_bits(hb_ctx *ctx, const uint64_t *raw) {
+  const hb::HostTables &h = ctx->ht;
+  const unsigned D = h.dimevk;
+  const size_t N = h.N;
+  if (!ctx->keycheck_consts) {
+    const hb::BigU &PD = h.Pfull[D];
+    const unsigned WX = (PD.bits() + 8 + 63) / 64 + 1;
+    if (WX > (unsigned)hbkg::MAXW) return ~0u;                       // wider than the generic kernels: treated as unbounded
+    std::vector<uint64_t> hc;
+    auto put = [&](const std::vector<uint64_t> &v) { const size_t off = hc.size(); hc.insert(hc.end(), v.begin(), v.end()); return off; };
+    std::vector<uint64_t> primes(D), inv(D), phat((size_t)D * WX);
+    for (unsigned d = 0; d < D; d++) {
+      primes[d] = h.primes[d].p;
+      const hb::BigU ph = PD.divmod_u64(primes[d], nullptr);
+      inv[d] = hb::powmod(ph.mod_u64(primes[d]), primes[d] - 2, primes[d]);
+      const std::vector<uint64_t> lo = ph.low(WX);
+      std::copy(lo.begin(), lo.end(), phat.begin() + (size_t)d * WX);
+    }
+    const size_t o_pr = put(primes), o_inv = put(inv), o_ph = put(phat), o_PD = put(PD.low(WX)), o_PDh = put(PD.shr1().low(WX));
+    uint64_t *dc = (uint64_t *)hb_dev_alloc(ctx, hc.size() * 8 + 8);
+    CUDA_OK(cudaMemcpyAsync(dc, hc.data(), hc.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    ctx->keycheck_consts = dc;
+    ctx->keycheck = hbkg::Consts{dc + o_pr, dc + o_inv, dc + o_ph, dc + o_PD, dc + o_PDh, nullptr, nullptr, nullptr, nullptr, D, WX, 0, (unsigned)N};
+  }
+  const size_t limbs = (size_t)2 * D * N;
+  uint64_t *coef = (uint64_t *)hb_dev_alloc(ctx, limbs * 8 + 8);
+  unsigned *dmax = (unsigned *)(coef + limbs);
+  CUDA_OK(cudaMemsetAsync(dmax, 0, 8, ctx->stream));
+  do_ntt_inv(ctx, raw, coef, (size_t)2 * D, 0, D);
+  launch(ctx, "k_lift_bits", hbkg::k_lift_bits, (unsigned)((2 * N + 127) / 128), 128, 0, 1, (const uint64_t *)coef, ctx->keycheck, 2u, dmax);
+  unsigned bits = 0;
+  CUDA_OK(cudaMemcpyAsync(&bits, dmax, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  CUDA_OK(cudaFree(coef));
+  return bits;
+}
+
+extern "C" void hb_evk_upload(hb_ctx *ctx, hb_evk *evk, const uint64_t *p0, const uint64_t *p1) { use_device(ctx);
   // stored as Shoup pairs (w, floor(w 2^64 / p_d)): the key is a fixed multiplicand of every key switch
   const size_t half = (size_t)ctx->ht.dimevk * ctx->ht.N;
   if (ctx->ht.dimevk > ctx->ht.dimub) hb_die("hb_evk_upload: keys of %u limbs but the prime chain has %u", ctx->ht.dimevk, ctx->ht.dimub);
@@ -793,9 +919,14 @@ extern "C" void hb_evk_upload(hb_ctx *ctx, hb_evk *evk, const uint64_t *p0, cons
   CUDA_OK(cudaMemcpyAsync(raw, p0, half * 8, cudaMemcpyHostToDevice, ctx->stream));
   CUDA_OK(cudaMemcpyAsync(raw + half, p1, half * 8, cudaMemcpyHostToDevice, ctx->stream));
   do_shoup_prep(ctx, raw, (ulonglong2 *)evk->p, ctx->ht.dimevk, (size_t)2 * ctx->ht.dimevk, 1, 0);   // key * N^-1
+  ctx->evk_bits[evk->p] = key_lift_bits(ctx, raw);
   hb_dev_free(ctx, raw);   // synchronises
 }
-extern "C" void hb_evk_free(hb_ctx *ctx, hb_evk *evk) { hb_dev_free(ctx, evk->p); evk->p = nullptr; }
+extern "C" void hb_evk_free(hb_ctx *ctx, hb_evk *evk) { use_device(ctx);
+  ctx->evk_bits.erase(evk->p);
+  hb_dev_free(ctx, evk->p);
+  evk->p = nullptr;
+}
 
 // ---------------------------------------------------------------------------------------------------------
 // encode / decode
@@ -806,7 +937,7 @@ extern "C" void hb_encode(const hb_ctx *ctx, const double *m, double Delta, uint
 extern "C" void hb_decode(const hb_ctx *ctx, const uint64_t *words, unsigned W, double Delta, double *m) {
   hb_ring_decode(ctx->ring, ctx->ht.slots, words, W, Delta, m);
 }
-extern "C" void hb_he_ecd(hb_ctx *ctx, hb_pt *pt, const double *m) {
+extern "C" void hb_he_ecd(hb_ctx *ctx, hb_pt *pt, const double *m) { use_device(ctx);
   if (!pt->words) hb_die("hb_he_ecd: plaintext handle is not allocated");
   // he_ecd writes 2*slots coefficients and keeps the rest (he-encode.c:58-63): read-modify-write
   const size_t bytes = (size_t)ctx->ht.WC * ctx->ht.N * 8;
@@ -817,7 +948,7 @@ extern "C" void hb_he_ecd(hb_ctx *ctx, hb_pt *pt, const double *m) {
   hb_pt_upload(ctx, pt, ctx->enc_host.data(), Delta);
 }
 
-extern "C" void hb_he_const_pt(hb_ctx *ctx, hb_pt *pt, double re, double im) {
+extern "C" void hb_he_const_pt(hb_ctx *ctx, hb_pt *pt, double re, double im) { use_device(ctx);
   if (!pt->words) hb_die("hb_he_const_pt: plaintext handle is not allocated");
   // he_const_pt writes coefficients 0 and N/2 and keeps the rest (he-encode.c:119-125): read-modify-write like hb_he_ecd
   const size_t bytes = (size_t)ctx->ht.WC * ctx->ht.N * 8;
@@ -846,8 +977,8 @@ static void addsub(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b, int o
   const size_t npoly = (size_t)ct->batch * 2, total = npoly * ctx->ht.N;
   launch(ctx, "k_ct_addsub", hbdev::k_ct_addsub, (unsigned)((total + 255) / 256), 256, 0, 1, a->words, b->words, ct->words, W, k, op, ctx->ht.N, npoly);
 }
-extern "C" void hb_he_add(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b) { addsub(ctx, ct, a, b, 0, "hb_he_add"); }
-extern "C" void hb_he_sub(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b) { addsub(ctx, ct, a, b, 1, "hb_he_sub"); }
+extern "C" void hb_he_add(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b) { use_device(ctx); addsub(ctx, ct, a, b, 0, "hb_he_add"); }
+extern "C" void hb_he_sub(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b) { use_device(ctx); addsub(ctx, ct, a, b, 1, "hb_he_sub"); }
 static void addsub_pt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt, int op, const char *what) {
   same_shape(dst, src, what);
   if (!pt || !pt->words) hb_die("%s: plaintext handle is not allocated", what);
@@ -858,9 +989,9 @@ static void addsub_pt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt
   const size_t npoly = (size_t)dst->batch * 2, total = npoly * ctx->ht.N;
   launch(ctx, "k_ct_addpt", hbdev::k_ct_addpt, (unsigned)((total + 255) / 256), 256, 0, 1, src->words, pt->words, dst->words, W, k, op, ctx->ht.N, npoly);
 }
-extern "C" void hb_he_addpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt) { addsub_pt(ctx, dst, src, pt, 0, "hb_he_addpt"); }
-extern "C" void hb_he_subpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt) { addsub_pt(ctx, dst, src, pt, 1, "hb_he_subpt"); }
-extern "C" void hb_he_neg(hb_ctx *ctx, hb_ct *ct) {
+extern "C" void hb_he_addpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt) { use_device(ctx); addsub_pt(ctx, dst, src, pt, 0, "hb_he_addpt"); }
+extern "C" void hb_he_subpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt) { use_device(ctx); addsub_pt(ctx, dst, src, pt, 1, "hb_he_subpt"); }
+extern "C" void hb_he_neg(hb_ctx *ctx, hb_ct *ct) { use_device(ctx);
   need_ct(ct, "hb_he_neg");
   const int W = hb::words_of_level(ctx->ht, ct->l), k = ctx->ht.logq_l[ct->l];
   const size_t npoly = (size_t)ct->batch * 2, total = npoly * ctx->ht.N;
@@ -880,7 +1011,7 @@ static void rescale_like(hb_ctx *ctx, hb_ct *ct, int shift, const char *what) {
   pool_put(ctx, ct->words);
   ct->words = out;
 }
-extern "C" void hb_he_rs(hb_ctx *ctx, hb_ct *ct) {
+extern "C" void hb_he_rs(hb_ctx *ctx, hb_ct *ct) { use_device(ctx);
   need_ct(ct, "hb_he_rs");
   const double Delta = std::ldexp(1.0, (int)ctx->ht.logDelta);
   const double n = ctx->ht.N, Brs = std::sqrt(n / 3.) * (3 + 8 * std::sqrt(64.0));   // precomp.c:417
@@ -888,7 +1019,7 @@ extern "C" void hb_he_rs(hb_ctx *ctx, hb_ct *ct) {
   ct->B = ct->B / Delta + Brs;
   rescale_like(ctx, ct, (int)ctx->ht.logDelta, "hb_he_rs");
 }
-extern "C" void hb_he_moddown(hb_ctx *ctx, hb_ct *ct) { rescale_like(ctx, ct, 0, "hb_he_moddown"); }
+extern "C" void hb_he_moddown(hb_ctx *ctx, hb_ct *ct) { use_device(ctx); rescale_like(ctx, ct, 0, "hb_he_moddown"); }
 
 // pthat[D][N] -> chat -> dst   (shared by hb_he_mulpt and the gemv plan)
 static void mulpt_with_hat(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const ulonglong2 *pthat, unsigned D, double ptnu) {
@@ -902,7 +1033,7 @@ static void mulpt_with_hat(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const ulon
   do_recon_smod(ctx, chat, D, dst->words, W, k, (size_t)src->batch * 2, true);
 }
 
-extern "C" void hb_he_mulpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt) {
+extern "C" void hb_he_mulpt(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt) { use_device(ctx);
   same_shape(dst, src, "hb_he_mulpt");
   if (!pt || !pt->words) hb_die("hb_he_mulpt: plaintext handle is not allocated");
   const unsigned D = hb::dim_mulpt(ctx->ht, src->l, pt->nu);
@@ -949,15 +1080,15 @@ static void keyswitch_inplace(hb_ctx *ctx, hb_ct *ct, unsigned ginv, const hb_ev
   ct->words = out;
 }
 
-extern "C" void hb_he_rot(hb_ctx *ctx, hb_ct *ct, int rot, const hb_evk *rk) {
+extern "C" void hb_he_rot(hb_ctx *ctx, hb_ct *ct, int rot, const hb_evk *rk) { use_device(ctx);
   if (rot < 0 || (unsigned)rot >= ctx->ht.slots) hb_die("hb_he_rot: rotation %d outside [0,%u)", rot, ctx->ht.slots);
   keyswitch_inplace(ctx, ct, pow5_inv_mod_2n(ctx, (unsigned)rot), &rk[rot], "hb_he_rot");
 }
-extern "C" void hb_he_conj(hb_ctx *ctx, hb_ct *ct, const hb_evk *ck) {
+extern "C" void hb_he_conj(hb_ctx *ctx, hb_ct *ct, const hb_evk *ck) { use_device(ctx);
   keyswitch_inplace(ctx, ct, 2 * ctx->ht.N - 1, ck, "hb_he_conj");
 }
 
-extern "C" void hb_he_mul(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b, const hb_evk *rlk) {
+extern "C" void hb_he_mul(hb_ctx *ctx, hb_ct *ct, const hb_ct *a, const hb_ct *b, const hb_evk *rlk) { use_device(ctx);
   same_shape(a, b, "hb_he_mul"); same_shape(ct, a, "hb_he_mul");
   if (a->l != b->l) hb_die("hb_he_mul: operands are at different levels (%u vs %u)", a->l, b->l);   // assert, he-mult.c:90
   if (!rlk || !rlk->p) hb_die("hb_he_mul: relinearisation key is not loaded");
@@ -1042,6 +1173,12 @@ static const GemvPlan &gemv_plan(hb_ctx *ctx, const double *A, unsigned l) {
       }
       hb_ring_encode(ctx->ring, S, rd.data(), Delta, host.data() + (size_t)idx * ptw, h.WC);
     }
+  }
+  for (unsigned i = 0; i < n2; i++) {
+    bool any = false;
+    const uint64_t *w = host.data() + (size_t)i * n1 * ptw;
+    for (size_t t = 0; t < (size_t)n1 * ptw && !any; t++) any = w[t] != 0;
+    if (any) plan.giant_nz.push_back(i);
   }
   {
     // May the n1 products of a giant step be summed before reconstruction?  Every |ct coefficient| <= q_l/2, so a
@@ -1156,7 +1293,11 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
   if (Dk > h.dimevk || Dk > h.dimub) hb_die("hb_he_gemv: needs %u limbs but keys hold %u and the prime chain %u", Dk, h.dimevk, h.dimub);
   const size_t cstride = (size_t)batch * 2 * Dk * N;                // one batch of key-switch limbs
   const bool grouped = !ctx->no_hoist && N <= 65536 && n1 <= HB_MAX_GROUPS && n2 <= HB_MAX_GROUPS;
-  uint64_t *hat = ws_get(ctx, ctx->wsC, ctx->wsC_bytes, (size_t)n1 * jstride * 8);
+  // 30-bit path: D32 limbs of 4 bytes per coefficient reuse the 59-bit workspaces; D32 may exceed 2 D (D = 1: two primes
+  // below 2^30 do not cover a 60-bit P_1), so both buffers take the larger of the two layouts
+  const size_t jstride32 = plan.use32 ? (size_t)batch * 2 * plan.D32 * N : 0;
+  const size_t hat_bytes = std::max((size_t)n1 * jstride * 8, (size_t)n1 * jstride32 * 4);
+  uint64_t *hat = ws_get(ctx, ctx->wsC, ctx->wsC_bytes, hat_bytes);
   if (!grouped) {
     // one launch per rotation and per giant step (A/B timing, very large rings)
     hb_ct inner, outer, rot;
@@ -1171,7 +1312,9 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
     for (unsigned i = 0; i < n2; i++) {
       const unsigned shift = i * n1;
       uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, jstride * 8);
-      do_mulacc_intt(ctx, hat, jstride, plan.pthat + (size_t)shift * D * N, 0, n1, 1, chat, D, batch);
+      hbdev::GroupMap G0;
+      memset(&G0, 0, sizeof G0);
+      do_mulacc_intt(ctx, hat, jstride, plan.pthat + (size_t)shift * D * N, 0, G0, n1, 1, chat, D, batch);
       do_recon_smod(ctx, chat, D, inner.words, W, k, (size_t)batch * 2, true);
       inner.l = l;
       for (unsigned j = 0; j < n1; j++) {          // metadata exactly as he_mulpt / he_add update it
@@ -1192,7 +1335,7 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
   }
   // ---- grouped schedule: every phase of the matvec is ONE launch over (rotations or giant steps) x batch ----
   const unsigned ng = n1 > n2 ? n1 : n2;
-  uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, (size_t)ng * cstride * 8);
+  uint64_t *chat = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, std::max((size_t)ng * cstride * 8, (size_t)n2 * jstride32 * 4));
   uint64_t *cts = ws_get(ctx, ctx->wsD, ctx->wsD_bytes, (size_t)(ng + n2) * batch * bstride * 8);   // rots / inner sums, then switched sums
   // 1. baby rotations: one decomposition + forward transform of ct.c1 per limb serves up to four key switches
   hbdev::TailGroups TB;
@@ -1213,43 +1356,53 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
   }
   //    tails of all n1 rotations: c0 = rdiv(.) + sigma_j(ct.c0), c1 = rdiv(.)   (he-automorphism.c:68-76)
   do_ks_finish_g(ctx, chat, Dk, ct->words, nullptr, bstride, W, TB, cts, W, k, n1 * batch);
-  uint64_t *inner = cts;                                           // [n2][batch][2][W][N]
+  // giant steps actually evaluated: all of them, or only those with a non-zero diagonal (GemvPlan::giant_nz)
+  hbdev::GroupMap GM;
+  memset(&GM, 0, sizeof GM);
+  unsigned ngs = 0;
+  if (!ctx->no_skip && !plan.giant_nz.empty())
+    for (unsigned i : plan.giant_nz) GM.idx[ngs++] = i;
+  else
+    for (unsigned i = 0; i < n2; i++) GM.idx[ngs++] = i;
+  uint64_t *inner = cts;                                           // [ngs][batch][2][W][N]
   if (plan.use32) {
     // 2-3 on the internal 30-bit basis (twice the butterfly throughput per modulus bit; same integers, hb_tables32.hpp)
     const unsigned D32 = plan.D32;
-    const size_t jstride32 = (size_t)batch * 2 * D32 * N;
-    uint32_t *hat32 = (uint32_t *)hat, *mchat32 = (uint32_t *)chat;       // 4 D32 <= 8 D bytes per coefficient: the buffers fit
+    uint32_t *hat32 = (uint32_t *)hat, *mchat32 = (uint32_t *)chat;       // sized above for either layout
     do32_poly_ntt(ctx, cts, polyw, W, hat32, D32, (size_t)n1 * batch * 2, false);
-    do32_mulacc_intt(ctx, hat32, jstride32, plan.pthat32, (size_t)n1 * D32, n1, n2, mchat32, D32, batch);
-    do32_recon_smod(ctx, mchat32, D32, inner, W, k, (size_t)n2 * batch * 2);
+    do32_mulacc_intt(ctx, hat32, jstride32, plan.pthat32, (size_t)n1 * D32, GM, n1, ngs, mchat32, D32, batch);
+    do32_recon_smod(ctx, mchat32, D32, inner, W, k, (size_t)ngs * batch * 2);
   } else {
     // 2. transform the rotated ciphertexts once
     do_poly_ntt(ctx, cts, polyw, W, hat, D, (size_t)n1 * batch * 2);
     // 3. all giant steps: inner_i = sum_j rot_j * diag_{i n1 + j}, summed in the transform domain
-    uint64_t *mchat = chat;                                          // [n2][batch][2][D][N], D <= Dk
-    do_mulacc_intt(ctx, hat, jstride, plan.pthat, (size_t)n1 * D * N, n1, n2, mchat, D, batch);
-    do_recon_smod(ctx, mchat, D, inner, W, k, (size_t)n2 * batch * 2, true);
+    uint64_t *mchat = chat;                                          // [ngs][batch][2][D][N], D <= Dk
+    do_mulacc_intt(ctx, hat, jstride, plan.pthat, (size_t)n1 * D * N, GM, n1, ngs, mchat, D, batch);
+    do_recon_smod(ctx, mchat, D, inner, W, k, (size_t)ngs * batch * 2, true);
   }
   // 4. key-switch every inner sum with its own rotation i n1
   hbdev::KsGroups SG;
   hbdev::TailGroups TG;
+  hbdev::SumGroups SS;
   memset(&SG, 0, sizeof SG);
   memset(&TG, 0, sizeof TG);
+  memset(&SS, 0, sizeof SS);
   SG.gbatch = TG.gbatch = batch;
-  for (unsigned i = 0; i < n2; i++) {
-    const unsigned shift = i * n1;
+  SS.ng = ngs;
+  unsigned keybits = 0;
+  for (unsigned s = 0; s < ngs; s++) {
+    const unsigned shift = GM.idx[s] * n1;
     if (shift >= h.slots) hb_die("hb_he_gemv: rotation %u outside [0,%u)", shift, h.slots);
     if (!rk[shift].p) hb_die("hb_he_gemv: rotation key %u is not loaded", shift);
-    TG.ginv[i] = SG.ginv[i] = pow5_inv_mod_2n(ctx, shift);
-    SG.g[i] = inv_odd_mod_2n(ctx, SG.ginv[i]);
-    SG.evk[i] = (const ulonglong2 *)rk[shift].p;
+    SS.ginv[s] = TG.ginv[s] = SG.ginv[s] = pow5_inv_mod_2n(ctx, shift);
+    SG.g[s] = inv_odd_mod_2n(ctx, SG.ginv[s]);
+    SG.evk[s] = (const ulonglong2 *)rk[shift].p;
+    auto it = ctx->evk_bits.find(rk[shift].p);
+    keybits = std::max(keybits, it == ctx->evk_bits.end() ? ~0u : it->second);
   }
-  do_ks_limb_g(ctx, inner + polyw, bstride, W, SG, h.dimevk, chat, Dk, n2 * batch);
-  uint64_t *switched = cts + (size_t)ng * batch * bstride;          // [n2][batch][2][W][N]
-  do_ks_finish_g(ctx, chat, Dk, inner, nullptr, bstride, W, TG, switched, W, k, n2 * batch);
-  // 5. outer = sum_i, then he_rs: one pass (the centred sum never leaves the registers)
+  // metadata: the reference's own sequence of updates over ALL n1 x n2 steps (he_mulpt, he_add, he_rot, he_add, he_rs)
   dst->l = l;
-  {                                                                 // metadata: the reference's own sequence of updates
+  {
     double inu = 0, iB = 0, onu = 0, oB = 0;
     for (unsigned i = 0; i < n2; i++) {
       for (unsigned j = 0; j < n1; j++) {
@@ -1263,26 +1416,54 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
     dst->nu = onu; dst->B = oB;
   }
   if (l == 0) hb_die("hb_he_rs: ciphertext is already at level 0");
+  const double nn = h.N, Brs = std::sqrt(nn / 3.) * (3 + 8 * std::sqrt(64.0));   // precomp.c:417, as hb_he_rs
+  const int Wout = hb::words_of_level(h, l - 1), kout = h.logq_l[l - 1];
+  // 4'. summed giant steps (k_ks_limb_sum / k_ks_finish_sum): the giant-step key switches, their he_add chain and he_rs share one
+  //     reconstruction.  Needs every giant key to be a real switching key (|coefficient| < 2^keybits from hb_evk_upload), so that
+  //     X = sum_i x_i provably stays inside (-P_D/4, P_D/4):  log2 ngs + log2 N + (k - 1) + keybits < nbits(P_D) - 2.
+  {
+    unsigned lg = 0;
+    while ((1u << lg) < ngs) lg++;
+    const bool fits = keybits != ~0u && (uint64_t)lg + h.logn + (unsigned)(k - 1) + keybits + 2 < h.Pfull[Dk].bits();
+    const unsigned wk = (unsigned)(k + 63) / 64;
+    if (!ctx->no_sum && fits && h.logn <= 13 && ngs <= 8 && h.dim < Dk && ks_fast_ok(ctx, Dk, wk) && W <= 2 && Wout <= 2 &&
+        do_ks_finish_sum(ctx, nullptr, 0, nullptr, Dk, nullptr, 0, 0, 0, SS, nullptr, 0, 0, 0, 0, 0, true)) {
+      const unsigned dim = h.dim, Dx = Dk - dim;
+      const size_t pstride = (size_t)batch * 2 * dim * N;          // limbs of the primes of P, per giant step
+      uint64_t *chatP = chat, *chatX = chat + (size_t)ngs * pstride;   // fits: ngs (dim + Dx) <= ng Dk
+      if ((size_t)ngs * pstride + (size_t)batch * 2 * Dx * N > (size_t)ng * cstride) hb_die("internal: key-switch workspace too small");
+      do_ks_limb_g(ctx, inner + polyw, bstride, W, SG, h.dimevk, chatP, Dk, ngs * batch, 0, dim);
+      do_ks_limb_sum(ctx, inner + polyw, bstride, (size_t)batch * bstride, W, SG, ngs, h.dimevk, chatX, Dk, batch, dim, Dx);
+      dst->nu /= Delta;
+      dst->B = dst->B / Delta + Brs;
+      dst->l = l - 1;
+      do_ks_finish_sum(ctx, chatP, pstride, chatX, Dk, inner, (size_t)batch * bstride, bstride, W, SS, dst->words, Wout, k, (int)h.logDelta, kout,
+                       batch, false);
+      return;
+    }
+  }
+  do_ks_limb_g(ctx, inner + polyw, bstride, W, SG, h.dimevk, chat, Dk, ngs * batch);
+  uint64_t *switched = cts + (size_t)ng * batch * bstride;          // [ngs][batch][2][W][N]
+  do_ks_finish_g(ctx, chat, Dk, inner, nullptr, bstride, W, TG, switched, W, k, ngs * batch);
+  // 5. outer = sum_i, then he_rs: one pass (the centred sum never leaves the registers)
   if (W > 16) {                                                    // wider than the fused kernel's registers: two passes
     const size_t npoly = (size_t)batch * 2, total = npoly * N;
-    launch(ctx, "k_ct_sum", hbdev::k_ct_sum, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint64_t *)switched, (size_t)batch * bstride, n2,
+    launch(ctx, "k_ct_sum", hbdev::k_ct_sum, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint64_t *)switched, (size_t)batch * bstride, ngs,
            dst->words, W, k, (unsigned)N, npoly);
     hb_he_rs(ctx, dst);
     return;
   }
   {
-    const double n = h.N, Brs = std::sqrt(n / 3.) * (3 + 8 * std::sqrt(64.0));   // precomp.c:417, as hb_he_rs
     dst->nu /= Delta;
     dst->B = dst->B / Delta + Brs;
     dst->l = l - 1;
-    const int Wout = hb::words_of_level(h, l - 1), kout = h.logq_l[l - 1];
     const size_t npoly = (size_t)batch * 2, total = npoly * N;
-    launch(ctx, "k_ct_sum_rs", hbdev::k_ct_sum_rs, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint64_t *)switched, (size_t)batch * bstride, n2,
+    launch(ctx, "k_ct_sum_rs", hbdev::k_ct_sum_rs, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint64_t *)switched, (size_t)batch * bstride, ngs,
            dst->words, W, k, Wout, (int)h.logDelta, kout, (unsigned)N, npoly);
   }
 }
 
-extern "C" void hb_he_gemv(hb_ctx *ctx, hb_ct *dst, const double *A, const hb_ct *ct, const hb_evk *rk) {
+extern "C" void hb_he_gemv(hb_ctx *ctx, hb_ct *dst, const double *A, const hb_ct *ct, const hb_evk *rk) { use_device(ctx);
   same_shape(dst, ct, "hb_he_gemv");
   const unsigned S = ctx->ht.slots;
   const GemvPlan &plan = gemv_plan(ctx, A, ct->l);
@@ -1294,13 +1475,13 @@ extern "C" void hb_he_gemv(hb_ctx *ctx, hb_ct *dst, const double *A, const hb_ct
 }
 
 extern "C" void hb_ctr_hempc_eval(hb_ctx *ctx, hb_ct *up, const double *Ka, const double *Kb, const hb_ct *xhat,
-                                  const hb_ct *xr, const hb_ct *uhat, const hb_ct *ur, const hb_evk *rk) {
+                                  const hb_ct *xr, const hb_ct *uhat, const hb_ct *ur, const hb_evk *rk) { use_device(ctx);
   same_shape(xhat, xr, "hb_ctr_hempc_eval"); same_shape(uhat, ur, "hb_ctr_hempc_eval");
   same_shape(xhat, uhat, "hb_ctr_hempc_eval"); same_shape(up, xhat, "hb_ctr_hempc_eval");
   const unsigned batch = xhat->batch;
-  hb_ct xdiff, udiff, KaX, KbU, du, ucopy;
+  hb_ct xdiff, udiff, KaX, KbU;
   ct_alloc_tmp(ctx, &xdiff, batch); ct_alloc_tmp(ctx, &udiff, batch); ct_alloc_tmp(ctx, &KaX, batch);
-  ct_alloc_tmp(ctx, &KbU, batch); ct_alloc_tmp(ctx, &du, batch); ct_alloc_tmp(ctx, &ucopy, batch);
+  ct_alloc_tmp(ctx, &KbU, batch);
   hb_he_sub(ctx, &xdiff, xhat, xr);              // hempc.c:253
   hb_he_sub(ctx, &udiff, uhat, ur);              // hempc.c:255
   hb_he_gemv(ctx, &KaX, Ka, &xdiff, rk);         // hempc.c:257
@@ -1321,7 +1502,7 @@ extern "C" void hb_ctr_hempc_eval(hb_ctx *ctx, hb_ct *up, const double *Ka, cons
            (const uint64_t *)KaX.words, (const uint64_t *)KbU.words, up->words, Wout, kout, h.N, npoly);
   }
   hb_ct_free(ctx, &xdiff); hb_ct_free(ctx, &udiff); hb_ct_free(ctx, &KaX);
-  hb_ct_free(ctx, &KbU); hb_ct_free(ctx, &du); hb_ct_free(ctx, &ucopy);
+  hb_ct_free(ctx, &KbU);
 }
 
 // End to end from host buffers.  The batch is cut into chunks that flow through three streams -- upload (copy stream),
@@ -1329,7 +1510,7 @@ extern "C" void hb_ctr_hempc_eval(hb_ctx *ctx, hb_ct *up, const double *Ka, cons
 // transfers of chunk c+1 and c-1 overlap the evaluation of chunk c.  HB_E2E_CHUNK sets the chunk size (instances).
 extern "C" void hb_ctr_hempc_eval_host(hb_ctx *ctx, unsigned batch, unsigned l, const double *Ka, const double *Kb,
                                        const uint64_t *in_xhat, const uint64_t *in_xr, const uint64_t *in_uhat,
-                                       const uint64_t *in_ur, const hb_evk *rk, uint64_t *out_up) {
+                                       const uint64_t *in_ur, const hb_evk *rk, uint64_t *out_up) { use_device(ctx);
   check_level(ctx, l);
   if (l == 0) hb_die("hb_ctr_hempc_eval_host: inputs must be above level 0");
   if (batch == 0) return;
@@ -1341,15 +1522,7 @@ extern "C" void hb_ctr_hempc_eval_host(hb_ctx *ctx, unsigned batch, unsigned l, 
   const uint64_t *host_in[4] = {in_xhat, in_xr, in_uhat, in_ur};
   const size_t in_words = (size_t)2 * hb::words_of_level(ctx->ht, l) * ctx->ht.N;         // per instance
   const size_t out_words = (size_t)2 * hb::words_of_level(ctx->ht, l - 1) * ctx->ht.N;
-  if (!ctx->up_stream) {
-    CUDA_OK(cudaStreamCreateWithFlags(&ctx->up_stream, cudaStreamNonBlocking));
-    CUDA_OK(cudaStreamCreateWithFlags(&ctx->down_stream, cudaStreamNonBlocking));
-    for (int s = 0; s < 2; s++) {
-      CUDA_OK(cudaEventCreateWithFlags(&ctx->ev_up[s], cudaEventDisableTiming));
-      CUDA_OK(cudaEventCreateWithFlags(&ctx->ev_comp[s], cudaEventDisableTiming));
-      CUDA_OK(cudaEventCreateWithFlags(&ctx->ev_down[s], cudaEventDisableTiming));
-    }
-  }
+  pipeline_streams(ctx);
   const unsigned nsets = batch > chunk ? 2 : 1;
   hb_ct in[2][4], up[2];
   for (unsigned s = 0; s < nsets; s++) {
@@ -1394,6 +1567,78 @@ extern "C" void hb_ctr_hempc_eval_host(hb_ctx *ctx, unsigned batch, unsigned l, 
   }
 }
 
+static void pipeline_streams(hb_ctx *ctx) {
+  if (ctx->up_stream) return;
+  CUDA_OK(cudaStreamCreateWithFlags(&ctx->up_stream, cudaStreamNonBlocking));
+  CUDA_OK(cudaStreamCreateWithFlags(&ctx->down_stream, cudaStreamNonBlocking));
+  for (int s = 0; s < 2; s++) {
+    CUDA_OK(cudaEventCreateWithFlags(&ctx->ev_up[s], cudaEventDisableTiming));
+    CUDA_OK(cudaEventCreateWithFlags(&ctx->ev_comp[s], cudaEventDisableTiming));
+    CUDA_OK(cudaEventCreateWithFlags(&ctx->ev_down[s], cudaEventDisableTiming));
+  }
+}
+
+// Streaming form of hb_ctr_hempc_eval_host for a server that evaluates batch after batch: enqueue the upload of this batch's
+// four inputs (copy stream), its evaluation (the context's stream) and the download of its result (second copy stream), and
+// return a ticket.  Two submissions may be in flight -- two persistent sets of device buffers --, so the transfers of batch
+// k+1 and k-1 overlap the evaluation of batch k while every launch keeps the full batch size.  A third submission first
+// waits for the first one.  hb_ctr_hempc_wait(ticket) returns once out_up of that submission is complete.
+extern "C" uint64_t hb_ctr_hempc_submit_host(hb_ctx *ctx, unsigned batch, unsigned l, const double *Ka, const double *Kb,
+                                             const uint64_t *in_xhat, const uint64_t *in_xr, const uint64_t *in_uhat,
+                                             const uint64_t *in_ur, const hb_evk *rk, uint64_t *out_up) { use_device(ctx);
+  check_level(ctx, l);
+  if (l == 0) hb_die("hb_ctr_hempc_submit_host: inputs must be above level 0");
+  if (batch == 0) hb_die("hb_ctr_hempc_submit_host: empty batch");
+  pipeline_streams(ctx);
+  const uint64_t ticket = ctx->job_next++;
+  const unsigned s = (unsigned)(ticket & 1);
+  if (!ctx->job_done[0])
+    for (int q = 0; q < 2; q++) CUDA_OK(cudaEventCreateWithFlags(&ctx->job_done[q], cudaEventDisableTiming));
+  if (ctx->job_busy[s]) { CUDA_OK(cudaEventSynchronize(ctx->job_done[s])); ctx->job_busy[s] = false; }
+  if (batch > ctx->job_cap) {                       // (re)size both sets; nothing may be in flight
+    for (int q = 0; q < 2; q++)
+      if (ctx->job_busy[q]) { CUDA_OK(cudaEventSynchronize(ctx->job_done[q])); ctx->job_busy[q] = false; }
+    CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    for (int t = 0; t < 2; t++) {
+      if (ctx->job_cap) {
+        for (int q = 0; q < 4; q++) { ctx->job_in[t][q].batch = ctx->job_cap; hb_ct_free(ctx, &ctx->job_in[t][q]); }
+        ctx->job_up[t].batch = ctx->job_cap;
+        hb_ct_free(ctx, &ctx->job_up[t]);
+      }
+      for (int q = 0; q < 4; q++) ct_alloc_tmp(ctx, &ctx->job_in[t][q], batch);
+      ct_alloc_tmp(ctx, &ctx->job_up[t], batch);
+    }
+    ctx->job_cap = batch;
+  }
+  const double Delta = std::ldexp(1.0, (int)ctx->ht.logDelta);
+  const uint64_t *host_in[4] = {in_xhat, in_xr, in_uhat, in_ur};
+  const size_t in_words = (size_t)2 * hb::words_of_level(ctx->ht, l) * ctx->ht.N;
+  const size_t out_words = (size_t)2 * hb::words_of_level(ctx->ht, l - 1) * ctx->ht.N;
+  // set s was last read by the evaluation of ticket - 2 and its result left job_up[s] before job_done[s] fired (waited above)
+  for (int q = 0; q < 4; q++) {
+    hb_ct &c = ctx->job_in[s][q];
+    c.batch = batch; c.l = l; c.nu = Delta; c.B = 1.0;
+    CUDA_OK(cudaMemcpyAsync(c.words, host_in[q], (size_t)batch * in_words * 8, cudaMemcpyHostToDevice, ctx->up_stream));
+  }
+  CUDA_OK(cudaEventRecord(ctx->ev_up[s], ctx->up_stream));
+  CUDA_OK(cudaStreamWaitEvent(ctx->stream, ctx->ev_up[s], 0));
+  ctx->job_up[s].batch = batch;
+  hb_ctr_hempc_eval(ctx, &ctx->job_up[s], Ka, Kb, &ctx->job_in[s][0], &ctx->job_in[s][1], &ctx->job_in[s][2], &ctx->job_in[s][3], rk);
+  CUDA_OK(cudaEventRecord(ctx->ev_comp[s], ctx->stream));
+  CUDA_OK(cudaStreamWaitEvent(ctx->down_stream, ctx->ev_comp[s], 0));
+  CUDA_OK(cudaMemcpyAsync(out_up, ctx->job_up[s].words, (size_t)batch * out_words * 8, cudaMemcpyDeviceToHost, ctx->down_stream));
+  CUDA_OK(cudaEventRecord(ctx->job_done[s], ctx->down_stream));
+  ctx->job_busy[s] = true;
+  return ticket;
+}
+
+extern "C" void hb_ctr_hempc_wait(hb_ctx *ctx, uint64_t ticket) { use_device(ctx);
+  if (ticket >= ctx->job_next) hb_die("hb_ctr_hempc_wait: ticket %llu was never issued", (unsigned long long)ticket);
+  if (ticket + 2 < ctx->job_next) return;           // its buffer set has been reused since: that submission had to finish first
+  const unsigned s = (unsigned)(ticket & 1);
+  if (ctx->job_busy[s]) { CUDA_OK(cudaEventSynchronize(ctx->job_done[s])); ctx->job_busy[s] = false; }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // client side on the device: he_enc_pk / he_dec (he-encrypt.c:37-74,107-123)
 // ---------------------------------------------------------------------------------------------------------
@@ -1410,7 +1655,7 @@ static void do_recon_add(hb_ctx *c, const uint64_t *chat, unsigned D, uint64_t *
   }
 }
 
-extern "C" void hb_pk_upload(hb_ctx *ctx, hb_evk *pk, const uint64_t *p0_words, const uint64_t *p1_words) {
+extern "C" void hb_pk_upload(hb_ctx *ctx, hb_evk *pk, const uint64_t *p0_words, const uint64_t *p1_words) { use_device(ctx);
   const hb::HostTables &h = ctx->ht;
   const size_t polyw = (size_t)h.WC * h.N, half = (size_t)h.dim * h.N;
   uint64_t *words = (uint64_t *)hb_dev_alloc(ctx, 2 * polyw * 8);
@@ -1424,7 +1669,7 @@ extern "C" void hb_pk_upload(hb_ctx *ctx, hb_evk *pk, const uint64_t *p0_words, 
   hb_dev_free(ctx, raw);
 }
 
-extern "C" void hb_sk_upload(hb_ctx *ctx, hb_sk *sk, const int64_t *s) {
+extern "C" void hb_sk_upload(hb_ctx *ctx, hb_sk *sk, const int64_t *s) { use_device(ctx);
   const hb::HostTables &h = ctx->ht;
   memset(sk, 0, sizeof *sk);
   uint64_t *words = (uint64_t *)hb_dev_alloc(ctx, (size_t)h.N * 8);
@@ -1433,14 +1678,14 @@ extern "C" void hb_sk_upload(hb_ctx *ctx, hb_sk *sk, const int64_t *s) {
   do_poly_ntt(ctx, words, h.N, 1, sk->hat, h.dimub, 1);
   hb_dev_free(ctx, words);
 }
-extern "C" void hb_sk_free(hb_ctx *ctx, hb_sk *sk) {
+extern "C" void hb_sk_free(hb_ctx *ctx, hb_sk *sk) { use_device(ctx);
   hb_dev_free(ctx, sk->hat);
   for (uint64_t *&p : sk->scaled) { hb_dev_free(ctx, p); p = nullptr; }
   sk->hat = nullptr;
 }
 
 extern "C" void hb_he_enc_pk(hb_ctx *ctx, hb_ct *ct, const uint64_t *pt_words, double pt_nu, const hb_evk *pk, const int64_t *v,
-                             const int64_t *e0, const int64_t *e1) {
+                             const int64_t *e0, const int64_t *e1) { use_device(ctx);
   need_ct(ct, "hb_he_enc_pk");
   if (!pk || !pk->p) hb_die("hb_he_enc_pk: public key is not loaded");
   const hb::HostTables &h = ctx->ht;
@@ -1468,7 +1713,7 @@ extern "C" void hb_he_enc_pk(hb_ctx *ctx, hb_ct *ct, const uint64_t *pt_words, d
   CUDA_OK(cudaStreamSynchronize(ctx->stream));      // the host arrays may be reused by the caller
 }
 
-extern "C" void hb_he_dec(hb_ctx *ctx, uint64_t *pt_words, const hb_ct *ct, const hb_sk *sk) {
+extern "C" void hb_he_dec(hb_ctx *ctx, uint64_t *pt_words, const hb_ct *ct, const hb_sk *sk) { use_device(ctx);
   need_ct(ct, "hb_he_dec");
   if (!sk || !sk->hat) hb_die("hb_he_dec: secret key is not loaded");
   const hb::HostTables &h = ctx->ht;
@@ -1501,7 +1746,7 @@ extern "C" void hb_he_dec(hb_ctx *ctx, uint64_t *pt_words, const hb_ct *ct, cons
 extern "C" unsigned hb_genswk_words(const hb_ctx *ctx) { return (ctx->ht.nbitsPqL + 1 + 63) / 64; }
 
 extern "C" void hb_he_genswk(hb_ctx *ctx, unsigned nkeys, const uint64_t *a_words, const int64_t *e, const int64_t *sp, const hb_sk *sk,
-                             uint64_t *out_p0, uint64_t *out_p1) {
+                             uint64_t *out_p0, uint64_t *out_p1) { use_device(ctx);
   if (!sk || !sk->hat) hb_die("hb_he_genswk: secret key is not loaded");
   if (!nkeys) return;
   const hb::HostTables &h = ctx->ht;
@@ -1579,15 +1824,15 @@ extern "C" void hb_he_genswk(hb_ctx *ctx, unsigned nkeys, const uint64_t *a_word
 static void check_primes(const hb_ctx *ctx, unsigned d0, unsigned D, const char *what) {
   if (D == 0 || d0 + D > ctx->ht.dimub) hb_die("%s: primes [%u,%u) outside the chain of %u", what, d0, d0 + D, ctx->ht.dimub);
 }
-extern "C" void hb_ntt_forward(hb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D, int strict) {
+extern "C" void hb_ntt_forward(hb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D, int strict) { use_device(ctx);
   check_primes(ctx, d0, D, "hb_ntt_forward");
   if (nlimbs) do_ntt_fwd(ctx, in, out, nlimbs, d0, D, strict != 0);
 }
-extern "C" void hb_ntt_inverse(hb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D) {
+extern "C" void hb_ntt_inverse(hb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D) { use_device(ctx);
   check_primes(ctx, d0, D, "hb_ntt_inverse");
   if (nlimbs) do_ntt_inv(ctx, in, out, nlimbs, d0, D);
 }
-extern "C" void hb_ntt_forward_host(hb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D, int strict) {
+extern "C" void hb_ntt_forward_host(hb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t nlimbs, unsigned d0, unsigned D, int strict) { use_device(ctx);
   check_primes(ctx, d0, D, "hb_ntt_forward_host");
   const size_t bytes = nlimbs * ctx->ht.N * 8;
   uint64_t *buf = ws_get(ctx, ctx->wsA, ctx->wsA_bytes, bytes);
@@ -1596,18 +1841,19 @@ extern "C" void hb_ntt_forward_host(hb_ctx *ctx, const uint64_t *in, uint64_t *o
   CUDA_OK(cudaMemcpyAsync(out, buf, bytes, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_OK(cudaStreamSynchronize(ctx->stream));
 }
-extern "C" void hb_poly_ntt(hb_ctx *ctx, const uint64_t *polys, unsigned W, size_t npoly, unsigned D, uint64_t *out) {
+extern "C" void hb_poly_ntt(hb_ctx *ctx, const uint64_t *polys, unsigned W, size_t npoly, unsigned D, uint64_t *out) { use_device(ctx);
   check_primes(ctx, 0, D, "hb_poly_ntt");
   if (W == 0 || W > ctx->ht.WC) hb_die("hb_poly_ntt: %u words per coefficient outside [1,%u]", W, ctx->ht.WC);
   if (npoly) do_poly_ntt(ctx, polys, (size_t)W * ctx->ht.N, (int)W, out, D, npoly);
 }
-extern "C" void hb_rns2words(hb_ctx *ctx, const uint64_t *limbs, size_t npoly, unsigned D, unsigned k, unsigned Wout, uint64_t *out) {
+extern "C" void hb_rns2words(hb_ctx *ctx, const uint64_t *limbs, size_t npoly, unsigned D, unsigned k, unsigned Wout, uint64_t *out) { use_device(ctx);
   check_primes(ctx, 0, D, "hb_rns2words");
   if (k == 0 || k > 64 * ctx->ht.WC) hb_die("hb_rns2words: modulus 2^%u outside (0, 2^%u]", k, 64 * ctx->ht.WC);
   if (npoly) do_recon_smod(ctx, limbs, D, out, (int)Wout, (int)k, npoly, false);
 }
-extern "C" void hb_poly_rot(hb_ctx *ctx, const uint64_t *polys, unsigned W, size_t npoly, int rot, uint64_t *out) {
+extern "C" void hb_poly_rot(hb_ctx *ctx, const uint64_t *polys, unsigned W, size_t npoly, int rot, uint64_t *out) { use_device(ctx);
   const unsigned ginv = rot < 0 ? 2 * ctx->ht.N - 1 : pow5_inv_mod_2n(ctx, (unsigned)rot);
   const size_t total = npoly * ctx->ht.N;
+  if (out == polys) hb_die("hb_poly_rot: the permutation is not in place (out must not alias polys)");
   if (total) launch(ctx, "k_poly_automorph", hbdev::k_poly_automorph, (unsigned)((total + 255) / 256), 256, 0, 1, polys, out, (int)W, ginv, ctx->ht.N, npoly);
 }

@@ -9,6 +9,7 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 #include "hb_dev.cuh"
+#include "hb_kernels.cuh"
 
 namespace hb32 {
 
@@ -224,14 +225,14 @@ __global__ void k32_shoup_prep(const uint32_t *__restrict__ in, uint32_t *__rest
 // ---------------------------------------------------------------------------------------------------------------
 template <int LOGN>
 __global__ void __launch_bounds__(Cfg32<LOGN>::THREADS)
-k32_mulacc_intt(const uint32_t *__restrict__ hat, size_t hat_jstride, const uint32_t *__restrict__ pthat_all, size_t pthat_gstride, unsigned n1,
-                unsigned nq, uint32_t *__restrict__ chat, Tables32 T, unsigned D) {
+k32_mulacc_intt(const uint32_t *__restrict__ hat, size_t hat_jstride, const uint32_t *__restrict__ pthat_all, size_t pthat_gstride,
+                const __grid_constant__ hbdev::GroupMap GM, unsigned n1, unsigned nq, uint32_t *__restrict__ chat, Tables32 T, unsigned D) {
   typedef Cfg32<LOGN> G;
   extern __shared__ __align__(16) uint32_t sm32[];
   const unsigned qq = blockIdx.x / D, d = blockIdx.x % D, q = qq % nq;
   const uint32_t p = T.primes[d].p, p2 = 2 * p;
   const uint32_t *a = hat + ((size_t)q * D + d) * G::N;
-  const uint32_t *w = pthat_all + ((size_t)(qq / nq) * pthat_gstride + d) * 2 * G::N;       // strides in limbs
+  const uint32_t *w = pthat_all + ((size_t)GM.idx[qq / nq] * pthat_gstride + d) * 2 * G::N;       // strides in limbs
 #pragma unroll 2
   for (int i = threadIdx.x; i < G::N; i += G::THREADS) {
     uint32_t acc = 0;
@@ -367,7 +368,7 @@ k32_poly_ntt_all(const uint64_t *__restrict__ src, size_t poly_stride, uint32_t 
 template <int LOGN, int NJ>
 __global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_MA_MINB)
 k32_mulacc_intt_all(const uint32_t *__restrict__ hat, size_t hat_jstride, const uint32_t *__restrict__ pthat_all, size_t pthat_gstride,
-                    unsigned ngroups, unsigned nq, uint32_t *__restrict__ chat, Tables32 T, unsigned D) {
+                    const __grid_constant__ hbdev::GroupMap GM, unsigned ngroups, unsigned nq, uint32_t *__restrict__ chat, Tables32 T, unsigned D) {
   typedef Cfg32<LOGN> G;
   constexpr int V = G::N / 4 / G::THREADS;                    // uint4 per thread
   extern __shared__ __align__(16) uint32_t sm32[];
@@ -383,7 +384,7 @@ k32_mulacc_intt_all(const uint32_t *__restrict__ hat, size_t hat_jstride, const 
   const uint2 *itw = T.itw + (size_t)d * G::N;
 #pragma unroll 1
   for (unsigned g = 0; g < ngroups; g++) {
-    const uint32_t *w = pthat_all + ((size_t)g * pthat_gstride + d) * 2 * G::N;               // strides in limbs
+    const uint32_t *w = pthat_all + ((size_t)GM.idx[g] * pthat_gstride + d) * 2 * G::N;       // strides in limbs
 #pragma unroll
     for (int k = 0; k < V; k++) {
       const int i4 = threadIdx.x + k * G::THREADS;

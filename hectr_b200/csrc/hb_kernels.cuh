@@ -18,6 +18,11 @@ struct KsGroups {
   unsigned g[HB_MAX_GROUPS], ginv[HB_MAX_GROUPS];
   unsigned gbatch;
 };
+// giant steps taken by a launch: slot s of the launch is giant step idx[s] of the matrix (identically zero giant steps of a
+// sparse matrix are skipped: their inner sum is the zero ciphertext, whose key switch is zero again)
+struct GroupMap {
+  unsigned idx[HB_MAX_GROUPS];
+};
 struct TailGroups {
   unsigned ginv[HB_MAX_GROUPS];
   unsigned gbatch;
@@ -127,17 +132,14 @@ __global__ void k_shoup_prep(const uint64_t *__restrict__ in, ulonglong2 *__rest
 template <int LOGN>
 __global__ void __launch_bounds__(Cfg<LOGN>::THREADS, KsBlocks<LOGN>::value)
 k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, const __grid_constant__ KsGroups S,
-          unsigned dimevk, uint64_t *__restrict__ chat, Tables T, unsigned D) {
+          unsigned dimevk, uint64_t *__restrict__ chat, Tables T, unsigned D, unsigned d0, unsigned Dn) {
+  // D: limbs of the CRT basis (selects the pre-weights); this launch covers limbs [d0, d0 + Dn) and writes them compactly:
+  // chat[b][h][Dn][N].  A whole key switch has d0 = 0, Dn = D.
   typedef Cfg<LOGN> G;
   extern __shared__ __align__(16) uint64_t smem[];
   uint64_t *smA = smem, *smB = smem + G::SMEM_WORDS;
   const unsigned idx = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
-#ifdef HB_DMAJOR
-  const unsigned nb = gridDim.x / (G::C * D);
-  const unsigned d = idx / nb, b = idx % nb;
-#else
-  const unsigned b = idx / D, d = idx % D;
-#endif
+  const unsigned b = idx / Dn, dd = idx % Dn, d = d0 + dd;
   const PrimeConsts pc = T.primes[d];
   const Mod m = make_mod(pc.p);
   const uint64_t negW = pc.p - T.pow64[(size_t)d * (T.WC + 1) + W];
@@ -155,8 +157,63 @@ k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, const __g
       smB[pidx(i)] = shoup_lazy(smA[pidx(i)], k.x, k.y, m);
     }
     __syncthreads();
-    uint64_t *dst = chat + (((size_t)b * 2 + h) * D + d) * G::N;
+    uint64_t *dst = chat + (((size_t)b * 2 + h) * Dn + dd) * G::N;
     ntt_inverse<LOGN, INV_RAW>(smB, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, make_tw(T, d, true), pc, m);
+  }
+}
+
+// =========================================================================================================
+// Giant steps of he_gemv (GPQHE/src/he-algo.c:80-84), limbs that do NOT divide P, summed over the giant steps:
+//   chatX[b][h][d - d0] = y-weighted invntt( sum_g ntt( decompose( sigma_g(inner_g[b].c1) ) mod p_d ) o rk[g n1].p_h[d] )
+// he_gemv adds the n2 key-switched inner sums.  Each key switch is  c_g = (x_g - R_g)/P + round_g (+ sigma_g(c0)), with x_g the
+// exact product and R_g = x_g mod P, so  sum_g c_g = (X - sum_g R_g)/P + sum_g round_g,  X = sum_g x_g.  R_g needs x_g modulo
+// the primes of P only (limbs d < dim: k_ks_limb with d0 = 0, Dn = dim); for every other limb the sum is taken in the transform
+// domain and ONE inverse transform per half serves all giant steps.  X is the same integer as long as |X| < P_D / 2, which the
+// host checks from the key bound recorded at hb_evk_upload (hb_api.cu gemv_fused).  The he_add chain only re-centres modulo
+// q_l, so the words are the reference's.  One limb per CTA (N <= 2^13), three shared-memory buffers.
+// =========================================================================================================
+template <int LOGN>
+struct KsSumBlocks { static constexpr int value = (LOGN <= 12) ? 2 : 1; };
+
+template <int LOGN>
+__global__ void __launch_bounds__(Cfg<LOGN>::THREADS, KsSumBlocks<LOGN>::value)
+k_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src_gstride, int W, const __grid_constant__ KsGroups S,
+              unsigned ng, unsigned dimevk, uint64_t *__restrict__ chatX, Tables T, unsigned D, unsigned d0, unsigned Dn) {
+  typedef Cfg<LOGN> G;
+  static_assert(G::C == 1, "the summed giant-step kernel keeps one limb per CTA");
+  extern __shared__ __align__(16) uint64_t smem[];
+  uint64_t *smA = smem;
+  const unsigned b = blockIdx.x / Dn, dd = blockIdx.x % Dn, d = d0 + dd;
+  const PrimeConsts pc = T.primes[d];
+  const Mod m = make_mod(pc.p);
+  const uint64_t negW = pc.p - T.pow64[(size_t)d * (T.WC + 1) + W];
+  const ulonglong2 *dc = T.dec_s + ((size_t)D * T.dimub + d) * (T.WC + 1);
+  const Tw tw = make_tw(T, d, false);
+#pragma unroll 1
+  for (unsigned g = 0; g < ng; g++) {
+    const uint64_t *poly = src + (size_t)g * src_gstride + (size_t)b * src_bstride;
+    poly_forward<LOGN, true>(smA, poly, W, S.g[g], S.ginv[g], pc, m, negW, tw, dc);
+    const bool last = g + 1 == ng;
+#pragma unroll 1
+    for (int h = 0; h < 2; h++) {
+      uint64_t *acc = smem + (size_t)(1 + h) * G::SMEM_WORDS;
+      const ulonglong2 *key = S.evk[g] + ((size_t)h * dimevk + d) * G::N;
+#pragma unroll 4
+      for (int i = threadIdx.x; i < G::N; i += G::THREADS) {
+        const ulonglong2 k = HB_LDS2(&key[i]);
+        uint64_t v = shoup_lazy(smA[pidx(i)], k.x, k.y, m);              // below 2p; at most 8 terms: below 16p
+        if (g) v += acc[pidx(i)];
+        acc[pidx(i)] = (last && ng > 1) ? fold(v, m) : v;                // the inverse transform takes values below 2p
+      }
+    }
+    __syncthreads();                                                     // smA is refilled; the accumulators are thread-private
+  }
+  const Tw itw = make_tw(T, d, true);
+#pragma unroll 1
+  for (int h = 0; h < 2; h++) {
+    uint64_t *acc = smem + (size_t)(1 + h) * G::SMEM_WORDS;
+    uint64_t *dst = chatX + (((size_t)b * 2 + h) * Dn + dd) * G::N;
+    ntt_inverse<LOGN, INV_RAW>(acc, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, itw, pc, m);
   }
 }
 
@@ -259,13 +316,13 @@ k_mulpt_limb(const uint64_t *__restrict__ ct, size_t poly_stride, int W, const u
 template <int LOGN>
 __global__ void __launch_bounds__(Cfg<LOGN>::THREADS, Cfg<LOGN>::MINBLOCKS)
 k_mulacc_intt(const uint64_t *__restrict__ hat, size_t hat_jstride, const ulonglong2 *__restrict__ pthat_all, size_t pthat_gstride,
-              unsigned n1, unsigned nq, uint64_t *__restrict__ chat, Tables T, unsigned D) {
+              const __grid_constant__ GroupMap GM, unsigned n1, unsigned nq, uint64_t *__restrict__ chat, Tables T, unsigned D) {
   typedef Cfg<LOGN> G;
   extern __shared__ __align__(16) uint64_t smem[];
   const unsigned idx = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
   // all giant steps in one launch: group i = qq / nq reads the SAME hat[j][q] with its own diagonals pthat_all + i * gstride
   const unsigned qq = idx / D, d = idx % D, q = qq % nq;
-  const ulonglong2 *pthat = pthat_all + (size_t)(qq / nq) * pthat_gstride;
+  const ulonglong2 *pthat = pthat_all + (size_t)GM.idx[qq / nq] * pthat_gstride;
   const PrimeConsts pc = T.primes[d];
   const Mod m = make_mod(pc.p);
   const size_t off = (size_t)chunk * G::M;
@@ -446,15 +503,11 @@ __global__ void k_recon_add(const uint64_t *__restrict__ chat, unsigned D, uint6
 // first `dim` limbs (P = p_0...p_{dim-1}); see DESIGN.md "key-switch tail" for the proof.
 // add0/add1: optional polynomials (batch stride given) with the automorphism ginv applied on the fly.
 // =========================================================================================================
-// exact path for one coefficient: t = (x - R) P^-1 mod 2^(64 WK), roundup = [R > floor(P/2)]
-template <int WK, int WPK>
-__device__ __forceinline__ void ks_exact(const uint64_t *__restrict__ limbs, unsigned D, const Tables &T, uint64_t (&t)[WK],
-                                      bool &roundup_out) {
-  const unsigned N = T.N;
-  uint64_t acc[WK];
-  crt_low<WK, true>([&](unsigned d) { return limbs[(size_t)d * N]; }, D, T, acc);
-  // ---- R = x mod P, exact ----
-  uint64_t R[WPK];
+// R = x mod P rebuilt exactly from the limbs of the primes of P (limbs[e * N], pre-weighted for a D-limb basis, any value
+// below 2^64), and roundup = [R > floor(P/2)]  (mpi_rdiv, types.c:115-128)
+template <int WPK>
+__device__ __forceinline__ void ks_R_exact(const uint64_t *__restrict__ limbs, size_t lstride, unsigned D, const Tables &T,
+                                           uint64_t (&R)[WPK], bool &roundup_out) {
 #pragma unroll
   for (int w = 0; w < WPK; w++) R[w] = 0;
   uint64_t Flo = 0, Fhi = 0;
@@ -462,7 +515,7 @@ __device__ __forceinline__ void ks_exact(const uint64_t *__restrict__ limbs, uns
   for (unsigned d = 0; d < T.dim; d++) {
     const uint64_t p = T.primes[d].p, mu = T.primes[d].mu;
     const ulonglong2 kz = T.ks_z[(size_t)D * T.dim + d];                      // limbs hold y_d: re-weight for P
-    const uint64_t z = shoup(limbs[(size_t)d * N], kz.x, kz.y, p);
+    const uint64_t z = shoup(limbs[(size_t)d * lstride], kz.x, kz.y, p);
     uint64_t lo = z * mu, hi = __umul64hi(z, mu);
     Flo += lo;
     Fhi += hi + (Flo < lo);
@@ -522,7 +575,7 @@ __device__ __forceinline__ void ks_exact(const uint64_t *__restrict__ limbs, uns
       }
     }
   }
-  bool roundup = false;  // R > floor(P/2)   (mpi_rdiv, types.c:115-128)
+  bool roundup = false;  // R > floor(P/2)
   {
     bool decided = false;
 #pragma unroll
@@ -533,19 +586,12 @@ __device__ __forceinline__ void ks_exact(const uint64_t *__restrict__ limbs, uns
       }
     }
   }
-  // ---- t = (x - R) * P^-1 mod 2^(64 WK) ----
-  uint64_t diff[WK];
-  {
-    uint64_t bw = 0;
-#pragma unroll
-    for (int w = 0; w < WK; w++) {
-      const uint64_t rw = (w < WPK && w < WP) ? R[w < WPK ? w : 0] : 0;
-      uint64_t sub = rw + bw;
-      uint64_t nb = (sub < rw) | (acc[w] < sub);
-      diff[w] = acc[w] - sub;
-      bw = nb;
-    }
-  }
+  roundup_out = roundup;
+}
+
+// t = diff * P^-1 mod 2^(64 WK)
+template <int WK>
+__device__ __forceinline__ void mul_Pinv(const uint64_t (&diff)[WK], const Tables &T, uint64_t (&t)[WK]) {
 #pragma unroll
   for (int w = 0; w < WK; w++) t[w] = 0;
 #pragma unroll
@@ -563,7 +609,32 @@ __device__ __forceinline__ void ks_exact(const uint64_t *__restrict__ limbs, uns
       carry = hh;
     }
   }
-  roundup_out = roundup;
+}
+
+// exact path for one coefficient: t = (x - R) P^-1 mod 2^(64 WK), roundup = [R > floor(P/2)]
+template <int WK, int WPK>
+__device__ __forceinline__ void ks_exact(const uint64_t *__restrict__ limbs, unsigned D, const Tables &T, uint64_t (&t)[WK],
+                                      bool &roundup_out) {
+  const unsigned N = T.N;
+  uint64_t acc[WK];
+  crt_low<WK, true>([&](unsigned d) { return limbs[(size_t)d * N]; }, D, T, acc);
+  uint64_t R[WPK];
+  ks_R_exact<WPK>(limbs, N, D, T, R, roundup_out);
+  const int WP = T.WP;
+  // ---- t = (x - R) * P^-1 mod 2^(64 WK) ----
+  uint64_t diff[WK];
+  {
+    uint64_t bw = 0;
+#pragma unroll
+    for (int w = 0; w < WK; w++) {
+      const uint64_t rw = (w < WPK && w < WP) ? R[w < WPK ? w : 0] : 0;
+      uint64_t sub = rw + bw;
+      uint64_t nb = (sub < rw) | (acc[w] < sub);
+      diff[w] = acc[w] - sub;
+      bw = nb;
+    }
+  }
+  mul_Pinv<WK>(diff, T, t);
 }
 
 // t + roundup + sigma(add_h)[i], centred mod 2^k, stored as Wout words
@@ -710,6 +781,147 @@ __global__ void __launch_bounds__(128) k_ks_finish_fast(const uint64_t *__restri
   ks_tail<WK>(t, roundup, add, add_bstride, Wadd, ginv, N, b, badd, h, i, out, Wout, k);
 }
 
+// ---- summed giant steps -----------------------------------------------------------------------------------------
+// Tail of the n2 giant-step key switches of he_gemv, their he_add chain and the closing he_rs (he-algo.c:80-90) in one pass:
+//   out = smod( rdiv( smod( sum_g [ (x_g - R_g)/P + [R_g > P/2] + sigma_g(inner_g.c0) ], 2^k ), 2^shift ), 2^kout )
+// X = sum_g x_g comes from ONE reconstruction: the limbs of the primes of P are the sums of the per-giant-step limbs
+// (chatP, which also give every R_g exactly as in k_ks_finish_fast), the other limbs were summed in the transform domain by
+// k_ks_limb_sum (chatX).  Fixed-point decisions with the same margins as the fast tail; a thread that lands within the margin
+// of any boundary takes ks_sum_slow, which settles all of them with multiword arithmetic.  q_l <= 2^128.
+struct SumGroups {
+  unsigned ginv[HB_MAX_GROUPS];
+  unsigned ng;
+};
+
+template <int WPK>
+__device__ __noinline__ void ks_sum_slow(const uint64_t *__restrict__ limbsP, size_t gstride, const uint64_t *__restrict__ limbsX,
+                                         unsigned D, unsigned ng, const Tables &T, uint64_t (&t)[2], unsigned &nround) {
+  const unsigned N = T.N, dim = T.dim;
+  uint64_t acc[2];
+  crt_low<2, true>(
+      [&](unsigned d) -> uint64_t {
+        const Mod m = make_mod(T.primes[d].p);
+        if (d >= dim) return canon(limbsX[(size_t)(d - dim) * N], m);
+        uint64_t sum = 0;
+        for (unsigned g = 0; g < ng; g++) sum = addmod(sum, canon(limbsP[(size_t)g * gstride + (size_t)d * N], m), m.p);
+        return sum;
+      },
+      D, T, acc);
+  nround = 0;
+  const int WP = T.WP;
+  for (unsigned g = 0; g < ng; g++) {
+    uint64_t R[WPK];
+    bool up;
+    ks_R_exact<WPK>(limbsP + (size_t)g * gstride, N, D, T, R, up);
+    nround += up ? 1u : 0u;
+    uint64_t bw = 0;
+#pragma unroll
+    for (int w = 0; w < 2; w++) {
+      const uint64_t rw = (w < WPK && w < WP) ? R[w] : 0;
+      const uint64_t sub = rw + bw;
+      const uint64_t nb = (sub < rw) | (acc[w] < sub);
+      acc[w] -= sub;
+      bw = nb;
+    }
+  }
+  mul_Pinv<2>(acc, T, t);
+}
+
+template <int WPK, int D, int DIM>
+__global__ void __launch_bounds__(128)
+k_ks_finish_sum(const uint64_t *__restrict__ chatP, size_t chatP_gstride, const uint64_t *__restrict__ chatX, const __grid_constant__ KsFast F,
+                const uint64_t *__restrict__ add0, size_t add_gstride, size_t add_bstride, int Wadd, const __grid_constant__ SumGroups SG,
+                uint64_t *__restrict__ out, int Wout, int k, int shift, int kout, const __grid_constant__ Tables T, unsigned batch) {
+  static_assert(D <= 8 && DIM <= 4 && DIM < D, "summed key-switch tail: D <= 8, dim <= 4");
+  typedef unsigned __int128 u128;
+  const unsigned N = T.N;
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)batch * 2 * N) return;
+  const unsigned i = gid % N, h = (gid / N) & 1, b = gid / (2 * (size_t)N);
+  const unsigned ng = SG.ng;
+  const uint64_t *limbsP = chatP + ((size_t)b * 2 + h) * DIM * N + i;          // + g * chatP_gstride + e * N
+  const uint64_t *limbsX = chatX + ((size_t)b * 2 + h) * (D - DIM) * N + i;    // + (d - DIM) * N
+  const uint64_t ONE = 1ULL << 56, HALF = 1ULL << 55, MASK = ONE - 1, MARGIN = 1ULL << 38;
+  uint64_t acc[2] = {0, 0}, Fx = 0;
+#pragma unroll
+  for (int d = DIM; d < D; d++) {
+    const uint64_t y = HB_LD(&limbsX[(size_t)(d - DIM) * N]);                   // below 2p
+    Fx += (uint64_t)hi32(y) * hi32(F.mu[d]);
+    mac_low<2>(acc, y, F.phat[d]);
+  }
+  uint64_t ysum[DIM];
+#pragma unroll
+  for (int e = 0; e < DIM; e++) ysum[e] = 0;
+  u128 Rsum = 0;
+  unsigned nround = 0;
+  bool unsure = false;
+#pragma unroll 1
+  for (unsigned g = 0; g < ng; g++) {
+    uint64_t Rl[2] = {0, 0}, Fr = 0;
+#pragma unroll
+    for (int e = 0; e < DIM; e++) {
+      const uint64_t a = HB_LD(&limbsP[(size_t)g * chatP_gstride + (size_t)e * N]);     // below 2p
+      ysum[e] += a;                                                             // at most 8 giant steps: below 16p < 2^64
+      const Mod m = make_mod(F.p[e]);
+      const uint64_t z = shoup_lazy(a, F.kinv[e], F.kinvq[e], m);
+      Fr += (uint64_t)hi32(z) * hi32(F.mu[e]);
+      mac_low<2>(Rl, z, F.kphat[e]);
+    }
+    const uint64_t fr = Fr & MASK, v2 = Fr >> 56;
+    unsure |= fr < MARGIN || fr > ONE - MARGIN || (fr > HALF - MARGIN && fr < HALF + MARGIN);
+    nround += fr > HALF ? 1u : 0u;
+    uint64_t sub[2] = {0, 0};
+    mac_low<2>(sub, v2, F.kP);
+    Rsum += (((u128)Rl[1] << 64) | Rl[0]) - (((u128)sub[1] << 64) | sub[0]);
+  }
+#pragma unroll
+  for (int e = 0; e < DIM; e++) {
+    Fx += (uint64_t)hi32(ysum[e]) * hi32(F.mu[e]);
+    mac_low<2>(acc, ysum[e], F.phat[e]);
+  }
+  const uint64_t fx = (Fx + HALF) & MASK;
+  unsure |= fx < MARGIN || fx > ONE - MARGIN;
+  u128 tt;
+  if (unsure) {
+    uint64_t t[2];
+    ks_sum_slow<WPK>(limbsP, chatP_gstride, limbsX, D, ng, T, t, nround);
+    tt = ((u128)t[1] << 64) | t[0];
+  } else {
+    const uint64_t v = (Fx + HALF) >> 56;
+    uint64_t dlt[2] = {0, 0};
+    mac_low<2>(dlt, v, F.PD);
+    tt = ((((u128)acc[1]) << 64) | acc[0]) - ((((u128)dlt[1]) << 64) | dlt[0]) - Rsum;      // every constant already times P^-1
+  }
+  tt += nround;
+  if (h == 0 && add0) {                                                          // sum_g sigma_g(inner_g.c0)
+#pragma unroll 1
+    for (unsigned g = 0; g < ng; g++) {
+      const unsigned ip = (i * SG.ginv[g]) & (2 * N - 1);
+      const uint64_t *ap = add0 + (size_t)g * add_gstride + (size_t)b * add_bstride + (ip & (N - 1));
+      const uint64_t lo = HB_LD(&ap[0]);
+      const uint64_t hi = Wadd > 1 ? HB_LD(&ap[N]) : (uint64_t)((int64_t)lo >> 63);
+      const u128 a = ((u128)hi << 64) | lo;
+      tt = (ip >= N) ? tt - a : tt + a;
+    }
+  }
+  uint64_t x[2] = {(uint64_t)tt, (uint64_t)(tt >> 64)};
+  sext_bits<2>(x, k);                                                            // the centred sum of the he_add chain
+  if (shift > 0 || kout != k) {                                                  // he_rs: rounded shift, ties toward -inf (types.c:115-128)
+    const __int128 vs = (__int128)((((u128)x[1]) << 64) | x[0]);
+    __int128 q = vs;
+    if (shift > 0) {
+      const u128 rem = (u128)vs & ((((u128)1) << shift) - 1), half = ((u128)1) << (shift - 1);
+      q = (vs >> shift) + (rem > half ? 1 : 0);
+    }
+    x[0] = (uint64_t)(u128)q;
+    x[1] = (uint64_t)((u128)q >> 64);
+    sext_bits<2>(x, kout);
+  }
+  uint64_t *o = out + ((size_t)b * 2 + h) * Wout * N + i;
+  HB_ST(&o[0], x[0]);
+  if (Wout > 1) HB_ST(&o[N], x[1]);
+}
+
 template <int WK, int WPK>
 __global__ void k_ks_finish(const uint64_t *__restrict__ chat, unsigned D, const uint64_t *__restrict__ add0,
                             const uint64_t *__restrict__ add1, size_t add_bstride, int Wadd, const __grid_constant__ TailGroups TG,
@@ -731,7 +943,9 @@ __global__ void k_ks_finish(const uint64_t *__restrict__ chat, unsigned D, const
 //   op 0: a + b   op 1: a - b   op 2: -a      then smod(., 2^k) = sign-extension from bit k-1.
 // One thread per (polynomial, coefficient); W words each.
 // =========================================================================================================
-__global__ void k_ct_addsub(const uint64_t *__restrict__ a, const uint64_t *__restrict__ b, uint64_t *__restrict__ out,
+// a, b and out may alias (he_neg works in place, he_add(s, s, x) he-algo.c:78): no __restrict__; every thread reads its own
+// words before it writes them.
+__global__ void k_ct_addsub(const uint64_t *a, const uint64_t *b, uint64_t *out,
                             int W, int k, int op, unsigned N, size_t npoly) {
   const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= npoly * N) return;
@@ -864,7 +1078,7 @@ __global__ void k_ct_combine(const uint64_t *__restrict__ u, int Wu, const uint6
 }
 
 // he_addpt / he_subpt (he-add.c:80-123): c0 +- pt, c1 only re-centred; pt is one polynomial [WC][N] shared by the batch.
-__global__ void k_ct_addpt(const uint64_t *__restrict__ a, const uint64_t *__restrict__ pt, uint64_t *__restrict__ out, int W, int k,
+__global__ void k_ct_addpt(const uint64_t *a, const uint64_t *__restrict__ pt, uint64_t *out, int W, int k,     // a, out may alias
                            int op, unsigned N, size_t npoly) {
   const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= npoly * N) return;

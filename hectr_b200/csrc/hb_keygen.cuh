@@ -160,4 +160,28 @@ __global__ void k_tail(const uint64_t *__restrict__ prod, Consts C, const int64_
   for (unsigned w = 0; w < C.WA; w++) out_a[((size_t)kk * C.WA + w) * C.N + i] = u[w];
 }
 
+// Bound of an evaluation key (hb_evk_upload).  coef[npoly][D][N]: the key's limbs back in the coefficient domain, canonical.
+// Per coefficient the exact CRT over the D key primes, centred mod P_D -- the integer he_genswk decomposed (he-kem.c:97-110), as
+// long as it was below P_D / 2, which smod(., P q_L) guarantees -- and the maximum bit length of its magnitude over the whole key.
+// A key made by he_genswk stays below P q_L / 2; limbs that are merely uniform residues (synthetic keys) reach P_D.
+__global__ void k_lift_bits(const uint64_t *__restrict__ coef, Consts C, unsigned npoly, unsigned *__restrict__ out_max) {
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)npoly * C.N) return;
+  const unsigned i = gid % C.N, q = gid / C.N;
+  const int W = (int)C.WX;
+  uint64_t u[MAXW];
+  for (int w = 0; w < W; w++) u[w] = 0;
+  for (unsigned d = 0; d < C.D; d++) {
+    const uint64_t p = C.primes[d];
+    const uint64_t y = mulmod(coef[((size_t)q * C.D + d) * C.N + i] % p, C.inv[d], p);
+    addmul(u, C.phat + (size_t)d * W, y, W);
+  }
+  for (unsigned it = 0; it <= C.D && ucmp(u, C.PD, W) >= 0; it++) sub(u, C.PD, W);
+  if (ucmp(u, C.PDh, W) >= 0) { sub(u, C.PD, W); neg(u, W); }         // magnitude of the centred value
+  unsigned bits = 0;
+  for (int w = W - 1; w >= 0; w--)
+    if (u[w]) { bits = 64u * (unsigned)w + (64u - (unsigned)__clzll((long long)u[w])); break; }
+  atomicMax(out_max, bits);
+}
+
 }  // namespace hbkg

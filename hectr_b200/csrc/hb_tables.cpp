@@ -20,7 +20,7 @@ uint64_t powmod(uint64_t a, uint64_t e, uint64_t m) {
 
 // Deterministic Miller-Rabin for 64-bit inputs (first twelve prime bases).  The reference uses 50
 // random rand() witnesses (precomp.c:153-191); both decide primality correctly for these inputs, and
-// tests/test_tables.py checks the resulting chain against the compiled reference.
+// tests/test_host_tables.py checks the resulting chain against the compiled reference.
 bool is_prime_u64(uint64_t n) {
   if (n < 2) return false;
   static const uint64_t small[] = {2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31, 37};

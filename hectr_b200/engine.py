@@ -318,6 +318,19 @@ class Engine:
                                         _ptr(ur), rk.arr, _ptr(out))
         return out
 
+    def ctr_hempc_submit_host(self, Ka, Kb, xhat, xr, uhat, ur, rk: EvalKeys, l: int, out: np.ndarray) -> int:
+        """Streaming form (hb_ctr_hempc_submit_host): returns a ticket; ``out`` is complete after ``ctr_hempc_wait(ticket)``.
+        The arrays must stay alive (and should be pinned) until then."""
+        Ka = np.ascontiguousarray(Ka, dtype=np.complex128)
+        Kb = np.ascontiguousarray(Kb, dtype=np.complex128)
+        for a in (xhat, xr, uhat, ur, out):
+            assert a.flags["C_CONTIGUOUS"] and a.dtype == np.uint64
+        return int(self.lib.hb_ctr_hempc_submit_host(self.ctx, xhat.shape[0], l, _ptr(Ka), _ptr(Kb), _ptr(xhat), _ptr(xr), _ptr(uhat),
+                                                     _ptr(ur), rk.arr, _ptr(out)))
+
+    def ctr_hempc_wait(self, ticket: int):
+        self.lib.hb_ctr_hempc_wait(self.ctx, ticket)
+
     # ---- client side on the device (he-encrypt.c) ---------------------------------------------------------
     def pk(self, p0_words: np.ndarray, p1_words: np.ndarray) -> HbEvk:
         """he_pk (gpqhe.h:72-76) as words[W_L][N] each -> device transform limbs."""

@@ -155,6 +155,16 @@ void hb_ctr_hempc_eval_host(hb_ctx *ctx, unsigned batch, unsigned l, const doubl
                             const uint64_t *in_xhat, const uint64_t *in_xr, const uint64_t *in_uhat,
                             const uint64_t *in_ur, const hb_evk *rk, uint64_t *out_up);
 
+/* Streaming form for a server that evaluates batch after batch: enqueue upload, evaluation and download of one batch and
+ * return a ticket; hb_ctr_hempc_wait blocks until that batch's out_up is complete.  Two submissions may be in flight (two
+ * persistent device buffer sets), so the PCIe transfers of batch k+1 and k-1 overlap the evaluation of batch k while every
+ * launch keeps the full batch size; a third submission first waits for the first.  Host buffers should be pinned
+ * (hb_host_alloc) and must stay valid until the wait returns. */
+uint64_t hb_ctr_hempc_submit_host(hb_ctx *ctx, unsigned batch, unsigned l, const double *Ka, const double *Kb,
+                                  const uint64_t *in_xhat, const uint64_t *in_xr, const uint64_t *in_uhat,
+                                  const uint64_t *in_ur, const hb_evk *rk, uint64_t *out_up);
+void hb_ctr_hempc_wait(hb_ctx *ctx, uint64_t ticket);
+
 /* ---- compositions of he-algo.c, built only from the entry points above: hb_algo.cpp -------------- */
 void hb_he_sum(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, const hb_evk *rk);                       /* he_sum  he-algo.c:95-103 */
 void hb_he_idx(hb_ctx *ctx, hb_ct *dst, const hb_ct *ct, unsigned idx, const hb_evk *rk);         /* he_idx  :105-112 */

@@ -277,6 +277,26 @@ class Ref:
         return np.stack([np.ctypeslib.as_array(evk.p0.coeffs, shape=shape).copy(),
                          np.ctypeslib.as_array(evk.p1.coeffs, shape=shape).copy()])
 
+    def evk_from_array(self, arr: np.ndarray) -> HeEvk:
+        """uint64[2][dimevk][N] -> a reference he_evk_t holding those limbs (keys made elsewhere, e.g. by hb_he_genswk)."""
+        arr = np.ascontiguousarray(arr, dtype=np.uint64)
+        assert arr.shape == (2, self.dimevk, self.n), arr.shape
+        evk = HeEvk()
+        self.lib.he_alloc_evk(C.byref(evk))
+        C.memmove(evk.p0.coeffs, arr[0].ctypes.data, arr[0].nbytes)
+        C.memmove(evk.p1.coeffs, arr[1].ctypes.data, arr[1].nbytes)
+        return evk
+
+    def rk_from_array(self, arr: np.ndarray):
+        """uint64[slots][2][dimevk][N] -> he_evk_t[slots]"""
+        rk = (HeEvk * self.slots)()
+        for i in range(self.slots):
+            self.lib.he_alloc_evk(C.byref(rk[i]))
+            a = np.ascontiguousarray(arr[i], dtype=np.uint64)
+            C.memmove(rk[i].p0.coeffs, a[0].ctypes.data, a[0].nbytes)
+            C.memmove(rk[i].p1.coeffs, a[1].ctypes.data, a[1].nbytes)
+        return rk
+
     def encode(self, m) -> HePt:
         m = np.ascontiguousarray(m, dtype=np.complex128)
         assert m.shape == (self.slots,)

@@ -3,6 +3,8 @@ compiled, unmodified reference.  A deep level chain (q = 2^520, Delta = 2^40, L 
 (N = 128: below 2^10 the reference accepts any q, precomp.c:339-340) keeps the CPU side to seconds; every function is a
 fixed sequence of he_mul / he_rs / he_moddown / he_mulpt / he_addpt ..., so a bit-exact result pins the order of
 operations, the level bookkeeping and every primitive across thirteen levels (1 to 9 words per coefficient)."""
+import ctypes as C
+
 import numpy as np
 import pytest
 
@@ -176,7 +178,8 @@ def test_genswk_config_A_rotation_keys_work(ref_available):
         L = ref.L
         W = eng.words(L)
         s2 = ref.poly_mul_words(sk, s, eng.logq(L) // 59 + 1, eng.logq(L), W)            # he_genrlk, he-kem.c:133
-        assert W == 1 or not s2[1:].any() or True
+        # |sk^2| <= hamming weight: one signed word; the higher words of the W-word form are its sign extension
+        assert all(np.array_equal(s2[w].view(np.int64), s2[0].view(np.int64) >> 63) for w in range(1, W))
         sps = [ref.poly_rot(s, 1)[0].view(np.int64), ref.poly_rot(s, 5)[0].view(np.int64), s2[0].view(np.int64)]
         got, dsk = _genswk_case(ref, eng, sk, sps)
         keys = np.zeros((16,) + got.shape[1:], dtype=np.uint64)
@@ -191,3 +194,75 @@ def test_genswk_config_A_rotation_keys_work(ref_available):
         rk.free()
     finally:
         eng.close()
+
+
+GENRK_CHILD = r"""
+import sys
+sys.path.insert(0, %(root)r)
+import numpy as np
+from oracle.ref import Ref
+mode, out = sys.argv[1], sys.argv[2]
+params = (12, 109, 16, 50)
+ref = Ref.get(*params)
+pk, sk = ref.keypair()
+NK = 3
+if mode == "ref":
+    rk = ref.genrk(sk)                                   # he_genrk itself (he-kem.c:154-169)
+    np.save(out, np.stack([ref.evk_to_array(rk[i]) for i in range(NK)]))
+else:
+    from hectr_b200 import Engine
+    eng = Engine(*params)
+    s = ref.poly_to_words(sk, 1)
+    WA = eng.genswk_words()
+    es, aws, sps = [], [], []
+    for k in range(NK):                                  # he_genswk's draws, in its order (he-kem.c:89,94)
+        sps.append(ref.poly_rot(s, k)[0].view(np.int64))
+        es.append(ref.sample_error())
+        aws.append(ref.poly_to_words(ref.sample_uniform_PqL(), WA))
+    dsk = eng.sk(s[0].view(np.int64))
+    np.save(out, eng.he_genswk(np.stack(aws), np.stack(es), np.stack(sps), dsk))
+    eng.close()
+"""
+
+
+def test_genswk_equals_he_genrk_itself(ref_available, tmp_path):
+    """hb_he_genswk against the keys he_genrk ITSELF emits for the same SUPERCOP stream: he_genswk is static and samples
+    internally, but the stream restarts with every process, so one fresh process runs he_keypair + he_genrk and another
+    he_keypair + the same draws by hand + the device."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for mode in ("ref", "dev"):
+        out = str(tmp_path / (mode + ".npy"))
+        r = subprocess.run([sys.executable, "-c", GENRK_CHILD % {"root": root}, mode, out], capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(np.load(out))
+    assert outs[0].shape == outs[1].shape
+    assert np.array_equal(outs[0], outs[1])
+
+
+@pytest.mark.parametrize("rot", [0, 1, 7, -1])
+def test_poly_rot_direct(deep, rot):
+    """hb_poly_rot against poly_rot / poly_conj (GPQHE/src/poly.c:263-283): rotation 0, 1, slots-1 and conjugation (rot < 0),
+    multiword coefficients including the negation edge -2^(k-1) and zero."""
+    ref, eng = deep["ref"], deep["eng"]
+    from conftest import random_ct_words
+    rng = np.random.default_rng(300 + rot)
+    L = ref.L
+    W, k = eng.words(L), eng.logq(L)
+    w = random_ct_words(rng, 1, W, eng.n, k)[0]           # [2][W][N]
+    w[0, :, 0] = 0
+    w[0, :, 1] = 0
+    w[0, W - 1, 1] = (1 << 64) - (1 << ((k - 1) % 64))     # -2^(k-1)
+    got = eng.poly_rot(w, rot)
+    for q in range(2):
+        if rot >= 0:
+            want = ref.poly_rot(w[q], rot)
+        else:
+            a, r = ref.alloc_poly(), ref.alloc_poly()
+            ref.words_to_poly(a, w[q])
+            ref.lib.poly_conj(C.byref(r), C.byref(a))
+            want = ref.poly_to_words(r, W)
+        assert np.array_equal(got[q], want), (rot, q)

@@ -185,8 +185,9 @@ def test_gemv_and_hempc(cfgA):
     assert np.array_equal(up.download()[0], ref.ct_to_words(up_ref)), "ctr_hempc ciphertext differs"
     out = eng.ctr_hempc_eval_host(Ka, Kb, w["xhat"], w["xr"], w["uhat"], w["ur"], keys, 2)
     assert np.array_equal(out[0], ref.ct_to_words(up_ref))
-    # decrypted control action vs the plaintext computation (CKKS error; tolerance 1e-7 on O(1) values)
-    dec = ref.decode(ref.dec(up_ref, sk))
+    # decrypted control action vs the plaintext computation (CKKS error; tolerance 1e-7 on O(1) values): the ENGINE's
+    # ciphertext goes through the reference's he_dec / he_dcd
+    dec = ref.decode(ref.dec(ref.ct_from_words(up.download()[0], up.l, nu=up.nu, B=up.B), sk))
     plain = vals["uhat"] - (Ka @ (vals["xhat"] - vals["xr"]) + Kb @ (vals["uhat"] - vals["ur"]))
     assert np.abs(dec - plain).max() < 1e-7
 
