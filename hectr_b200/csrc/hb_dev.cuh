@@ -27,7 +27,7 @@
 namespace cg = cooperative_groups;
 
 // streaming accesses (evict-first) for data touched once, so the twiddle tables stay in L1
-#ifdef HB_STREAM
+#if defined(HB_STREAM) && !defined(HB_NOSTREAM)
 #define HB_LD(p) __ldcs(p)
 #define HB_LDS2(p) __ldcs(p)
 #define HB_ST(p, v) __stcs(p, v)

@@ -31,11 +31,12 @@ def rand_ct(rng, batch, W, n, k):
 
 
 def rand_keys(eng, rng, nkeys):
-    primes = eng.primes()
-    keys = np.empty((nkeys, 2, eng.info.dimevk, eng.n), dtype=np.uint64)
-    for d in range(eng.info.dimevk):
-        keys[:, :, d, :] = rng.integers(0, int(primes[d]), size=(nkeys, 2, eng.n), dtype=np.uint64)
-    return keys
+    """REAL switching keys (hb_he_genswk from a sampled secret, as bench.py makes them): the bound-checked shortcuts of he_gemv
+    only apply to keys whose lift stays below P q_L / 2."""
+    import bench
+    secret = bench.make_secret(rng, eng.n)
+    rots = bench.gemv_rotations(eng.slots) if nkeys == eng.slots else list(range(nkeys))
+    return bench.make_rotation_keys(eng, rng, secret, rots)[:nkeys]
 
 
 def prof_report(eng):

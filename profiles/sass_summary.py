@@ -29,7 +29,12 @@ def main(path, top=12):
         d = dict(zip(hdr, row))
         src = d["Source"].strip()
         op = src.split()[0] if not src.startswith("@") else src.split()[1]
-        op = op.split(".")[0]
+        for pre in ("IMAD.WIDE", "IMAD.MOV", "IMAD.IADD", "IMAD.X", "IMAD.SHL", "IMAD.HI"):      # the IMAD family shares the fmaheavy pipe
+            if op.startswith(pre):
+                op = pre
+                break
+        else:
+            op = op.split(".")[0]
         n = int(d["Instructions Executed"] or 0)
         ops[kern][op] += n
         s = int(d["# Samples"] or 0)

@@ -11,6 +11,12 @@ import os
 import re
 import sys
 
+ALT = {   # metric name variants across ncu versions
+    "dram__throughput.avg.pct_of_peak_sustained_elapsed": ["gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"],
+    "smsp__issue_active.avg.pct_of_peak_sustained_elapsed": ["smsp__issue_active.avg.pct_of_peak_sustained_active", "sm__inst_issued.avg.pct_of_peak_sustained_active",
+                                                             "smsp__inst_issued.avg.pct_of_peak_sustained_active"],
+}
+
 COLS = [
     ("gpu__time_duration.sum", "time"),
     ("dram__bytes_read.sum", "dram rd"),
@@ -45,8 +51,8 @@ def main():
     ap.add_argument("--traffic", default=os.path.join(os.path.dirname(os.path.abspath(__file__)), "traffic.json"))
     a = ap.parse_args()
     traffic = {}
-    print("| kernel | " + " | ".join(c[1] for c in COLS) + " |")
-    print("|---|" + "---|" * len(COLS))
+    print("| kernel | " + " | ".join(c[1] for c in COLS) + " | top stall (warps per issue) |")
+    print("|---|" + "---|" * (len(COLS) + 1))
     for path in a.files:
         rows = list(csv.reader(open(path)))
         hdr, units = rows[0], rows[1]
@@ -62,6 +68,8 @@ def main():
             rd = wr = 0.0
             heavy = None
             for key, label in COLS:
+                if key not in idx:
+                    key = next((alt for alt in ALT.get(key, []) if alt in idx), key)
                 if key not in idx:
                     cells.append("-")
                     continue
@@ -84,12 +92,36 @@ def main():
                         cells.append(v)
                 except ValueError:
                     cells.append(v)
+            # first stall reason: the largest smsp__average_warps_issue_stalled_*_per_issue_active column
+            stall = None
+            for hname, i in idx.items():
+                m = re.match(r"smsp__average_warps?_(?:latency_)?issue_stalled_(.+?)_per_(?:issue_active|warp_active).*", hname)
+                if m and not m.group(1).endswith("not_issued"):
+                    try:
+                        val = float(r[i].replace(",", ""))
+                    except ValueError:
+                        continue
+                    if stall is None or val > stall[1]:
+                        stall = (m.group(1), val)
+            cells.append(f"{stall[0]} ({stall[1]:.2f})" if stall else "-")
             print(f"| `{name}` | " + " | ".join(cells) + " |")
             base = name.split("<")[0]
             traffic.setdefault(base, {})[str(a.batch)] = rd + wr
             if heavy is not None:
                 traffic[base]["fmaheavy_pct"] = heavy      # the pipe IMAD / IMAD.WIDE issue to: the binding unit of this path
-    json.dump(traffic, open(a.traffic, "w"), indent=1, sort_keys=True)
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    merged = {"sources_digest": bench.sources_digest(), "kernels": {}}
+    if os.path.exists(a.traffic):                      # keep captures of other kernels made from the same sources
+        try:
+            old = json.load(open(a.traffic))
+            if old.get("sources_digest") == merged["sources_digest"]:
+                merged["kernels"].update(old.get("kernels", {}))
+        except Exception:
+            pass
+    for kname, rec in traffic.items():
+        merged["kernels"].setdefault(kname, {}).update(rec)
+    json.dump(merged, open(a.traffic, "w"), indent=1, sort_keys=True)
     print(f"\n(traffic per launch written to {os.path.relpath(a.traffic)})", file=sys.stderr)
 
 

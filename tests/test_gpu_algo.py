@@ -247,8 +247,10 @@ def test_genswk_equals_he_genrk_itself(ref_available, tmp_path):
 def test_poly_rot_direct(deep, rot):
     """hb_poly_rot against poly_rot / poly_conj (GPQHE/src/poly.c:263-283): rotation 0, 1, slots-1 and conjugation (rot < 0),
     multiword coefficients including the negation edge -2^(k-1) and zero."""
-    ref, eng = deep["ref"], deep["eng"]
     from conftest import random_ct_words
+    from oracle.ref import Ref
+    eng = deep["eng"]
+    ref = Ref.get(*PARAMS)          # the reference keeps ONE global context: an earlier test of this module re-initialised it
     rng = np.random.default_rng(300 + rot)
     L = ref.L
     W, k = eng.words(L), eng.logq(L)

@@ -81,7 +81,8 @@ def test_config_E_4096_instances(cfgA, monkeypatch):
 
     def check(out, label):
         for s, b in enumerate(PROBES):
-            assert np.array_equal(out[b], want[s]), (label, "probe", b)
+            if b < out.shape[0]:
+                assert np.array_equal(out[b], want[s]), (label, "probe", b)
         assert np.array_equal(out, np.stack(want)[src[: out.shape[0]]]), (label, "copies")
 
     dev = [eng.ct(host[nm], l, nu=cts[0][nm].nu, B=cts[0][nm].B) for nm in names]
@@ -99,6 +100,81 @@ def test_config_E_4096_instances(cfgA, monkeypatch):
         d.free()
     check(eng.ctr_hempc_eval_host(Ka, Kb, *[host[nm] for nm in names], keys, l), "host pipeline 4096 (default chunks)")
     check(eng.ctr_hempc_eval_host(Ka, Kb, *[host[nm][:512] for nm in names], keys, l), "host pipeline 512 (8-GPU shard)")
+
+
+# (the tests that share the module's config-A reference context come first: the reference keeps ONE global context and
+# every Ref.get with other parameters re-initialises it)
+def test_summed_giant_steps_equal_one_tail_per_step(cfgA, monkeypatch):
+    """he_gemv's giant-step key switches share one reconstruction (k_ks_limb_sum / k_ks_finish_sum) and identically zero giant
+    steps are skipped; HB_GEMV_NOSUM / HB_GEMV_NOSKIP switch both off.  All variants must give the same words on 192 full-size
+    random ciphertexts per level (a few of the 3 M coefficients land inside the fixed-point margin and take ks_sum_slow), for a
+    dense matrix and for the hempc block matrices; the profile names which kernels ran."""
+    from hectr_b200 import Engine
+    eng, ref = cfgA["eng"], cfgA["ref"]
+    rk_arr = np.stack([ref.evk_to_array(cfgA["rk"][i]) for i in range(16)])
+    rng = np.random.default_rng(811)
+    Ka, Kb = hempc_gains(rng)
+    Ad = rng.standard_normal((16, 16)) + 1j * rng.standard_normal((16, 16))
+    monkeypatch.setenv("HB_GEMV_NOSUM", "1")
+    monkeypatch.setenv("HB_GEMV_NOSKIP", "1")
+    plain = Engine(*A_PARAMS)
+    monkeypatch.delenv("HB_GEMV_NOSUM")
+    monkeypatch.delenv("HB_GEMV_NOSKIP")
+
+    def names_of(e):
+        need = e.lib.hb_prof_report(e.ctx, None, 0)
+        buf = C.create_string_buffer(need + 1)
+        e.lib.hb_prof_report(e.ctx, buf, need + 1)
+        return json.loads(buf.value.decode())
+
+    try:
+        keys2 = plain.keys(rk_arr)
+        for l in (2, 1):
+            a = random_ct_words(rng, 192, eng.words(l), eng.n, eng.logq(l))
+            a[0, 1] = 0                                     # c1 = 0: every R is exactly 0, all decisions go to the slow path
+            for M in (Ad, Ka, Kb):
+                for e in (eng, plain):
+                    e.lib.hb_prof_reset(e.ctx)
+                    e.lib.hb_prof_enable(e.ctx, 1)
+                got = eng.he_gemv(M, eng.ct(a, l), cfgA["keys"])
+                want = plain.he_gemv(M, plain.ct(a, l), keys2)
+                pe, pp = names_of(eng), names_of(plain)
+                for e in (eng, plain):
+                    e.lib.hb_prof_enable(e.ctx, 0)
+                assert "k_ks_finish_sum" in pe and "k_ks_limb_sum" in pe, sorted(pe)
+                assert "k_ks_finish_sum" not in pp and "k_ct_sum_rs" in pp, sorted(pp)
+                assert got.l == want.l and got.nu == want.nu and got.B == want.B
+                assert np.array_equal(got.download(), want.download()), l
+                got.free()
+                want.free()
+        keys2.free()
+    finally:
+        plain.close()
+
+
+def test_synthetic_keys_keep_the_per_step_tails(cfgA):
+    """Uniform residues are not a switching key: their lift reaches P_D, the products wrap, and the sum of the wrapped
+    reconstructions is not the reconstruction of the sum.  hb_evk_upload records the bound of every key (k_lift_bits) and
+    he_gemv keeps one tail per giant step for such keys."""
+    eng = cfgA["eng"]
+    rng = np.random.default_rng(5)
+    primes = eng.primes()
+    fake = np.empty((16, 2, eng.info.dimevk, eng.n), dtype=np.uint64)
+    for d in range(eng.info.dimevk):
+        fake[:, :, d, :] = rng.integers(0, int(primes[d]), size=(16, 2, eng.n), dtype=np.uint64)
+    keys = eng.keys(fake)
+    A = rng.standard_normal((16, 16)) + 1j * rng.standard_normal((16, 16))
+    a = random_ct_words(rng, 2, eng.words(2), eng.n, eng.logq(2))
+    eng.lib.hb_prof_reset(eng.ctx)
+    eng.lib.hb_prof_enable(eng.ctx, 1)
+    eng.he_gemv(A, eng.ct(a, 2), keys).free()
+    need = eng.lib.hb_prof_report(eng.ctx, None, 0)
+    buf = C.create_string_buffer(need + 1)
+    eng.lib.hb_prof_report(eng.ctx, buf, need + 1)
+    eng.lib.hb_prof_enable(eng.ctx, 0)
+    names = json.loads(buf.value.decode())
+    assert "k_ks_finish_sum" not in names and "k_ct_sum_rs" in names, sorted(names)
+    keys.free()
 
 
 @pytest.mark.parametrize("slots,n1,n2", [(64, 8, 8), (128, 16, 8)])
@@ -207,79 +283,6 @@ def test_gemv_single_limb_plaintext_products(ref_available, P):
         keys.free()
     finally:
         eng.close()
-
-
-def test_summed_giant_steps_equal_one_tail_per_step(cfgA, monkeypatch):
-    """he_gemv's giant-step key switches share one reconstruction (k_ks_limb_sum / k_ks_finish_sum) and identically zero giant
-    steps are skipped; HB_GEMV_NOSUM / HB_GEMV_NOSKIP switch both off.  All variants must give the same words on 192 full-size
-    random ciphertexts per level (a few of the 3 M coefficients land inside the fixed-point margin and take ks_sum_slow), for a
-    dense matrix and for the hempc block matrices; the profile names which kernels ran."""
-    from hectr_b200 import Engine
-    eng, ref = cfgA["eng"], cfgA["ref"]
-    rk_arr = np.stack([ref.evk_to_array(cfgA["rk"][i]) for i in range(16)])
-    rng = np.random.default_rng(811)
-    Ka, Kb = hempc_gains(rng)
-    Ad = rng.standard_normal((16, 16)) + 1j * rng.standard_normal((16, 16))
-    monkeypatch.setenv("HB_GEMV_NOSUM", "1")
-    monkeypatch.setenv("HB_GEMV_NOSKIP", "1")
-    plain = Engine(*A_PARAMS)
-    monkeypatch.delenv("HB_GEMV_NOSUM")
-    monkeypatch.delenv("HB_GEMV_NOSKIP")
-
-    def names_of(e):
-        need = e.lib.hb_prof_report(e.ctx, None, 0)
-        buf = C.create_string_buffer(need + 1)
-        e.lib.hb_prof_report(e.ctx, buf, need + 1)
-        return json.loads(buf.value.decode())
-
-    try:
-        keys2 = plain.keys(rk_arr)
-        for l in (2, 1):
-            a = random_ct_words(rng, 192, eng.words(l), eng.n, eng.logq(l))
-            a[0, 1] = 0                                     # c1 = 0: every R is exactly 0, all decisions go to the slow path
-            for M in (Ad, Ka, Kb):
-                for e in (eng, plain):
-                    e.lib.hb_prof_reset(e.ctx)
-                    e.lib.hb_prof_enable(e.ctx, 1)
-                got = eng.he_gemv(M, eng.ct(a, l), cfgA["keys"])
-                want = plain.he_gemv(M, plain.ct(a, l), keys2)
-                pe, pp = names_of(eng), names_of(plain)
-                for e in (eng, plain):
-                    e.lib.hb_prof_enable(e.ctx, 0)
-                assert "k_ks_finish_sum" in pe and "k_ks_limb_sum" in pe, sorted(pe)
-                assert "k_ks_finish_sum" not in pp and "k_ct_sum_rs" in pp, sorted(pp)
-                assert got.l == want.l and got.nu == want.nu and got.B == want.B
-                assert np.array_equal(got.download(), want.download()), l
-                got.free()
-                want.free()
-        keys2.free()
-    finally:
-        plain.close()
-
-
-def test_synthetic_keys_keep_the_per_step_tails(cfgA):
-    """Uniform residues are not a switching key: their lift reaches P_D, the products wrap, and the sum of the wrapped
-    reconstructions is not the reconstruction of the sum.  hb_evk_upload records the bound of every key (k_lift_bits) and
-    he_gemv keeps one tail per giant step for such keys."""
-    eng = cfgA["eng"]
-    rng = np.random.default_rng(5)
-    primes = eng.primes()
-    fake = np.empty((16, 2, eng.info.dimevk, eng.n), dtype=np.uint64)
-    for d in range(eng.info.dimevk):
-        fake[:, :, d, :] = rng.integers(0, int(primes[d]), size=(16, 2, eng.n), dtype=np.uint64)
-    keys = eng.keys(fake)
-    A = rng.standard_normal((16, 16)) + 1j * rng.standard_normal((16, 16))
-    a = random_ct_words(rng, 2, eng.words(2), eng.n, eng.logq(2))
-    eng.lib.hb_prof_reset(eng.ctx)
-    eng.lib.hb_prof_enable(eng.ctx, 1)
-    eng.he_gemv(A, eng.ct(a, 2), keys).free()
-    need = eng.lib.hb_prof_report(eng.ctx, None, 0)
-    buf = C.create_string_buffer(need + 1)
-    eng.lib.hb_prof_report(eng.ctx, buf, need + 1)
-    eng.lib.hb_prof_enable(eng.ctx, 0)
-    names = json.loads(buf.value.decode())
-    assert "k_ks_finish_sum" not in names and "k_ct_sum_rs" in names, sorted(names)
-    keys.free()
 
 
 def test_config_C_full_level_chain(ref_available):
