@@ -100,6 +100,13 @@ struct hb_ctx {
   std::map<const void *, unsigned> evk_bits;
   uint64_t *keycheck_consts = nullptr;
   hbkg::Consts keycheck;
+  // hybrid-basis key switch (hb_dev32.cuh): every uploaded key also lives on the first hyb_mmax primes of the 30-bit basis
+  unsigned hyb_mmax = 0;            // 0: the hybrid path is not available for this context
+  uint32_t *hyb_q32 = nullptr;      // DEVICE [hyb_mmax] primes
+  std::map<const void *, uint32_t *> evk32;     // evk.p -> DEVICE key32[2][hyb_mmax][2][N] (multiplicand / quotient planes, times N^-1)
+  struct HybBasis { unsigned m = 0, Mbits = 0; ulonglong2 *dec59 = nullptr; uint2 *dec32 = nullptr; hbdev::KsHyb F; };
+  std::map<unsigned, HybBasis> hyb; // constants of M = P * Q_m, by m
+  bool no_hyb = false;              // HB_GEMV_NOHYB=1: every key-switch limb on the reference's 59-bit primes
   bool no_sum = false;              // HB_GEMV_NOSUM=1: one tail per giant step (A/B timing, tests)
   bool no_skip = false;             // HB_GEMV_NOSKIP=1: evaluate identically zero giant steps too
   std::vector<uint64_t> enc_host;   // [WC][N] scratch for hb_he_ecd / gemv plans
@@ -212,6 +219,43 @@ struct Launch32 {
            pthat, gstride, GM, n1, batch * 2, chat, c->dt32, D);
   }
 };
+template <int LOGN>
+struct LaunchHyb {
+  typedef hb32::Cfg32<LOGN> G;
+  static void ks_baby(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hb32::Baby32 &S, unsigned m, const uint2 *dec32, uint32_t *chat,
+                      size_t jstride, unsigned batch) {
+    want_smem(hb32::k32_ks_baby<LOGN>, 2 * G::SMEM_BYTES);
+    launch(c, "k32_ks_baby", hb32::k32_ks_baby<LOGN>, batch * m, G::THREADS, 2 * G::SMEM_BYTES, 1, src, bstride, W, S, m, c->hyb_mmax, dec32, 2 * c->ht.WC + 1, chat,
+           jstride, c->dt32);
+  }
+  static void ks_limb_sum(hb_ctx *c, const uint64_t *src, size_t bstride, size_t gstride, int W, const hb32::Groups32 &S, unsigned ng, unsigned m,
+                          const uint2 *dec32, uint32_t *chatX, unsigned batch) {
+    want_smem(hb32::k32_ks_limb_sum<LOGN>, 3 * G::SMEM_BYTES);
+    launch(c, "k32_ks_limb_sum", hb32::k32_ks_limb_sum<LOGN>, batch * m, G::THREADS, 3 * G::SMEM_BYTES, 1, src, bstride, gstride, W, S, ng, m, c->hyb_mmax, dec32,
+           2 * c->ht.WC + 1, chatX, c->dt32);
+  }
+  static void ntt_fwd_plain(hb_ctx *c, const uint32_t *in, uint32_t *out, size_t nlimbs, unsigned D) {
+    launch(c, "k32_ntt_fwd_plain", hb32::k32_ntt_fwd_plain<LOGN>, (unsigned)nlimbs, G::THREADS, G::SMEM_BYTES, 1, in, out, c->dt32, D);
+  }
+};
+static void do32_ks_baby(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hb32::Baby32 &S, unsigned m, const uint2 *dec32, uint32_t *chat,
+                         size_t jstride, unsigned batch) {
+#define X(L) case L: LaunchHyb<L>::ks_baby(c, src, bstride, W, S, m, dec32, chat, jstride, batch); break;
+  switch (c->ht.logn) { HB_LOGN32_CASES(X) default: hb_die("logn=%u has no 30-bit path", c->ht.logn); }
+#undef X
+}
+static void do32_ks_limb_sum(hb_ctx *c, const uint64_t *src, size_t bstride, size_t gstride, int W, const hb32::Groups32 &S, unsigned ng, unsigned m,
+                             const uint2 *dec32, uint32_t *chatX, unsigned batch) {
+#define X(L) case L: LaunchHyb<L>::ks_limb_sum(c, src, bstride, gstride, W, S, ng, m, dec32, chatX, batch); break;
+  switch (c->ht.logn) { HB_LOGN32_CASES(X) default: hb_die("logn=%u has no 30-bit path", c->ht.logn); }
+#undef X
+}
+static void do32_ntt_fwd_plain(hb_ctx *c, const uint32_t *in, uint32_t *out, size_t nlimbs, unsigned D) {
+#define X(L) case L: LaunchHyb<L>::ntt_fwd_plain(c, in, out, nlimbs, D); break;
+  switch (c->ht.logn) { HB_LOGN32_CASES(X) default: hb_die("logn=%u has no 30-bit path", c->ht.logn); }
+#undef X
+}
+
 static void do32_poly_ntt(hb_ctx *c, const uint64_t *src, size_t stride, int W, uint32_t *out, unsigned D, size_t npoly, bool canon) {
 #define X(L) case L: Launch32<L>::poly_ntt(c, src, stride, W, out, D, npoly, canon); break;
   switch (c->ht.logn) { HB_LOGN32_CASES(X) default: hb_die("logn=%u has no 30-bit path", c->ht.logn); }
@@ -246,10 +290,10 @@ struct Launch {
     launch(c, "k_poly_ntt", hbdev::k_poly_ntt<LOGN>, (unsigned)(npoly * D * G::C), G::THREADS, G::SMEM_BYTES, G::C, src, stride, W, out, c->dt, D);
   }
   static void ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hbdev::KsGroups &S,
-                      unsigned key_limbs, uint64_t *chat, unsigned D, unsigned batch, unsigned d0, unsigned Dn) {
+                      unsigned key_limbs, uint64_t *chat, unsigned D, unsigned batch, unsigned d0, unsigned Dn, const ulonglong2 *dec) {
     want_smem(hbdev::k_ks_limb<LOGN>, 2 * G::SMEM_BYTES);
     launch(c, "k_ks_limb", hbdev::k_ks_limb<LOGN>, (unsigned)((size_t)batch * Dn * G::C), G::THREADS, 2 * G::SMEM_BYTES, G::C, src, bstride, W,
-           S, key_limbs, chat, c->dt, D, d0, Dn);
+           S, key_limbs, chat, c->dt, D, d0, Dn, dec);
   }
   static void ks_limb_sum(hb_ctx *c, const uint64_t *src, size_t bstride, size_t gstride, int W, const hbdev::KsGroups &S, unsigned ng,
                           unsigned key_limbs, uint64_t *chatX, unsigned D, unsigned batch, unsigned d0, unsigned Dn) {
@@ -262,10 +306,10 @@ struct Launch {
     }
   }
   static void ks_baby(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hbdev::BabySet &S, uint64_t *chat, size_t jstride,
-                      unsigned D, unsigned batch) {
+                      unsigned D, unsigned batch, unsigned Dn, const ulonglong2 *dec) {
     want_smem(hbdev::k_ks_baby<LOGN>, 2 * G::SMEM_BYTES);
-    launch(c, "k_ks_baby", hbdev::k_ks_baby<LOGN>, (unsigned)((size_t)batch * D * G::C), G::THREADS, 2 * G::SMEM_BYTES, G::C, src, bstride, W,
-           S, c->ht.dimevk, chat, jstride, c->dt, D);
+    launch(c, "k_ks_baby", hbdev::k_ks_baby<LOGN>, (unsigned)((size_t)batch * Dn * G::C), G::THREADS, 2 * G::SMEM_BYTES, G::C, src, bstride, W,
+           S, c->ht.dimevk, chat, jstride, c->dt, D, Dn, dec);
   }
   static void mulpt_limb(hb_ctx *c, const uint64_t *ct, size_t poly_stride, int W, const ulonglong2 *pthat, uint64_t *chat, unsigned D,
                          size_t npoly) {
@@ -304,9 +348,9 @@ static void do_poly_ntt(hb_ctx *c, const uint64_t *src, size_t stride, int W, ui
 // batch = instances in the launch (all groups); S.gbatch instances per group
 // limbs [d0, d0 + Dn) of a D-limb key switch (Dn = 0: all of them), written compactly as chat[b][h][Dn][N]
 static void do_ks_limb_g(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hbdev::KsGroups &S, unsigned key_limbs,
-                         uint64_t *chat, unsigned D, unsigned batch, unsigned d0 = 0, unsigned Dn = 0) {
+                         uint64_t *chat, unsigned D, unsigned batch, unsigned d0 = 0, unsigned Dn = 0, const ulonglong2 *dec = nullptr) {
   if (!Dn) Dn = D;
-#define X(L) case L: Launch<L>::ks_limb(c, src, bstride, W, S, key_limbs, chat, D, batch, d0, Dn); break;
+#define X(L) case L: Launch<L>::ks_limb(c, src, bstride, W, S, key_limbs, chat, D, batch, d0, Dn, dec); break;
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
 }
@@ -324,8 +368,9 @@ static void do_ks_limb(hb_ctx *c, const uint64_t *src, size_t bstride, int W, un
   do_ks_limb_g(c, src, bstride, W, S, key_limbs, chat, D, batch);
 }
 static void do_ks_baby(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hbdev::BabySet &S, uint64_t *chat, size_t jstride,
-                       unsigned D, unsigned batch) {
-#define X(L) case L: Launch<L>::ks_baby(c, src, bstride, W, S, chat, jstride, D, batch); break;
+                       unsigned D, unsigned batch, unsigned Dn = 0, const ulonglong2 *dec = nullptr) {
+  if (!Dn) Dn = D;
+#define X(L) case L: Launch<L>::ks_baby(c, src, bstride, W, S, chat, jstride, D, batch, Dn, dec); break;
   switch (c->ht.logn) { HB_LOGN_CASES(X) default: hb_die("logn=%u is not built into this library", c->ht.logn); }
 #undef X
 }
@@ -464,6 +509,39 @@ static bool do_ks_finish_sum(hb_ctx *c, const uint64_t *chatP, size_t chatP_gstr
   return false;
 }
 
+// hybrid-basis tails (k_ks_finish_hyb, k_ks_finish_sum_hyb); probe: is this (dim, m) pair instantiated?
+#define HB_HYB_PAIRS(X) X(3, 8) X(3, 7) X(3, 9) X(2, 4) X(2, 5) X(2, 6)
+static bool do_ks_finish_hyb(hb_ctx *c, const uint64_t *chat59, const uint32_t *chat32, const hbdev::KsHyb *F, const uint64_t *add0,
+                             const uint64_t *add1, size_t add_bstride, int Wadd, const hbdev::TailGroups &TG, uint64_t *out, int Wout, int k,
+                             unsigned batch, unsigned dim, unsigned m) {
+  const unsigned threads = 128;
+  const unsigned grid = (unsigned)(((size_t)batch * 2 * c->ht.N + threads - 1) / threads);
+#define X(DD, MM)                                                                                                                \
+  if (dim == DD && m == MM) {                                                                                                    \
+    if (F) launch(c, "k_ks_finish_hyb", hbdev::k_ks_finish_hyb<4, DD, MM>, grid, threads, 0, 1, chat59, chat32, *F, add0, add1, add_bstride, \
+                  Wadd, TG, out, Wout, k, c->dt, batch);                                                                         \
+    return true;                                                                                                                 \
+  }
+  HB_HYB_PAIRS(X)
+#undef X
+  return false;
+}
+static bool do_ks_finish_sum_hyb(hb_ctx *c, const uint64_t *chatP, size_t chatP_gstride, const uint32_t *chatX32, const hbdev::KsHyb *F,
+                                 const uint64_t *add0, size_t add_gstride, size_t add_bstride, int Wadd, const hbdev::SumGroups &SG, uint64_t *out,
+                                 int Wout, int k, int shift, int kout, unsigned batch, unsigned dim, unsigned m) {
+  const unsigned threads = 128;
+  const unsigned grid = (unsigned)(((size_t)batch * 2 * c->ht.N + threads - 1) / threads);
+#define X(DD, MM)                                                                                                                \
+  if (dim == DD && m == MM) {                                                                                                    \
+    if (F) launch(c, "k_ks_finish_sum_hyb", hbdev::k_ks_finish_sum_hyb<4, DD, MM>, grid, threads, 0, 1, chatP, chatP_gstride, chatX32, *F, add0, \
+                  add_gstride, add_bstride, Wadd, SG, out, Wout, k, shift, kout, c->dt, batch);                                  \
+    return true;                                                                                                                 \
+  }
+  HB_HYB_PAIRS(X)
+#undef X
+  return false;
+}
+
 static void do_ks_finish_g(hb_ctx *c, const uint64_t *chat, unsigned D, const uint64_t *add0, const uint64_t *add1,
                            size_t add_bstride, int Wadd, const hbdev::TailGroups &TG, uint64_t *out, int Wout, int k, unsigned batch) {
   const unsigned threads = 128;
@@ -569,6 +647,8 @@ extern "C" hb_ctx *hb_ctx_create(unsigned logn, unsigned logq, unsigned slots, u
     ctx->exact_tail = e && *e && *e != '0';
     e = getenv("HB_GEMV_NOHOIST");
     ctx->no_hoist = e && *e && *e != '0';
+    e = getenv("HB_GEMV_NOHYB");
+    ctx->no_hyb = e && *e && *e != '0';
     e = getenv("HB_GEMV_NOSUM");
     ctx->no_sum = e && *e && *e != '0';
     e = getenv("HB_GEMV_NOSKIP");
@@ -597,6 +677,18 @@ extern "C" hb_ctx *hb_ctx_create(unsigned logn, unsigned logq, unsigned slots, u
       d.crt_Q = upload_vec(ctx, g.crt_Q);
       d.N = g.N; d.logn = g.logn; d.nprimes = g.nprimes; d.WC = g.WC; d.ndig = g.ndig;
       ctx->have32 = true;
+      // Hybrid key switch: limbs needed for the largest product this context can ask for (top level, 8 summed giant steps,
+      // a key of P q_L / 2): |x| < 2^bound must stay below M / 8, M = P Q_m >= 2^(nbitsP + qbits[m] - 2).
+      const unsigned bound = 3 + h.logn + (h.logq_l[h.L] - 1) + (h.nbitsPqL - 1);
+      unsigned m = 0;
+      for (unsigned t = 1; t <= g.nprimes; t++)
+        if (h.nbitsP + g.qbits[t] - 2 >= bound + 3) { m = t; break; }
+      if (m && m <= HB_HYB_MAX32 && h.dim <= 4 && h.dim < h.dimevk && h.WP <= 4 && !ctx->no_hyb) {
+        ctx->hyb_mmax = m;
+        std::vector<uint32_t> q(m);
+        for (unsigned t = 0; t < m; t++) q[t] = g.primes[t].p;
+        ctx->hyb_q32 = upload_vec(ctx, q);
+      }
     }
   }
   return ctx;
@@ -619,6 +711,8 @@ extern "C" void hb_ctx_destroy(hb_ctx *ctx) { use_device(ctx);
   cudaFree(ctx->wsD);
   cudaFree(ctx->keycheck_consts);
   for (auto &kv : ctx->perms) cudaFree(kv.second);
+  for (auto &kv : ctx->evk32) cudaFree(kv.second);
+  for (auto &kv : ctx->hyb) { cudaFree(kv.second.dec59); cudaFree(kv.second.dec32); }
   if (ctx->up_stream) {
     cudaStreamDestroy(ctx->up_stream);
     cudaStreamDestroy(ctx->down_stream);
@@ -871,8 +965,9 @@ extern "C" void hb_pt_upload(hb_ctx *ctx, hb_pt *pt, const uint64_t *host, doubl
   CUDA_OK(cudaMemcpyAsync(pt->words, host, (size_t)ctx->ht.WC * ctx->ht.N * 8, cudaMemcpyHostToDevice, ctx->stream));
   CUDA_OK(cudaStreamSynchronize(ctx->stream));
 }
-// largest |coefficient| (bit length) of a key given as canonical-or-[0,p] transform limbs raw[2][dimevk][N] on the device
-static unsigned key_lift_bits(hb_ctx *ctx, const uint64_t *raw) {
+// largest |coefficient| (bit length) of a key given as canonical-or-[0,p] transform limbs raw[2][dimevk][N] on the device.
+// key32_out (hybrid path available): the same key on the 30-bit primes, key32[2][hyb_mmax][2][N] planes, times N^-1.
+static unsigned key_lift_bits(hb_ctx *ctx, const uint64_t *raw, uint32_t **key32_out) {
   const hb::HostTables &h = ctx->ht;
   const unsigned D = h.dimevk;
   const size_t N = h.N;
@@ -902,12 +997,108 @@ static unsigned key_lift_bits(hb_ctx *ctx, const uint64_t *raw) {
   unsigned *dmax = (unsigned *)(coef + limbs);
   CUDA_OK(cudaMemsetAsync(dmax, 0, 8, ctx->stream));
   do_ntt_inv(ctx, raw, coef, (size_t)2 * D, 0, D);
-  launch(ctx, "k_lift_bits", hbkg::k_lift_bits, (unsigned)((2 * N + 127) / 128), 128, 0, 1, (const uint64_t *)coef, ctx->keycheck, 2u, dmax);
+  const unsigned m = key32_out ? ctx->hyb_mmax : 0;
+  uint32_t *res32 = nullptr, *hat32 = nullptr;
+  if (m) {
+    res32 = (uint32_t *)hb_dev_alloc(ctx, (size_t)2 * m * N * 4);
+    hat32 = (uint32_t *)hb_dev_alloc(ctx, (size_t)2 * m * N * 4);
+  }
+  launch(ctx, "k_lift_bits", hbkg::k_lift_bits, (unsigned)((2 * N + 127) / 128), 128, 0, 1, (const uint64_t *)coef, ctx->keycheck, 2u, dmax,
+         (const uint32_t *)ctx->hyb_q32, m, res32);
+  if (m) {
+    uint32_t *key32 = (uint32_t *)hb_dev_alloc(ctx, (size_t)2 * m * 2 * N * 4);
+    do32_ntt_fwd_plain(ctx, res32, hat32, (size_t)2 * m, m);
+    const size_t total = (size_t)2 * m * N;
+    launch(ctx, "k32_shoup_prep", hb32::k32_shoup_prep, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint32_t *)hat32, key32, ctx->dt32, m, (size_t)2 * m, 0u);
+    *key32_out = key32;
+  }
   unsigned bits = 0;
   CUDA_OK(cudaMemcpyAsync(&bits, dmax, 4, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_OK(cudaStreamSynchronize(ctx->stream));
   CUDA_OK(cudaFree(coef));
+  if (res32) { CUDA_OK(cudaFree(res32)); CUDA_OK(cudaFree(hat32)); }
   return bits;
+}
+
+// constants of the hybrid basis M = P * Q_m (hb_dev32.cuh), built once per m
+static const hb_ctx::HybBasis &hyb_basis(hb_ctx *ctx, unsigned m) {
+  auto it = ctx->hyb.find(m);
+  if (it != ctx->hyb.end()) return it->second;
+  const hb::HostTables &h = ctx->ht;
+  const hb::HostTables32 &g = ctx->ht32;
+  hb_ctx::HybBasis B;
+  B.m = m;
+  hb::BigU Q(1);
+  for (unsigned i = 0; i < m; i++) Q = Q.mul_u64(g.primes[i].p);
+  const hb::BigU &P = h.Pfull[h.dim];
+  const hb::BigU M = hb::BigU::mul(P, Q);
+  B.Mbits = M.bits();
+  hbdev::KsHyb &F = B.F;
+  memset(&F, 0, sizeof F);
+  F.dim = h.dim; F.m = m;
+  typedef unsigned __int128 u128;
+  u128 pinv = 0;
+  for (unsigned w = 0; w < 2 && w < h.WC; w++) pinv |= (u128)h.ks_Pinv[w] << (64 * w);
+  auto fold2 = [&](const hb::BigU &v, uint64_t (&o)[2]) {
+    const std::vector<uint64_t> lo = v.low(2);
+    const u128 x = ((((u128)lo[1]) << 64) | lo[0]) * pinv;
+    o[0] = (uint64_t)x; o[1] = (uint64_t)(x >> 64);
+  };
+  std::vector<uint64_t> dec59((size_t)h.dim * (h.WC + 1) * 2), ztab((size_t)h.dim * 2);
+  for (unsigned e = 0; e < h.dim; e++) {
+    const uint64_t pe = h.primes[e].p;
+    const hb::BigU Mhat = M.divmod_u64(pe, nullptr);
+    const uint64_t mh = Mhat.mod_u64(pe), inv = hb::powmod(mh, pe - 2, pe);
+    F.p[e] = pe; F.mu[e] = h.primes[e].mu;
+    fold2(Mhat, F.phat[e]);
+    for (unsigned w = 0; w <= h.WC; w++) {
+      const uint64_t c = hb::mulmod(h.pow64[(size_t)e * (h.WC + 1) + w], inv, pe);
+      dec59[((size_t)e * (h.WC + 1) + w) * 2] = c;
+      dec59[((size_t)e * (h.WC + 1) + w) * 2 + 1] = hb::shoup_quotient(c, pe);
+    }
+    // y_e = a_e (M/p_e)^-1  ->  z_e = a_e (P/p_e)^-1 = y_e (M/p_e) (P/p_e)^-1
+    const uint64_t z = hb::mulmod(h.ks_inv[e], mh, pe);
+    F.kinv[e] = z; F.kinvq[e] = hb::shoup_quotient(z, pe);
+    ztab[2 * e] = z; ztab[2 * e + 1] = F.kinvq[e];
+    hb::BigU kph;
+    kph.w.assign(h.ks_phat.begin() + (size_t)e * h.WP, h.ks_phat.begin() + (size_t)(e + 1) * h.WP);
+    kph.trim();
+    fold2(kph, F.kphat[e]);
+  }
+  fold2(P, F.kP);
+  fold2(M, F.M);
+  const unsigned nd = 2 * h.WC + 1;
+  std::vector<uint32_t> dec32((size_t)m * nd * 2);
+  for (unsigned i = 0; i < m; i++) {
+    const uint64_t qi = g.primes[i].p;
+    const hb::BigU Qhat = M.divmod_u64(qi, nullptr);
+    const uint64_t inv = hb::powmod(Qhat.mod_u64(qi), qi - 2, qi);
+    F.q[i] = (uint32_t)qi; F.mu32[i] = g.primes[i].mu;
+    fold2(Qhat, F.qhat[i]);
+    for (unsigned w = 0; w < nd; w++) {
+      const uint64_t c = hb::mulmod(g.pow32[((size_t)i * (g.ndig + 1) + w) * 2], inv, qi);
+      dec32[((size_t)i * nd + w) * 2] = (uint32_t)c;
+      dec32[((size_t)i * nd + w) * 2 + 1] = hb::shoup_quotient32((uint32_t)c, (uint32_t)qi);
+    }
+  }
+  // one allocation: dec59 | ztab, and dec32
+  std::vector<uint64_t> pack(dec59);
+  pack.insert(pack.end(), ztab.begin(), ztab.end());
+  B.dec59 = (ulonglong2 *)hb_dev_alloc(ctx, pack.size() * 8);
+  CUDA_OK(cudaMemcpyAsync(B.dec59, pack.data(), pack.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+  B.dec32 = (uint2 *)hb_dev_alloc(ctx, dec32.size() * 4);
+  CUDA_OK(cudaMemcpyAsync(B.dec32, dec32.data(), dec32.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  F.ztab = B.dec59 + (size_t)h.dim * (h.WC + 1);
+  return ctx->hyb.emplace(m, B).first->second;
+}
+
+// 30-bit limbs needed so that |x| < 2^bound_bits stays below M / 8 (0: not available)
+static unsigned hyb_limbs_for(const hb_ctx *ctx, unsigned bound_bits) {
+  if (!ctx->hyb_mmax) return 0;
+  for (unsigned m = 1; m <= ctx->hyb_mmax; m++)
+    if (ctx->ht.nbitsP + ctx->ht32.qbits[m] - 2 >= bound_bits + 3) return m;
+  return 0;
 }
 
 extern "C" void hb_evk_upload(hb_ctx *ctx, hb_evk *evk, const uint64_t *p0, const uint64_t *p1) { use_device(ctx);
@@ -919,11 +1110,15 @@ extern "C" void hb_evk_upload(hb_ctx *ctx, hb_evk *evk, const uint64_t *p0, cons
   CUDA_OK(cudaMemcpyAsync(raw, p0, half * 8, cudaMemcpyHostToDevice, ctx->stream));
   CUDA_OK(cudaMemcpyAsync(raw + half, p1, half * 8, cudaMemcpyHostToDevice, ctx->stream));
   do_shoup_prep(ctx, raw, (ulonglong2 *)evk->p, ctx->ht.dimevk, (size_t)2 * ctx->ht.dimevk, 1, 0);   // key * N^-1
-  ctx->evk_bits[evk->p] = key_lift_bits(ctx, raw);
+  uint32_t *key32 = nullptr;
+  ctx->evk_bits[evk->p] = key_lift_bits(ctx, raw, ctx->hyb_mmax ? &key32 : nullptr);
+  if (key32) ctx->evk32[evk->p] = key32;
   hb_dev_free(ctx, raw);   // synchronises
 }
 extern "C" void hb_evk_free(hb_ctx *ctx, hb_evk *evk) { use_device(ctx);
   ctx->evk_bits.erase(evk->p);
+  auto it32 = ctx->evk32.find(evk->p);
+  if (it32 != ctx->evk32.end()) { hb_dev_free(ctx, it32->second); ctx->evk32.erase(it32); }
   hb_dev_free(ctx, evk->p);
   evk->p = nullptr;
 }
@@ -1341,21 +1536,54 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
   hbdev::TailGroups TB;
   memset(&TB, 0, sizeof TB);
   TB.gbatch = batch; TB.add_shared = 1;
+  // Hybrid basis (hb_dev32.cuh): the limbs that do not divide P move to 30-bit primes when every key involved has its 30-bit
+  // form and the product provably fits:  |x| < 2^(logn + k - 1 + keybits) <= M / 8.
+  const unsigned wk = (unsigned)(k + 63) / 64;
+  auto hybrid_m = [&](unsigned lg_terms, const std::vector<unsigned> &rots) -> unsigned {
+    if (ctx->no_hyb || !ctx->hyb_mmax || W > 2 || wk > 2 || ctx->exact_tail || h.dim >= Dk) return 0;
+    unsigned kb = 0;
+    for (unsigned r : rots) {
+      auto ib = ctx->evk_bits.find(rk[r].p);
+      if (ib == ctx->evk_bits.end() || ib->second == ~0u || !ctx->evk32.count(rk[r].p)) return 0;
+      kb = std::max(kb, ib->second);
+    }
+    const unsigned m = hyb_limbs_for(ctx, lg_terms + h.logn + (unsigned)(k - 1) + kb) ? ctx->hyb_mmax : 0;   // one limb count per context
+    if (!m || !do_ks_finish_hyb(ctx, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, hbdev::TailGroups(), nullptr, 0, 0, 0, h.dim, m)) return 0;
+    if ((size_t)h.dim * 8 + (size_t)m * 4 > (size_t)Dk * 8) return 0;          // the shared key-switch workspace holds Dk words per coefficient
+    return m;
+  };
+  std::vector<unsigned> baby_rots;
+  for (unsigned j = 0; j < n1; j++) {
+    if (!rk[j].p) hb_die("hb_he_gemv: rotation key %u is not loaded", j);
+    baby_rots.push_back(j);
+    TB.ginv[j] = pow5_inv_mod_2n(ctx, j);
+  }
+  const unsigned mb = hybrid_m(0, baby_rots);
+  const hb_ctx::HybBasis *HB = mb ? &hyb_basis(ctx, mb) : nullptr;
+  const size_t cstride59 = (size_t)batch * 2 * h.dim * N, jstride32h = (size_t)batch * 2 * mb * N;
+  uint32_t *chat32b = (uint32_t *)(chat + (size_t)n1 * cstride59);             // after the n1 batches of P-limbs
   for (unsigned j0 = 0; j0 < n1; j0 += 4) {
     hbdev::BabySet S;
+    hb32::Baby32 S32;
     memset(&S, 0, sizeof S);
-    S.nj = n1 - j0 < 4 ? n1 - j0 : 4;
+    memset(&S32, 0, sizeof S32);
+    S.nj = S32.nj = n1 - j0 < 4 ? n1 - j0 : 4;
     for (unsigned t = 0; t < S.nj; t++) {
       const unsigned j = j0 + t;
-      if (!rk[j].p) hb_die("hb_he_gemv: rotation key %u is not loaded", j);
-      TB.ginv[j] = pow5_inv_mod_2n(ctx, j);
       S.evk[t] = (const ulonglong2 *)rk[j].p;
-      S.perm[t] = perm_table(ctx, inv_odd_mod_2n(ctx, TB.ginv[j]));
+      S.perm[t] = S32.perm[t] = perm_table(ctx, inv_odd_mod_2n(ctx, TB.ginv[j]));
+      if (mb) S32.key[t] = ctx->evk32[rk[j].p];
     }
-    do_ks_baby(ctx, ct->words + polyw, bstride, W, S, chat + (size_t)j0 * cstride, cstride, Dk, batch);
+    if (mb) {
+      do_ks_baby(ctx, ct->words + polyw, bstride, W, S, chat + (size_t)j0 * cstride59, cstride59, Dk, batch, h.dim, HB->dec59);
+      do32_ks_baby(ctx, ct->words + polyw, bstride, W, S32, mb, HB->dec32, chat32b + (size_t)j0 * jstride32h, jstride32h, batch);
+    } else {
+      do_ks_baby(ctx, ct->words + polyw, bstride, W, S, chat + (size_t)j0 * cstride, cstride, Dk, batch);
+    }
   }
   //    tails of all n1 rotations: c0 = rdiv(.) + sigma_j(ct.c0), c1 = rdiv(.)   (he-automorphism.c:68-76)
-  do_ks_finish_g(ctx, chat, Dk, ct->words, nullptr, bstride, W, TB, cts, W, k, n1 * batch);
+  if (mb) do_ks_finish_hyb(ctx, chat, chat32b, &HB->F, ct->words, nullptr, bstride, W, TB, cts, W, k, n1 * batch, h.dim, mb);
+  else do_ks_finish_g(ctx, chat, Dk, ct->words, nullptr, bstride, W, TB, cts, W, k, n1 * batch);
   // giant steps actually evaluated: all of them, or only those with a non-zero diagonal (GemvPlan::giant_nz)
   hbdev::GroupMap GM;
   memset(&GM, 0, sizeof GM);
@@ -1432,11 +1660,25 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
       const size_t pstride = (size_t)batch * 2 * dim * N;          // limbs of the primes of P, per giant step
       uint64_t *chatP = chat, *chatX = chat + (size_t)ngs * pstride;   // fits: ngs (dim + Dx) <= ng Dk
       if ((size_t)ngs * pstride + (size_t)batch * 2 * Dx * N > (size_t)ng * cstride) hb_die("internal: key-switch workspace too small");
-      do_ks_limb_g(ctx, inner + polyw, bstride, W, SG, h.dimevk, chatP, Dk, ngs * batch, 0, dim);
-      do_ks_limb_sum(ctx, inner + polyw, bstride, (size_t)batch * bstride, W, SG, ngs, h.dimevk, chatX, Dk, batch, dim, Dx);
+      std::vector<unsigned> giant_rots;
+      for (unsigned s2 = 0; s2 < ngs; s2++) giant_rots.push_back(GM.idx[s2] * n1);
+      const unsigned mg = hybrid_m(lg, giant_rots);
       dst->nu /= Delta;
       dst->B = dst->B / Delta + Brs;
       dst->l = l - 1;
+      if (mg) {
+        const hb_ctx::HybBasis &HG = hyb_basis(ctx, mg);
+        hb32::Groups32 S32;
+        memset(&S32, 0, sizeof S32);
+        for (unsigned s2 = 0; s2 < ngs; s2++) { S32.key[s2] = ctx->evk32[rk[giant_rots[s2]].p]; S32.g[s2] = SG.g[s2]; }
+        do_ks_limb_g(ctx, inner + polyw, bstride, W, SG, h.dimevk, chatP, Dk, ngs * batch, 0, dim, HG.dec59);
+        do32_ks_limb_sum(ctx, inner + polyw, bstride, (size_t)batch * bstride, W, S32, ngs, mg, HG.dec32, (uint32_t *)chatX, batch);
+        do_ks_finish_sum_hyb(ctx, chatP, pstride, (const uint32_t *)chatX, &HG.F, inner, (size_t)batch * bstride, bstride, W, SS, dst->words, Wout, k,
+                             (int)h.logDelta, kout, batch, dim, mg);
+        return;
+      }
+      do_ks_limb_g(ctx, inner + polyw, bstride, W, SG, h.dimevk, chatP, Dk, ngs * batch, 0, dim);
+      do_ks_limb_sum(ctx, inner + polyw, bstride, (size_t)batch * bstride, W, SG, ngs, h.dimevk, chatX, Dk, batch, dim, Dx);
       do_ks_finish_sum(ctx, chatP, pstride, chatX, Dk, inner, (size_t)batch * bstride, bstride, W, SS, dst->words, Wout, k, (int)h.logDelta, kout,
                        batch, false);
       return;

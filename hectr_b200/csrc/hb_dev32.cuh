@@ -210,10 +210,12 @@ __global__ void k32_shoup_prep(const uint32_t *__restrict__ in, uint32_t *__rest
   if (gid >= nlimbs * T.N) return;
   const unsigned d = (unsigned)((gid / T.N) % D);
   const Prime32 pc = T.primes[d];
-  const uint2 inv = T.crt_inv[(size_t)Dw * T.nprimes + d];
   uint32_t w = in[gid];
   w = csub32(shoup32(w, pc.ninv, pc.ninv_q, pc.p), pc.p);
-  w = csub32(shoup32(w, inv.x, inv.y, pc.p), pc.p);
+  if (Dw) {                                                 // Dw == 0: times N^-1 only (evaluation keys on the hybrid basis)
+    const uint2 inv = T.crt_inv[(size_t)Dw * T.nprimes + d];
+    w = csub32(shoup32(w, inv.x, inv.y, pc.p), pc.p);
+  }
   const size_t limb = gid / T.N, i = gid % T.N;
   out[(2 * limb) * T.N + i] = w;
   out[(2 * limb + 1) * T.N + i] = (uint32_t)((((uint64_t)w) << 32) / pc.p);
@@ -495,6 +497,154 @@ k32_recon_smod4(const uint32_t *__restrict__ chat, uint64_t *__restrict__ out, i
       dst[0] = make_ulonglong2(x[0][w], x[1][w]);
       dst[1] = make_ulonglong2(x[2][w], x[3][w]);
     }
+}
+
+}  // namespace hb32
+
+namespace hb32 {
+
+// ===============================================================================================================
+// Key switching on a HYBRID basis (round 2).  A key switch needs the exact product x = sigma(c1) (*) key twice: modulo
+// the primes of P, to rebuild R = x mod P exactly (he-automorphism.c:68-76: rdiv by P), and as an integer modulo 2^k.
+// The reference takes D = 7 of its 59-bit primes so that x (below 2^406 at config A) does not wrap P_D.  Only the dim = 3
+// primes of P are dictated by the result; for the rest ANY primes whose product, times P, exceeds 2 |x| reconstruct the
+// same integer.  Here the rest are 30-bit primes of the engine's own basis (hb_tables32.hpp): a Harvey butterfly on them
+// costs a quarter of a 59-bit one, and twice as many limbs are needed.  x fits because a switching key is smod(., P q_L)
+// (he-kem.c:97-102) -- the bound is MEASURED per key at hb_evk_upload (hbkg::k_lift_convert), which also produces the key's
+// residues on the 30-bit primes.  Basis M = P * Q_m; limbs arrive at the tail pre-weighted by (M/prime)^-1.
+//
+// The kernels below are the 30-bit halves; the limbs of P stay on k_ks_baby / k_ks_limb (hb_kernels.cuh) with a limb range.
+// Keys: key32[h][i][2][N] u32 per key (multiplicand plane, quotient plane), times N^-1, transform domain.
+// dec32[i][2 W + 1]: digit weights 2^(32 j) (M/q_i)^-1 mod q_i (the CRT weight rides on the decomposition).
+// ===============================================================================================================
+struct Baby32 {
+  const uint32_t *key[4];        // rk[j] on the 30-bit primes
+  const uint16_t *perm[4];       // perm_{g_j}[N] (hb_kernels.cuh BabySet)
+  unsigned nj;
+};
+struct Groups32 {
+  const uint32_t *key[HB_MAX_GROUPS];
+  unsigned g[HB_MAX_GROUPS];     // automorphism exponent of each giant step
+};
+
+// residue (below 3q) of the signed W-word coefficient, times the weight folded into `pw`
+__device__ __forceinline__ uint32_t decompose32(const uint64_t *__restrict__ poly, int i, int W, unsigned N, const uint2 *__restrict__ pw,
+                                                uint32_t p, uint32_t p2, uint32_t negW) {
+  uint32_t acc = 0;
+  uint64_t top = 0;
+  for (int w = 0; w < W; w++) {
+    top = HB_LD(&poly[(size_t)w * N + i]);
+    const uint2 c0 = __ldg(&pw[2 * w]), c1 = __ldg(&pw[2 * w + 1]);
+    acc = csub32(acc + shoup32((uint32_t)top, c0.x, c0.y, p), p2);
+    acc = csub32(acc + shoup32((uint32_t)(top >> 32), c1.x, c1.y, p), p2);
+  }
+  return acc + (negW & (uint32_t)((int64_t)top >> 63));
+}
+
+// Baby rotations of he_gemv (he-algo.c:66-68) on the 30-bit limbs: ONE decomposition and forward transform of ct.c1 per limb,
+// then per rotation j and half h the permuted product with rk[j] and an inverse transform (same identity as k_ks_baby).
+//   chat32[j][b][h][i][N] = y-weighted invntt( perm_j( ntt(c1 mod q_i) ) o rk[j].p_h[i] ),  lazily reduced (below 2q)
+template <int LOGN>
+__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS)
+k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const __grid_constant__ Baby32 S, unsigned m, unsigned mkey,
+            const uint2 *__restrict__ dec32, unsigned decstride, uint32_t *__restrict__ chat, size_t chat_jstride, Tables32 T) {
+  // m: limbs of this launch; mkey: limbs per half in the key arrays (hb_ctx::hyb_mmax)
+  typedef Cfg32<LOGN> G;
+  extern __shared__ __align__(16) uint32_t sm32[];
+  uint32_t *smA = sm32, *smB = sm32 + G::SMEM_WORDS;
+  const unsigned b = blockIdx.x / m, i = blockIdx.x % m;
+  const uint32_t p = T.primes[i].p, p2 = 2 * p;
+  const uint2 *pw = dec32 + (size_t)i * decstride;
+  const uint32_t negW = p - __ldg(&pw[2 * W]).x;
+  const uint64_t *poly = src + (size_t)b * src_bstride;
+  for (int c = threadIdx.x; c < G::N; c += G::THREADS) smA[pidx32(c)] = decompose32(poly, c, W, G::N, pw, p, p2, negW);
+  ntt32_forward<LOGN>(smA, T.tw + (size_t)i * G::N, p);
+  const uint2 *itw = T.itw + (size_t)i * G::N;
+#pragma unroll 1
+  for (unsigned j = 0; j < S.nj; j++) {
+    const uint16_t *perm = S.perm[j];
+#pragma unroll 1
+    for (int h = 0; h < 2; h++) {
+      const uint32_t *kw = S.key[j] + ((size_t)h * mkey + i) * 2 * G::N, *kq = kw + G::N;
+#pragma unroll 4
+      for (int c = threadIdx.x; c < G::N; c += G::THREADS) {
+        const unsigned s = __ldg(&perm[c]);
+        smB[pidx32(c)] = shoup32(smA[pidx32(s)], __ldg(&kw[c]), __ldg(&kq[c]), p);      // below 2q
+      }
+      ntt32_inverse<LOGN>(smB, itw, p);
+      uint32_t *dst = chat + (size_t)j * chat_jstride + (((size_t)b * 2 + h) * m + i) * G::N;
+      for (int c = threadIdx.x; c < G::N; c += G::THREADS) __stcs(&dst[c], smB[pidx32(c)]);
+      __syncthreads();                                       // smB is refilled
+    }
+  }
+}
+
+// Giant steps of he_gemv (he-algo.c:80-84) on the 30-bit limbs, summed over the giant steps in the transform domain (the
+// 30-bit twin of k_ks_limb_sum):
+//   chatX[b][h][i][N] = y-weighted invntt( sum_g ntt( sigma_g(inner_g[b].c1) mod q_i ) o rk[g n1].p_h[i] )
+template <int LOGN>
+__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS)
+k32_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src_gstride, int W, const __grid_constant__ Groups32 S,
+                unsigned ng, unsigned m, unsigned mkey, const uint2 *__restrict__ dec32, unsigned decstride, uint32_t *__restrict__ chatX, Tables32 T) {
+  typedef Cfg32<LOGN> G;
+  extern __shared__ __align__(16) uint32_t sm32[];
+  uint32_t *smA = sm32;
+  const unsigned b = blockIdx.x / m, i = blockIdx.x % m;
+  const uint32_t p = T.primes[i].p, p2 = 2 * p;
+  const uint2 *pw = dec32 + (size_t)i * decstride;
+  const uint32_t negW = p - __ldg(&pw[2 * W]).x;
+  const uint2 *tw = T.tw + (size_t)i * G::N;
+#pragma unroll 1
+  for (unsigned g = 0; g < ng; g++) {
+    const uint64_t *poly = src + (size_t)g * src_gstride + (size_t)b * src_bstride;
+    const unsigned ge = S.g[g];
+    // sigma_g scatters coefficient c to c g mod 2N, negated past N (poly_rot, poly.c:263-283)
+    for (int c = threadIdx.x; c < G::N; c += G::THREADS) {
+      const uint32_t v = decompose32(poly, c, W, G::N, pw, p, p2, negW);            // below 3q
+      const unsigned k = ((unsigned)c * ge) & (2 * G::N - 1);
+      smA[pidx32(k & (G::N - 1))] = (k >= (unsigned)G::N) ? 3 * p - v : v;
+    }
+    ntt32_forward<LOGN>(smA, tw, p);
+#pragma unroll 1
+    for (int h = 0; h < 2; h++) {
+      uint32_t *acc = sm32 + (size_t)(1 + h) * G::SMEM_WORDS;
+      const uint32_t *kw = S.key[g] + ((size_t)h * mkey + i) * 2 * G::N, *kq = kw + G::N;
+#pragma unroll 4
+      for (int c = threadIdx.x; c < G::N; c += G::THREADS) {
+        uint32_t v = shoup32(smA[pidx32(c)], __ldg(&kw[c]), __ldg(&kq[c]), p);          // below 2q
+        if (g) v = csub32(v + acc[pidx32(c)], p2);
+        acc[pidx32(c)] = v;
+      }
+    }
+    __syncthreads();                                         // smA is refilled; the accumulators are thread-private
+  }
+  const uint2 *itw = T.itw + (size_t)i * G::N;
+#pragma unroll 1
+  for (int h = 0; h < 2; h++) {
+    uint32_t *acc = sm32 + (size_t)(1 + h) * G::SMEM_WORDS;
+    ntt32_inverse<LOGN>(acc, itw, p);
+    uint32_t *dst = chatX + (((size_t)b * 2 + h) * m + i) * G::N;
+    for (int c = threadIdx.x; c < G::N; c += G::THREADS) __stcs(&dst[c], acc[pidx32(c)]);
+  }
+}
+
+// plain forward transform of u32 limbs (limb j uses prime j % D), canonical output: the key conversion at hb_evk_upload
+template <int LOGN>
+__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS)
+k32_ntt_fwd_plain(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, Tables32 T, unsigned D) {
+  typedef Cfg32<LOGN> G;
+  extern __shared__ __align__(16) uint32_t sm32[];
+  const unsigned i = blockIdx.x % D;
+  const uint32_t p = T.primes[i].p, p2 = 2 * p;
+  const uint32_t *src = in + (size_t)blockIdx.x * G::N;
+  for (int c = threadIdx.x; c < G::N; c += G::THREADS) sm32[pidx32(c)] = src[c];
+  ntt32_forward<LOGN>(sm32, T.tw + (size_t)i * G::N, p);
+  uint32_t *dst = out + (size_t)blockIdx.x * G::N;
+  for (int c = threadIdx.x; c < G::N; c += G::THREADS) {
+    uint32_t v = sm32[pidx32(c)];
+    v = csub32(v, p2);
+    dst[c] = csub32(v, p);
+  }
 }
 
 }  // namespace hb32

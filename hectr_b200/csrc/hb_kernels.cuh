@@ -132,9 +132,11 @@ __global__ void k_shoup_prep(const uint64_t *__restrict__ in, ulonglong2 *__rest
 template <int LOGN>
 __global__ void __launch_bounds__(Cfg<LOGN>::THREADS, KsBlocks<LOGN>::value)
 k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, const __grid_constant__ KsGroups S,
-          unsigned dimevk, uint64_t *__restrict__ chat, Tables T, unsigned D, unsigned d0, unsigned Dn) {
+          unsigned dimevk, uint64_t *__restrict__ chat, Tables T, unsigned D, unsigned d0, unsigned Dn,
+          const ulonglong2 *__restrict__ dec_override) {
   // D: limbs of the CRT basis (selects the pre-weights); this launch covers limbs [d0, d0 + Dn) and writes them compactly:
-  // chat[b][h][Dn][N].  A whole key switch has d0 = 0, Dn = D.
+  // chat[b][h][Dn][N].  A whole key switch has d0 = 0, Dn = D.  dec_override: pre-weights of another basis, [limb][WC + 1]
+  // (the hybrid basis of hb_dev32.cuh), instead of the D-limb table.
   typedef Cfg<LOGN> G;
   extern __shared__ __align__(16) uint64_t smem[];
   uint64_t *smA = smem, *smB = smem + G::SMEM_WORDS;
@@ -144,7 +146,7 @@ k_ks_limb(const uint64_t *__restrict__ src, size_t src_bstride, int W, const __g
   const Mod m = make_mod(pc.p);
   const uint64_t negW = pc.p - T.pow64[(size_t)d * (T.WC + 1) + W];
   const uint64_t *poly = src + (size_t)b * src_bstride;
-  const ulonglong2 *dc = T.dec_s + ((size_t)D * T.dimub + d) * (T.WC + 1);
+  const ulonglong2 *dc = dec_override ? dec_override + (size_t)d * (T.WC + 1) : T.dec_s + ((size_t)D * T.dimub + d) * (T.WC + 1);
   const unsigned grp = b / S.gbatch;
   const ulonglong2 *evk = S.evk[grp];
   poly_forward<LOGN, true>(smA, poly, W, S.g[grp], S.ginv[grp], pc, m, negW, make_tw(T, d, false), dc);
@@ -235,17 +237,18 @@ struct BabySet {
 template <int LOGN>
 __global__ void __launch_bounds__(Cfg<LOGN>::THREADS, KsBlocks<LOGN>::value)
 k_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const __grid_constant__ BabySet S, unsigned dimevk,
-          uint64_t *__restrict__ chat, size_t chat_jstride, Tables T, unsigned D) {
+          uint64_t *__restrict__ chat, size_t chat_jstride, Tables T, unsigned D, unsigned Dn, const ulonglong2 *__restrict__ dec_override) {
+  // limbs [0, Dn) of the D-limb basis (Dn = D: all), written compactly as chat[j][b][h][Dn][N]; dec_override as in k_ks_limb
   typedef Cfg<LOGN> G;
   extern __shared__ __align__(16) uint64_t smem[];
   uint64_t *smA = smem, *smB = smem + G::SMEM_WORDS;
   const unsigned idx = blockIdx.x / G::C, chunk = chunk_rank<LOGN>();
-  const unsigned b = idx / D, d = idx % D;
+  const unsigned b = idx / Dn, d = idx % Dn;
   const PrimeConsts pc = T.primes[d];
   const Mod m = make_mod(pc.p);
   const uint64_t negW = pc.p - T.pow64[(size_t)d * (T.WC + 1) + W];
   const uint64_t *poly = src + (size_t)b * src_bstride;
-  const ulonglong2 *dc = T.dec_s + ((size_t)D * T.dimub + d) * (T.WC + 1);
+  const ulonglong2 *dc = dec_override ? dec_override + (size_t)d * (T.WC + 1) : T.dec_s + ((size_t)D * T.dimub + d) * (T.WC + 1);
   poly_forward<LOGN, true>(smA, poly, W, 1u, 1u, pc, m, negW, make_tw(T, d, false), dc);
   if constexpr (G::C > 1) cg::this_cluster().sync();        // peers' chunks of the transform are complete
   const Tw itw = make_tw(T, d, true);
@@ -265,7 +268,7 @@ k_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const __g
         smB[pidx(i)] = shoup_lazy(v, k.x, k.y, m);
       }
       __syncthreads();
-      uint64_t *dst = chat + (size_t)j * chat_jstride + (((size_t)b * 2 + h) * D + d) * G::N;
+      uint64_t *dst = chat + (size_t)j * chat_jstride + (((size_t)b * 2 + h) * Dn + d) * G::N;
       ntt_inverse<LOGN, INV_RAW>(smB, [&](int gi, uint64_t v) { HB_ST(&dst[gi], v); }, itw, pc, m);
     }
   }
@@ -507,14 +510,14 @@ __global__ void k_recon_add(const uint64_t *__restrict__ chat, unsigned D, uint6
 // below 2^64), and roundup = [R > floor(P/2)]  (mpi_rdiv, types.c:115-128)
 template <int WPK>
 __device__ __forceinline__ void ks_R_exact(const uint64_t *__restrict__ limbs, size_t lstride, unsigned D, const Tables &T,
-                                           uint64_t (&R)[WPK], bool &roundup_out) {
+                                           uint64_t (&R)[WPK], bool &roundup_out, const ulonglong2 *__restrict__ ztab = nullptr) {
 #pragma unroll
   for (int w = 0; w < WPK; w++) R[w] = 0;
   uint64_t Flo = 0, Fhi = 0;
   const int WP = T.WP;
   for (unsigned d = 0; d < T.dim; d++) {
     const uint64_t p = T.primes[d].p, mu = T.primes[d].mu;
-    const ulonglong2 kz = T.ks_z[(size_t)D * T.dim + d];                      // limbs hold y_d: re-weight for P
+    const ulonglong2 kz = ztab ? ztab[d] : T.ks_z[(size_t)D * T.dim + d];     // limbs hold y_d: re-weight for P
     const uint64_t z = shoup(limbs[(size_t)d * lstride], kz.x, kz.y, p);
     uint64_t lo = z * mu, hi = __umul64hi(z, mu);
     Flo += lo;
@@ -907,6 +910,187 @@ k_ks_finish_sum(const uint64_t *__restrict__ chatP, size_t chatP_gstride, const 
   uint64_t x[2] = {(uint64_t)tt, (uint64_t)(tt >> 64)};
   sext_bits<2>(x, k);                                                            // the centred sum of the he_add chain
   if (shift > 0 || kout != k) {                                                  // he_rs: rounded shift, ties toward -inf (types.c:115-128)
+    const __int128 vs = (__int128)((((u128)x[1]) << 64) | x[0]);
+    __int128 q = vs;
+    if (shift > 0) {
+      const u128 rem = (u128)vs & ((((u128)1) << shift) - 1), half = ((u128)1) << (shift - 1);
+      q = (vs >> shift) + (rem > half ? 1 : 0);
+    }
+    x[0] = (uint64_t)(u128)q;
+    x[1] = (uint64_t)((u128)q >> 64);
+    sext_bits<2>(x, kout);
+  }
+  uint64_t *o = out + ((size_t)b * 2 + h) * Wout * N + i;
+  HB_ST(&o[0], x[0]);
+  if (Wout > 1) HB_ST(&o[N], x[1]);
+}
+
+// ---- hybrid basis (hb_dev32.cuh "Key switching on a HYBRID basis"): limbs of P on 59-bit primes, the rest on 30-bit primes ----
+// Same tail as k_ks_finish_fast / k_ks_finish_sum with the CRT over M = P * Q_m.  The host guarantees |x| < M / 8 from the measured
+// key bound, so the rounding v = round(sum y/prime) sits at least 3/8 away from a boundary and the fixed-point sum (error below
+// 2^-18) always decides it; only the decisions about R = x mod P can land inside a margin, and those go to the exact path.
+#define HB_HYB_MAX32 12
+struct KsHyb {
+  uint64_t p[4], mu[4], phat[4][2];                       // limbs of P: modulus, floor(2^120/p), M/p_e mod 2^128 (times P^-1)
+  uint32_t q[HB_HYB_MAX32], mu32[HB_HYB_MAX32];           // 30-bit limbs: modulus, floor(2^61/q)
+  uint64_t qhat[HB_HYB_MAX32][2];                         // M/q_i mod 2^128 (times P^-1)
+  uint64_t M[2];                                          // M mod 2^128 (times P^-1)
+  uint64_t kinv[4], kinvq[4], kphat[4][2], kP[2];         // y_e -> z_e re-weighting, P/p_e and P mod 2^128 (times P^-1)
+  const ulonglong2 *ztab;                                 // DEVICE [dim]: kinv as Shoup pairs for the exact path
+  unsigned dim, m;
+};
+
+__device__ __forceinline__ void mac_low32(uint64_t (&acc)[2], uint32_t y, const uint64_t (&w)[2]) {   // acc += y * w (mod 2^128)
+  const uint64_t a = (uint64_t)y * lo32(w[0]);                       // bits 0..63
+  const uint64_t b = (uint64_t)y * hi32(w[0]);                       // bits 32..95
+  const uint64_t lo = a + (b << 32);
+  const uint64_t hi = (b >> 32) + (lo < a) + (uint64_t)y * w[1];     // low 64 bits of y * w[1] suffice
+  acc[0] += lo;
+  acc[1] += hi + (acc[0] < lo);
+}
+
+// x part of the hybrid tail for one coefficient: acc = sum y phat (mod 2^128), Fx = sum y / prime in units of 2^-56
+template <int DIM, int M32>
+__device__ __forceinline__ void hyb_x32(const uint32_t *__restrict__ limbs32, unsigned N, const KsHyb &F, uint64_t (&acc)[2], uint64_t &Fx) {
+  uint32_t y[M32];
+#pragma unroll
+  for (int i = 0; i < M32; i++) y[i] = __ldcs(&limbs32[(size_t)i * N]);
+#pragma unroll
+  for (int i = 0; i < M32; i++) {
+    Fx += ((uint64_t)y[i] * F.mu32[i]) >> 5;
+    mac_low32(acc, y[i], F.qhat[i]);
+  }
+}
+
+template <int WPK>
+__device__ __noinline__ void hyb_R_slow(const uint64_t *__restrict__ limbs59, unsigned N, const Tables &T, const ulonglong2 *__restrict__ ztab,
+                                        uint64_t (&RP)[2], bool &roundup) {
+  uint64_t R[WPK];
+  ks_R_exact<WPK>(limbs59, N, 0u, T, R, roundup, ztab);
+  uint64_t r2[2] = {R[0], (WPK > 1 && T.WP > 1) ? R[1 < WPK ? 1 : 0] : 0};
+  mul_Pinv<2>(r2, T, RP);                                   // R P^-1 mod 2^128
+}
+
+template <int WPK, int DIM, int M32>
+__global__ void __launch_bounds__(128)
+k_ks_finish_hyb(const uint64_t *__restrict__ chat59, const uint32_t *__restrict__ chat32, const __grid_constant__ KsHyb F,
+                const uint64_t *__restrict__ add0, const uint64_t *__restrict__ add1, size_t add_bstride, int Wadd,
+                const __grid_constant__ TailGroups TG, uint64_t *__restrict__ out, int Wout, int k, const __grid_constant__ Tables T, unsigned batch) {
+  typedef unsigned __int128 u128;
+  const unsigned N = T.N;
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)batch * 2 * N) return;
+  const unsigned i = gid % N, h = (gid / N) & 1, b = gid / (2 * (size_t)N);
+  const unsigned grp = b / TG.gbatch, ginv = TG.ginv[grp], badd = TG.add_shared ? b - grp * TG.gbatch : b;
+  const uint64_t *limbs59 = chat59 + ((size_t)b * 2 + h) * DIM * N + i;
+  const uint32_t *limbs32 = chat32 + ((size_t)b * 2 + h) * M32 * N + i;
+  const uint64_t ONE = 1ULL << 56, HALF = 1ULL << 55, MASK = ONE - 1, MARGIN = 1ULL << 38;
+  uint64_t acc[2] = {0, 0}, Rl[2] = {0, 0}, Fx = 0, Fr = 0;
+  hyb_x32<DIM, M32>(limbs32, N, F, acc, Fx);
+#pragma unroll
+  for (int e = 0; e < DIM; e++) {
+    const uint64_t y = HB_LD(&limbs59[(size_t)e * N]);                   // below 2p
+    Fx += (uint64_t)hi32(y) * hi32(F.mu[e]);
+    mac_low<2>(acc, y, F.phat[e]);
+    const Mod m = make_mod(F.p[e]);
+    const uint64_t z = shoup_lazy(y, F.kinv[e], F.kinvq[e], m);
+    Fr += (uint64_t)hi32(z) * hi32(F.mu[e]);
+    mac_low<2>(Rl, z, F.kphat[e]);
+  }
+  const uint64_t v = (Fx + HALF) >> 56;
+  uint64_t dlt[2] = {0, 0};
+  mac_low<2>(dlt, v, F.M);
+  u128 tt = ((((u128)acc[1]) << 64) | acc[0]) - ((((u128)dlt[1]) << 64) | dlt[0]);
+  const uint64_t fr = Fr & MASK;
+  bool roundup;
+  if (fr < MARGIN || fr > ONE - MARGIN || (fr > HALF - MARGIN && fr < HALF + MARGIN)) {
+    uint64_t RP[2];
+    hyb_R_slow<WPK>(limbs59, N, T, F.ztab, RP, roundup);
+    tt -= (((u128)RP[1]) << 64) | RP[0];
+  } else {
+    const uint64_t v2 = Fr >> 56;
+    roundup = fr > HALF;
+    uint64_t sub[2] = {0, 0};
+    mac_low<2>(sub, v2, F.kP);
+    tt -= ((((u128)Rl[1]) << 64) | Rl[0]) - ((((u128)sub[1]) << 64) | sub[0]);
+  }
+  uint64_t t[2] = {(uint64_t)tt, (uint64_t)(tt >> 64)};
+  ks_tail<2>(t, roundup, h ? add1 : add0, add_bstride, Wadd, ginv, N, b, badd, h, i, out, Wout, k);
+}
+
+// summed giant steps on the hybrid basis: chatP[g][b][h][DIM][N] (u64, limbs of P per giant step), chatX32[b][h][M32][N] (u32, summed)
+template <int WPK, int DIM, int M32>
+__global__ void __launch_bounds__(128)
+k_ks_finish_sum_hyb(const uint64_t *__restrict__ chatP, size_t chatP_gstride, const uint32_t *__restrict__ chatX32, const __grid_constant__ KsHyb F,
+                    const uint64_t *__restrict__ add0, size_t add_gstride, size_t add_bstride, int Wadd, const __grid_constant__ SumGroups SG,
+                    uint64_t *__restrict__ out, int Wout, int k, int shift, int kout, const __grid_constant__ Tables T, unsigned batch) {
+  typedef unsigned __int128 u128;
+  const unsigned N = T.N;
+  const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)batch * 2 * N) return;
+  const unsigned i = gid % N, h = (gid / N) & 1, b = gid / (2 * (size_t)N);
+  const unsigned ng = SG.ng;
+  const uint64_t *limbsP = chatP + ((size_t)b * 2 + h) * DIM * N + i;
+  const uint32_t *limbs32 = chatX32 + ((size_t)b * 2 + h) * M32 * N + i;
+  const uint64_t ONE = 1ULL << 56, HALF = 1ULL << 55, MASK = ONE - 1, MARGIN = 1ULL << 38;
+  uint64_t acc[2] = {0, 0}, Fx = 0;
+  hyb_x32<DIM, M32>(limbs32, N, F, acc, Fx);
+  uint64_t ysum[DIM];
+#pragma unroll
+  for (int e = 0; e < DIM; e++) ysum[e] = 0;
+  u128 Rsum = 0;
+  unsigned nround = 0;
+#pragma unroll 1
+  for (unsigned g = 0; g < ng; g++) {
+    uint64_t Rl[2] = {0, 0}, Fr = 0;
+    const uint64_t *lg = limbsP + (size_t)g * chatP_gstride;
+#pragma unroll
+    for (int e = 0; e < DIM; e++) {
+      const uint64_t a = HB_LD(&lg[(size_t)e * N]);                       // below 2p
+      ysum[e] += a;                                                      // at most 8 giant steps: below 16p < 2^64
+      const Mod m = make_mod(F.p[e]);
+      const uint64_t z = shoup_lazy(a, F.kinv[e], F.kinvq[e], m);
+      Fr += (uint64_t)hi32(z) * hi32(F.mu[e]);
+      mac_low<2>(Rl, z, F.kphat[e]);
+    }
+    const uint64_t fr = Fr & MASK;
+    if (fr < MARGIN || fr > ONE - MARGIN || (fr > HALF - MARGIN && fr < HALF + MARGIN)) {
+      uint64_t RP[2];
+      bool up;
+      hyb_R_slow<WPK>(lg, N, T, F.ztab, RP, up);
+      Rsum += (((u128)RP[1]) << 64) | RP[0];
+      nround += up ? 1u : 0u;
+    } else {
+      const uint64_t v2 = Fr >> 56;
+      nround += fr > HALF ? 1u : 0u;
+      uint64_t sub[2] = {0, 0};
+      mac_low<2>(sub, v2, F.kP);
+      Rsum += ((((u128)Rl[1]) << 64) | Rl[0]) - ((((u128)sub[1]) << 64) | sub[0]);
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < DIM; e++) {
+    Fx += (uint64_t)hi32(ysum[e]) * hi32(F.mu[e]);
+    mac_low<2>(acc, ysum[e], F.phat[e]);
+  }
+  const uint64_t v = (Fx + HALF) >> 56;
+  uint64_t dlt[2] = {0, 0};
+  mac_low<2>(dlt, v, F.M);
+  u128 tt = ((((u128)acc[1]) << 64) | acc[0]) - ((((u128)dlt[1]) << 64) | dlt[0]) - Rsum + nround;
+  if (h == 0 && add0) {                                                  // sum_g sigma_g(inner_g.c0)
+#pragma unroll 1
+    for (unsigned g = 0; g < ng; g++) {
+      const unsigned ip = (i * SG.ginv[g]) & (2 * N - 1);
+      const uint64_t *ap = add0 + (size_t)g * add_gstride + (size_t)b * add_bstride + (ip & (N - 1));
+      const uint64_t lo = HB_LD(&ap[0]);
+      const uint64_t hi = Wadd > 1 ? HB_LD(&ap[N]) : (uint64_t)((int64_t)lo >> 63);
+      const u128 a = ((u128)hi << 64) | lo;
+      tt = (ip >= N) ? tt - a : tt + a;
+    }
+  }
+  uint64_t x[2] = {(uint64_t)tt, (uint64_t)(tt >> 64)};
+  sext_bits<2>(x, k);
+  if (shift > 0 || kout != k) {                                          // he_rs (types.c:115-128)
     const __int128 vs = (__int128)((((u128)x[1]) << 64) | x[0]);
     __int128 q = vs;
     if (shift > 0) {

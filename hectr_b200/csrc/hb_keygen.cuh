@@ -164,7 +164,10 @@ __global__ void k_tail(const uint64_t *__restrict__ prod, Consts C, const int64_
 // Per coefficient the exact CRT over the D key primes, centred mod P_D -- the integer he_genswk decomposed (he-kem.c:97-110), as
 // long as it was below P_D / 2, which smod(., P q_L) guarantees -- and the maximum bit length of its magnitude over the whole key.
 // A key made by he_genswk stays below P q_L / 2; limbs that are merely uniform residues (synthetic keys) reach P_D.
-__global__ void k_lift_bits(const uint64_t *__restrict__ coef, Consts C, unsigned npoly, unsigned *__restrict__ out_max) {
+// With res32 != nullptr the same pass also reduces the lift modulo the m32 primes q32[] of the engine's 30-bit basis
+// (res32[q][i32][N], canonical): the key's limbs for the hybrid-basis key switch (hb_dev32.cuh).
+__global__ void k_lift_bits(const uint64_t *__restrict__ coef, Consts C, unsigned npoly, unsigned *__restrict__ out_max,
+                            const uint32_t *__restrict__ q32, unsigned m32, uint32_t *__restrict__ res32) {
   const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= (size_t)npoly * C.N) return;
   const unsigned i = gid % C.N, q = gid / C.N;
@@ -177,7 +180,17 @@ __global__ void k_lift_bits(const uint64_t *__restrict__ coef, Consts C, unsigne
     addmul(u, C.phat + (size_t)d * W, y, W);
   }
   for (unsigned it = 0; it <= C.D && ucmp(u, C.PD, W) >= 0; it++) sub(u, C.PD, W);
-  if (ucmp(u, C.PDh, W) >= 0) { sub(u, C.PD, W); neg(u, W); }         // magnitude of the centred value
+  bool negative = false;
+  if (ucmp(u, C.PDh, W) >= 0) { sub(u, C.PD, W); neg(u, W); negative = true; }         // magnitude of the centred value
+  if (res32) {
+    for (unsigned j = 0; j < m32; j++) {
+      const uint64_t qq = q32[j];
+      uint64_t r = 0;
+      for (int w = W - 1; w >= 0; w--) r = (uint64_t)((((unsigned __int128)r << 64) | u[w]) % qq);
+      if (negative && r) r = qq - r;
+      res32[((size_t)q * m32 + j) * C.N + i] = (uint32_t)r;
+    }
+  }
   unsigned bits = 0;
   for (int w = W - 1; w >= 0; w--)
     if (u[w]) { bits = 64u * (unsigned)w + (64u - (unsigned)__clzll((long long)u[w])); break; }

@@ -8,6 +8,6 @@ timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --mas
 echo "rc=$?"; tail -c 400 gpurun_out/bench_n$N.err
 python - <<PY
 import json
-d = json.load(open("gpurun_out/bench_n$N.json"))
+d = [json.loads(l) for l in open("gpurun_out/bench_n$N.json") if l.startswith("{")][-1]
 print("N=$N", round(d["value"]), "it/s  e2e", round(d["e2e"]["value"]), "single call", round(d["e2e"]["single_blocking_call"]["value"]), "parity", d.get("parity_spot"))
 PY

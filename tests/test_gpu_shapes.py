@@ -104,22 +104,28 @@ def test_config_E_4096_instances(cfgA, monkeypatch):
 
 # (the tests that share the module's config-A reference context come first: the reference keeps ONE global context and
 # every Ref.get with other parameters re-initialises it)
-def test_summed_giant_steps_equal_one_tail_per_step(cfgA, monkeypatch):
-    """he_gemv's giant-step key switches share one reconstruction (k_ks_limb_sum / k_ks_finish_sum) and identically zero giant
-    steps are skipped; HB_GEMV_NOSUM / HB_GEMV_NOSKIP switch both off.  All variants must give the same words on 192 full-size
-    random ciphertexts per level (a few of the 3 M coefficients land inside the fixed-point margin and take ks_sum_slow), for a
-    dense matrix and for the hempc block matrices; the profile names which kernels ran."""
+def test_gemv_shortcuts_equal_the_plain_schedule(cfgA, monkeypatch):
+    """Three exact shortcuts of he_gemv, all on by default and all bound-checked against the measured key size:
+      * identically zero giant steps are skipped                              (HB_GEMV_NOSKIP=1 switches it off)
+      * the giant-step key switches share one reconstruction                  (HB_GEMV_NOSUM=1;  k_ks_limb_sum / k_ks_finish_sum)
+      * the key-switch limbs that do not divide P run on 30-bit primes        (HB_GEMV_NOHYB=1;  k32_ks_baby / k32_ks_limb_sum / k_ks_finish_*hyb)
+    Engines with (all on), (hybrid off) and (everything off) must give the same words on 192 full-size random ciphertexts
+    per level -- a few of the 3 M coefficients land inside the fixed-point margins and take the exact paths; one instance has
+    c1 = 0, where EVERY decision about R sits on a boundary -- for a dense matrix and for the hempc block matrices; the launch
+    profile names which kernels ran."""
     from hectr_b200 import Engine
     eng, ref = cfgA["eng"], cfgA["ref"]
     rk_arr = np.stack([ref.evk_to_array(cfgA["rk"][i]) for i in range(16)])
     rng = np.random.default_rng(811)
     Ka, Kb = hempc_gains(rng)
     Ad = rng.standard_normal((16, 16)) + 1j * rng.standard_normal((16, 16))
+    monkeypatch.setenv("HB_GEMV_NOHYB", "1")
+    sum59 = Engine(*A_PARAMS)
     monkeypatch.setenv("HB_GEMV_NOSUM", "1")
     monkeypatch.setenv("HB_GEMV_NOSKIP", "1")
     plain = Engine(*A_PARAMS)
-    monkeypatch.delenv("HB_GEMV_NOSUM")
-    monkeypatch.delenv("HB_GEMV_NOSKIP")
+    for v in ("HB_GEMV_NOSUM", "HB_GEMV_NOSKIP", "HB_GEMV_NOHYB"):
+        monkeypatch.delenv(v)
 
     def names_of(e):
         need = e.lib.hb_prof_report(e.ctx, None, 0)
@@ -128,27 +134,33 @@ def test_summed_giant_steps_equal_one_tail_per_step(cfgA, monkeypatch):
         return json.loads(buf.value.decode())
 
     try:
-        keys2 = plain.keys(rk_arr)
+        keys_s, keys_p = sum59.keys(rk_arr), plain.keys(rk_arr)
+        engines = ((eng, cfgA["keys"]), (sum59, keys_s), (plain, keys_p))
         for l in (2, 1):
             a = random_ct_words(rng, 192, eng.words(l), eng.n, eng.logq(l))
-            a[0, 1] = 0                                     # c1 = 0: every R is exactly 0, all decisions go to the slow path
+            a[0, 1] = 0                                     # c1 = 0: every R is exactly 0
             for M in (Ad, Ka, Kb):
-                for e in (eng, plain):
+                outs, profs = [], []
+                for e, kk in engines:
                     e.lib.hb_prof_reset(e.ctx)
                     e.lib.hb_prof_enable(e.ctx, 1)
-                got = eng.he_gemv(M, eng.ct(a, l), cfgA["keys"])
-                want = plain.he_gemv(M, plain.ct(a, l), keys2)
-                pe, pp = names_of(eng), names_of(plain)
-                for e in (eng, plain):
+                    outs.append(e.he_gemv(M, e.ct(a, l), kk))
+                    profs.append(names_of(e))
                     e.lib.hb_prof_enable(e.ctx, 0)
-                assert "k_ks_finish_sum" in pe and "k_ks_limb_sum" in pe, sorted(pe)
-                assert "k_ks_finish_sum" not in pp and "k_ct_sum_rs" in pp, sorted(pp)
-                assert got.l == want.l and got.nu == want.nu and got.B == want.B
-                assert np.array_equal(got.download(), want.download()), l
-                got.free()
-                want.free()
-        keys2.free()
+                ph, ps, pp = profs
+                assert {"k32_ks_baby", "k_ks_finish_hyb", "k32_ks_limb_sum", "k_ks_finish_sum_hyb"} <= set(ph), sorted(ph)
+                assert {"k_ks_limb_sum", "k_ks_finish_sum"} <= set(ps) and not any("hyb" in n or n.startswith("k32_ks") for n in ps), sorted(ps)
+                assert "k_ct_sum_rs" in pp and not any("sum" in n and n != "k_ct_sum_rs" for n in pp) and not any("hyb" in n for n in pp), sorted(pp)
+                want = outs[2].download()
+                for o in outs[:2]:
+                    assert o.l == outs[2].l and o.nu == outs[2].nu and o.B == outs[2].B
+                    assert np.array_equal(o.download(), want), l
+                for o in outs:
+                    o.free()
+        keys_s.free()
+        keys_p.free()
     finally:
+        sum59.close()
         plain.close()
 
 
