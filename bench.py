@@ -225,8 +225,8 @@ def pinned_array(eng, shape):
 UNITS = {
     # one he_swk = read d0, d1 + write c0, c1 + the key shared by the batch; RNS intermediates count as on-chip.
     # The per-limb kernel and the per-coefficient tail are the two halves of the SAME key switches: the unit's time is the sum.
-    "baby key switches (n1 he_rot of one ciphertext, he-algo.c:66-68)": ("keyswitch_n1", ("k_ks_baby", "k_ks_finish_fast", "k_ks_finish")),
-    "giant key switches + he_add chain + he_rs (he-algo.c:80-90)": ("keyswitch_ngs", ("k_ks_limb", "k_ks_limb_sum", "k_ks_finish_sum", "k_ct_sum_rs", "k_ct_sum", "k_ct_rescale")),
+    "baby key switches (n1 he_rot of one ciphertext, he-algo.c:66-68)": ("keyswitch_n1", ("k_ks_baby", "k32_ks_baby", "k_ks_finish_hyb", "k_ks_finish_fast", "k_ks_finish")),
+    "giant key switches + he_add chain + he_rs (he-algo.c:80-90)": ("keyswitch_ngs", ("k_ks_limb", "k_ks_limb_sum", "k32_ks_limb_sum", "k_ks_finish_sum", "k_ks_finish_sum_hyb", "k_ct_sum_rs", "k_ct_sum", "k_ct_rescale")),
     "ct x pt diagonal products (he_mulpt, he-algo.c:70-79)": ("mulpt", ("k32_poly_ntt_all", "k32_poly_ntt", "k32_mulacc_intt_all", "k32_mulacc_intt", "k32_recon_smod4", "k32_recon_smod",
                                                                          "k_poly_ntt", "k_mulacc_intt", "k_recon_smod", "k_mulpt_limb")),
     "coefficient-wise passes (he_sub, he_add, he_neg, he_moddown)": ("elementwise", ("k_ct_addsub", "k_ct_combine", "k_ct_addpt")),
@@ -488,7 +488,9 @@ def finish_line(args, eng, keys, key_arr, secret, Ka, Kb, host, dev_out, prof, p
         units[uname] = {"kernels": [kn for kn in kernels if kn in prof], "ms_per_step": round(ms_u / steps, 4), "share_of_step": round(ms_u / tot_ms, 4),
                         "algorithmic_bytes_per_gemv": nbytes, "achieved_gbs": nbytes / (per_exec_ms / 1e3) / 1e9, "frac_of_hbm": nbytes / (per_exec_ms / 1e3) / 1e9 / peak}
     dom = max(prof, key=lambda kname: prof[kname]["ms"])
-    dom_unit = next(u for u, (kind, kernels) in UNITS.items() if dom in kernels)
+    dom_unit = next((u for u, (kind, kernels) in UNITS.items() if dom in kernels), None)
+    if dom_unit is None:                      # a kernel this table does not know: report the largest known unit instead
+        dom_unit = max(units, key=lambda u: units[u]["ms_per_step"])
     du = units[dom_unit]
     traffic, heavy, traffic_note = None, None, None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")

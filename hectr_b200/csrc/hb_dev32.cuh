@@ -544,8 +544,14 @@ __device__ __forceinline__ uint32_t decompose32(const uint64_t *__restrict__ pol
 // Baby rotations of he_gemv (he-algo.c:66-68) on the 30-bit limbs: ONE decomposition and forward transform of ct.c1 per limb,
 // then per rotation j and half h the permuted product with rk[j] and an inverse transform (same identity as k_ks_baby).
 //   chat32[j][b][h][i][N] = y-weighted invntt( perm_j( ntt(c1 mod q_i) ) o rk[j].p_h[i] ),  lazily reduced (below 2q)
+#ifndef HB32_KSB_MINB
+#define HB32_KSB_MINB 1
+#endif
+#ifndef HB32_KSS_MINB
+#define HB32_KSS_MINB 1
+#endif
 template <int LOGN>
-__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS)
+__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_KSB_MINB)
 k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const __grid_constant__ Baby32 S, unsigned m, unsigned mkey,
             const uint2 *__restrict__ dec32, unsigned decstride, uint32_t *__restrict__ chat, size_t chat_jstride, Tables32 T) {
   // m: limbs of this launch; mkey: limbs per half in the key arrays (hb_ctx::hyb_mmax)
@@ -583,7 +589,7 @@ k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const _
 // 30-bit twin of k_ks_limb_sum):
 //   chatX[b][h][i][N] = y-weighted invntt( sum_g ntt( sigma_g(inner_g[b].c1) mod q_i ) o rk[g n1].p_h[i] )
 template <int LOGN>
-__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS)
+__global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_KSS_MINB)
 k32_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src_gstride, int W, const __grid_constant__ Groups32 S,
                 unsigned ng, unsigned m, unsigned mkey, const uint2 *__restrict__ dec32, unsigned decstride, uint32_t *__restrict__ chatX, Tables32 T) {
   typedef Cfg32<LOGN> G;
