@@ -161,105 +161,6 @@ __device__ __forceinline__ void ntt32_inverse(uint32_t *sm, const uint2 *__restr
   inv32<LOGN, 0>(sm, itw, p);
 }
 
-// ---------------------------------------------------------------------------------------------------------------
-// Passes with caller-supplied tile access (round 2).  On 30-bit limbs a butterfly is eight instructions, so the traffic
-// around the transform weighs as much as the transform: a kernel that loads its limb into shared memory, transforms, and
-// reads it back for the next step pays four shared-memory round trips and five barriers per transform.  Here the FIRST pass
-// takes its tile from a functor (global words decomposed on the fly, register-resident digits, a product formed from two
-// operands) and the LAST pass hands its tile to a functor (global store, accumulation), which leaves two round trips and
-// three barriers.  A functor gets the tile's base index g and, at compile time, the element stride STR and the tile's
-// position r among the tiles this thread owns; element t of the tile is natural index g + t * STR.
-//   forward : first pass S = 0 (STR = N / 2^R, consecutive threads own consecutive g), last pass STR = 1 (2^R consecutive indices)
-//   inverse : first executed pass is the deepest one (STR = 1), the last executed is S = 0
-// ---------------------------------------------------------------------------------------------------------------
-struct SmLd32 {
-  const uint32_t *sm;
-  template <int R, int STR, int RI>
-  __device__ __forceinline__ void operator()(uint32_t (&x)[1 << R], int g) const {
-#pragma unroll
-    for (int t = 0; t < (1 << R); t++) x[t] = sm[pidx32(g + t * STR)];
-  }
-};
-struct SmSt32 {
-  uint32_t *sm;
-  template <int R, int STR, int RI>
-  __device__ __forceinline__ void operator()(const uint32_t (&x)[1 << R], int g) const {
-#pragma unroll
-    for (int t = 0; t < (1 << R); t++) sm[pidx32(g + t * STR)] = x[t];
-  }
-};
-
-template <int LOGN, int S, int R, bool INV, int RI, class LD, class ST>
-__device__ __forceinline__ void pass32x_one(const uint2 *__restrict__ tw, uint32_t p, const LD &ld, const ST &st) {
-  typedef Cfg32<LOGN> G;
-  constexpr int LOGST = LOGN - S - R, STR = 1 << LOGST, TILES = G::N >> R, LOGBLK = LOGN - S;
-  const int t0 = threadIdx.x + RI * G::THREADS;
-  const int tile = (LOGST == 4 && TILES >= 64) ? ((t0 & ~0x30) | ((t0 & 0x10) << 1) | ((t0 & 0x20) >> 1)) : t0;
-  const int b = tile >> LOGST, o = tile & (STR - 1), g = (b << LOGBLK) + o;
-  uint32_t x[1 << R];
-  ld.template operator()<R, STR, RI>(x, g);
-  if (INV) tile_inv32<R>(x, tw, (1u << S) + b, p);
-  else tile_fwd32<R>(x, tw, (1u << S) + b, p);
-  st.template operator()<R, STR, RI>(x, g);
-}
-template <int LOGN, int S, int R, bool INV, class LD, class ST>
-__device__ __forceinline__ void pass32x(const uint2 *__restrict__ tw, uint32_t p, const LD &ld, const ST &st) {
-  typedef Cfg32<LOGN> G;
-  constexpr int TILES = G::N >> R, PERT = TILES / G::THREADS;           // tiles per thread: 1, 2 or 4 (radix-8 tiles at N = 2^13)
-  static_assert(PERT * G::THREADS == TILES && PERT >= 1 && PERT <= 4, "tiles must divide evenly among the threads");
-  pass32x_one<LOGN, S, R, INV, 0>(tw, p, ld, st);
-  if constexpr (PERT > 1) pass32x_one<LOGN, S, R, INV, 1>(tw, p, ld, st);
-  if constexpr (PERT > 2) {
-    pass32x_one<LOGN, S, R, INV, 2>(tw, p, ld, st);
-    pass32x_one<LOGN, S, R, INV, 3>(tw, p, ld, st);
-  }
-}
-
-// forward transform: input through ld (first pass), output through st (last pass); the limb lives in sm in between.
-// Values below 4p in, below 4p out.  The caller orders its own earlier uses of sm before this call.
-template <int LOGN, int S, class LD, class ST>
-__device__ __forceinline__ void fwd32x(uint32_t *sm, const uint2 *__restrict__ tw, uint32_t p, const LD &ld, const ST &st) {
-  if constexpr (S < LOGN) {
-    constexpr int R = hbdev::PassSize<LOGN - S>::R;
-    constexpr bool first = S == 0, last = S + R == LOGN;
-    if constexpr (first && last) pass32x<LOGN, S, R, false>(tw, p, ld, st);
-    else if constexpr (first) pass32x<LOGN, S, R, false>(tw, p, ld, SmSt32{sm});
-    else if constexpr (last) pass32x<LOGN, S, R, false>(tw, p, SmLd32{sm}, st);
-    else pass32x<LOGN, S, R, false>(tw, p, SmLd32{sm}, SmSt32{sm});
-    if constexpr (!last) {
-      __syncthreads();
-      fwd32x<LOGN, S + R>(sm, tw, p, ld, st);
-    }
-  }
-}
-// inverse transform (not scaled by N^-1): input below 2p through ld (deepest pass, executed first), output below 2p through st
-template <int LOGN, int S, class LD, class ST>
-__device__ __forceinline__ void inv32x(uint32_t *sm, const uint2 *__restrict__ itw, uint32_t p, const LD &ld, const ST &st) {
-  if constexpr (S < LOGN) {
-    constexpr int R = hbdev::PassSize<LOGN - S>::R;
-    constexpr bool deepest = S + R == LOGN, top = S == 0;
-    if constexpr (!deepest) {
-      inv32x<LOGN, S + R>(sm, itw, p, ld, st);
-      __syncthreads();
-    }
-    if constexpr (deepest && top) pass32x<LOGN, S, R, true>(itw, p, ld, st);
-    else if constexpr (deepest) pass32x<LOGN, S, R, true>(itw, p, ld, SmSt32{sm});
-    else if constexpr (top) pass32x<LOGN, S, R, true>(itw, p, SmLd32{sm}, st);
-    else pass32x<LOGN, S, R, true>(itw, p, SmLd32{sm}, SmSt32{sm});
-  }
-}
-// stride of the first forward / last inverse pass, and tile width of the last forward / first inverse pass
-template <int LOGN>
-struct Shape32 {
-  static constexpr int R0 = hbdev::PassSize<LOGN>::R;                 // first forward pass: 2^R0 elements, stride N >> R0
-  template <int S>
-  static constexpr int last_r() {
-    constexpr int R = hbdev::PassSize<LOGN - S>::R;
-    if constexpr (S + R == LOGN) return R; else return last_r<S + R>();
-  }
-  static constexpr int RL = last_r<0>();                              // last forward pass: 2^RL consecutive elements
-};
-
 }  // namespace hb32
 
 namespace hb32 {
@@ -414,48 +315,6 @@ namespace hb32 {
 #ifndef HB32_MA_MINB
 #define HB32_MA_MINB 2
 #endif
-// tile <- the decomposition of register-resident digits (first forward pass: element t is coefficient tid + (RI + t STR/THREADS) THREADS)
-template <int LOGN, int WT>
-struct DigitsLd32 {
-  const uint32_t (*dig)[2 * WT];
-  const uint32_t *sign;
-  const uint2 *c;
-  uint32_t p, p2, negW;
-  template <int R, int STR, int RI>
-  __device__ __forceinline__ void operator()(uint32_t (&x)[1 << R], int) const {
-    constexpr int STEP = STR / Cfg32<LOGN>::THREADS;
-    static_assert(STEP * Cfg32<LOGN>::THREADS == STR, "first-pass stride must be a multiple of the thread count");
-#pragma unroll
-    for (int t = 0; t < (1 << R); t++) {
-      const int k = RI + t * STEP;
-      uint32_t acc = shoup32(dig[k][0], c[0].x, c[0].y, p);
-#pragma unroll
-      for (int w = 1; w < 2 * WT; w++) acc = csub32(acc + shoup32(dig[k][w], c[w].x, c[w].y, p), p2);
-      x[t] = acc + (negW & sign[k]);                                     // below 3p
-    }
-  }
-};
-// tile -> 2^R consecutive words of global memory (last forward pass), 16-byte stores
-struct RunSt32 {
-  uint32_t *dst;
-  template <int R, int STR, int RI>
-  __device__ __forceinline__ void operator()(const uint32_t (&x)[1 << R], int g) const {
-    static_assert(STR == 1 && R >= 2, "run store belongs to the stride-1 pass");
-    uint4 *o = reinterpret_cast<uint4 *>(dst + g);
-#pragma unroll
-    for (int q = 0; q < (1 << R) / 4; q++) __stcs(&o[q], make_uint4(x[4 * q], x[4 * q + 1], x[4 * q + 2], x[4 * q + 3]));
-  }
-};
-// tile -> global memory at stride STR (last inverse pass): consecutive threads write consecutive words
-struct StrideSt32 {
-  uint32_t *dst;
-  template <int R, int STR, int RI>
-  __device__ __forceinline__ void operator()(const uint32_t (&x)[1 << R], int g) const {
-#pragma unroll
-    for (int t = 0; t < (1 << R); t++) __stcs(&dst[g + t * STR], x[t]);
-  }
-};
-
 template <int LOGN, int WT>
 __global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_PN_MINB)
 k32_poly_ntt_all(const uint64_t *__restrict__ src, size_t poly_stride, uint32_t *__restrict__ out, Tables32 T, unsigned D) {
@@ -486,71 +345,73 @@ k32_poly_ntt_all(const uint64_t *__restrict__ src, size_t poly_stride, uint32_t 
 #pragma unroll
     for (int w = 0; w < 2 * WT; w++) c[w] = __ldg(&pw[w]);
     const uint32_t negW = p - __ldg(&pw[2 * WT]).x;
-    // the digits never visit shared memory: the first pass decomposes them in registers, the last pass stores to global
-    fwd32x<LOGN, 0>(sm32, T.tw + (size_t)d * G::N, p, DigitsLd32<LOGN, WT>{dig, sign, c, p, p2, negW},
-                    RunSt32{out + ((size_t)q * D + d) * G::N});
+#pragma unroll
+    for (int k = 0; k < PER; k++) {
+      uint32_t acc = shoup32(dig[k][0], c[0].x, c[0].y, p);
+#pragma unroll
+      for (int w = 1; w < 2 * WT; w++) acc = csub32(acc + shoup32(dig[k][w], c[w].x, c[w].y, p), p2);
+      sm32[pidx32(threadIdx.x + k * G::THREADS)] = acc + (negW & sign[k]);      // below 3p
+    }
+    ntt32_forward<LOGN>(sm32, T.tw + (size_t)d * G::N, p);
+    uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)q * D + d) * G::N);
+#pragma unroll
+    for (int k = 0; k < PER / 4; k++) {
+      const int i4 = threadIdx.x + k * G::THREADS;
+      uint4 v;
+      v.x = sm32[pidx32(4 * i4)]; v.y = sm32[pidx32(4 * i4 + 1)]; v.z = sm32[pidx32(4 * i4 + 2)]; v.w = sm32[pidx32(4 * i4 + 3)];
+      __stcs(&dst[i4], v);
+    }
     __syncthreads();                                          // the buffer is refilled for the next limb
   }
 }
 
 // One CTA per (polynomial q, limb d): the NJ rotated transforms hat[j][q][d] are read once into registers and serve every
 // giant step g < ngroups:  chat[g][q][d] = y-weighted invntt( sum_j hat[j][q][d] o pthat[g*NJ + j][d] ).
-// tile <- sum_j h[j] o key[j] for 2^R consecutive indices (first inverse pass); h: register-resident operands of this thread's
-// runs, keys: planar multiplicands / quotients, 16-byte loads
-template <int NJ, int Q4, int PERT>
-struct MulaccLd32 {
-  const uint4 (*h)[PERT][Q4];          // [NJ][PERT][Q4]
-  const uint32_t *w;                   // plane pair of diagonal j at w + j * jstride: multiplicands, then N quotients
-  size_t jstride;
-  unsigned N;
-  uint32_t p, p2;
-  template <int R, int STR, int RI>
-  __device__ __forceinline__ void operator()(uint32_t (&x)[1 << R], int g) const {
-    static_assert(STR == 1 && (1 << R) == 4 * Q4, "product load belongs to the stride-1 pass");
-#pragma unroll
-    for (int t = 0; t < (1 << R); t++) x[t] = 0;
-#pragma unroll
-    for (int j = 0; j < NJ; j++) {
-      const uint4 *kw = reinterpret_cast<const uint4 *>(w + (size_t)j * jstride + g);
-      const uint4 *kq = reinterpret_cast<const uint4 *>(w + (size_t)j * jstride + N + g);
-#pragma unroll
-      for (int q = 0; q < Q4; q++) {
-        const uint4 a = h[j][RI][q], m = __ldg(&kw[q]), mq = __ldg(&kq[q]);
-        x[4 * q] = csub32(x[4 * q] + shoup32(a.x, m.x, mq.x, p), p2);
-        x[4 * q + 1] = csub32(x[4 * q + 1] + shoup32(a.y, m.y, mq.y, p), p2);
-        x[4 * q + 2] = csub32(x[4 * q + 2] + shoup32(a.z, m.z, mq.z, p), p2);
-        x[4 * q + 3] = csub32(x[4 * q + 3] + shoup32(a.w, m.w, mq.w, p), p2);
-      }
-    }
-  }
-};
-
 template <int LOGN, int NJ>
 __global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_MA_MINB)
 k32_mulacc_intt_all(const uint32_t *__restrict__ hat, size_t hat_jstride, const uint32_t *__restrict__ pthat_all, size_t pthat_gstride,
                     const __grid_constant__ hbdev::GroupMap GM, unsigned ngroups, unsigned nq, uint32_t *__restrict__ chat, Tables32 T, unsigned D) {
   typedef Cfg32<LOGN> G;
-  constexpr int RL = Shape32<LOGN>::RL, Q4 = (1 << RL) / 4, PERT = (G::N >> RL) / G::THREADS;     // runs of 2^RL words per thread
+  constexpr int V = G::N / 4 / G::THREADS;                    // uint4 per thread
   extern __shared__ __align__(16) uint32_t sm32[];
   const unsigned q = blockIdx.x / D, d = blockIdx.x % D;
   const uint32_t p = T.primes[d].p, p2 = 2 * p;
-  uint4 h[NJ][PERT][Q4];                                       // the NJ rotated transforms, read once, as the first inverse pass wants them
+  uint4 h[NJ][V];
 #pragma unroll
   for (int j = 0; j < NJ; j++) {
-    const uint32_t *a = hat + (size_t)j * hat_jstride + ((size_t)q * D + d) * G::N;
+    const uint4 *a = reinterpret_cast<const uint4 *>(hat + (size_t)j * hat_jstride + ((size_t)q * D + d) * G::N);
 #pragma unroll
-    for (int r = 0; r < PERT; r++) {
-      const uint4 *a4 = reinterpret_cast<const uint4 *>(a + ((size_t)(threadIdx.x + r * G::THREADS) << RL));
-#pragma unroll
-      for (int k = 0; k < Q4; k++) h[j][r][k] = __ldcs(&a4[k]);
-    }
+    for (int k = 0; k < V; k++) h[j][k] = __ldcs(&a[threadIdx.x + k * G::THREADS]);
   }
   const uint2 *itw = T.itw + (size_t)d * G::N;
 #pragma unroll 1
   for (unsigned g = 0; g < ngroups; g++) {
     const uint32_t *w = pthat_all + ((size_t)GM.idx[g] * pthat_gstride + d) * 2 * G::N;       // strides in limbs
-    inv32x<LOGN, 0>(sm32, itw, p, MulaccLd32<NJ, Q4, PERT>{h, w, (size_t)D * 2 * G::N, (unsigned)G::N, p, p2},
-                    StrideSt32{chat + (((size_t)g * nq + q) * D + d) * G::N});
+#pragma unroll
+    for (int k = 0; k < V; k++) {
+      const int i4 = threadIdx.x + k * G::THREADS;
+      uint32_t acc[4] = {0, 0, 0, 0};
+#pragma unroll
+      for (int j = 0; j < NJ; j++) {
+        const uint4 *wp = reinterpret_cast<const uint4 *>(w + (size_t)j * D * 2 * G::N);
+        const uint4 kw = __ldg(&wp[i4]), kq = __ldg(&wp[G::N / 4 + i4]);    // elements 4 i4 .. 4 i4 + 3 of both planes
+        acc[0] = csub32(acc[0] + shoup32(h[j][k].x, kw.x, kq.x, p), p2);
+        acc[1] = csub32(acc[1] + shoup32(h[j][k].y, kw.y, kq.y, p), p2);
+        acc[2] = csub32(acc[2] + shoup32(h[j][k].z, kw.z, kq.z, p), p2);
+        acc[3] = csub32(acc[3] + shoup32(h[j][k].w, kw.w, kq.w, p), p2);
+      }
+#pragma unroll
+      for (int e = 0; e < 4; e++) sm32[pidx32(4 * i4 + e)] = acc[e];
+    }
+    ntt32_inverse<LOGN>(sm32, itw, p);
+    uint4 *dst = reinterpret_cast<uint4 *>(chat + (((size_t)g * nq + q) * D + d) * G::N);
+#pragma unroll
+    for (int k = 0; k < V; k++) {
+      const int i4 = threadIdx.x + k * G::THREADS;
+      uint4 v;
+      v.x = sm32[pidx32(4 * i4)]; v.y = sm32[pidx32(4 * i4 + 1)]; v.z = sm32[pidx32(4 * i4 + 2)]; v.w = sm32[pidx32(4 * i4 + 3)];
+      __stcs(&dst[i4], v);
+    }
     __syncthreads();
   }
 }
@@ -680,86 +541,22 @@ __device__ __forceinline__ uint32_t decompose32(const uint64_t *__restrict__ pol
   return acc + (negW & (uint32_t)((int64_t)top >> 63));
 }
 
-// resident CTAs per SM the two kernels are compiled for [B200, batch 4096, before the passes were fused]: k32_ks_baby 4.28 ms per
-// launch at 5 (51 registers), 4.55 at 4, 4.42 at 6 (spills); k32_ks_limb_sum 4.33 ms at 4 (64 registers), 5.26 at 3
-// (profiles/r02/variants_hybrid.log)
+// Baby rotations of he_gemv (he-algo.c:66-68) on the 30-bit limbs: ONE decomposition and forward transform of ct.c1 per limb,
+// then per rotation j and half h the permuted product with rk[j] and an inverse transform (same identity as k_ks_baby).
+//   chat32[j][b][h][i][N] = y-weighted invntt( perm_j( ntt(c1 mod q_i) ) o rk[j].p_h[i] ),  lazily reduced (below 2q)
+// resident CTAs per SM the two kernels are compiled for [B200, batch 4096]: k32_ks_baby 4.28 ms per launch at 5 (51 registers),
+// 4.55 at 4, 4.42 at 6 (spills); k32_ks_limb_sum 4.33 ms at 4 (64 registers), 5.26 at 3  (profiles/r02/variants_hybrid.log).
+// Measured and dropped: taking the first-pass tiles straight from global words / register digits / products and handing the
+// last-pass tiles to global memory or the accumulators (two shared-memory round trips and two barriers fewer per transform)
+// changed k32_ks_baby 8.55 -> 8.65, k32_ks_limb_sum 8.66 -> 8.48, k32_poly_ntt_all 6.76 -> 6.66 and k32_mulacc_intt_all
+// 6.05 -> 8.01 ms per step (its 64-byte-per-thread runs halve the coalescing): the 30-bit kernels are not bound by their
+// shared-memory traffic (profiles/r02/fused_passes.txt).
 #ifndef HB32_KSB_MINB
 #define HB32_KSB_MINB 5
 #endif
 #ifndef HB32_KSS_MINB
 #define HB32_KSS_MINB 4
 #endif
-// tile <- residues of global multiword coefficients (first forward pass: consecutive threads read consecutive coefficients)
-struct WordsLd32 {
-  const uint64_t *poly;
-  const uint2 *pw;
-  int W;
-  unsigned N;
-  uint32_t p, p2, negW;
-  template <int R, int STR, int RI>
-  __device__ __forceinline__ void operator()(uint32_t (&x)[1 << R], int g) const {
-#pragma unroll
-    for (int t = 0; t < (1 << R); t++) x[t] = decompose32(poly, g + t * STR, W, N, pw, p, p2, negW);      // below 3q
-  }
-};
-// tile <- perm(transform) o key for 2^R consecutive indices (first inverse pass of a baby rotation)
-struct PermKeyLd32 {
-  const uint32_t *smA;                 // the forward transform of c1, padded
-  const uint16_t *perm;
-  const uint32_t *kw, *kq;             // key planes of this rotation, half and limb
-  uint32_t p;
-  template <int R, int STR, int RI>
-  __device__ __forceinline__ void operator()(uint32_t (&x)[1 << R], int g) const {
-    static_assert(STR == 1 && R >= 3, "permuted product belongs to the stride-1 pass");
-    const uint4 *pm = reinterpret_cast<const uint4 *>(perm + g);
-    const uint4 *w4 = reinterpret_cast<const uint4 *>(kw + g), *q4 = reinterpret_cast<const uint4 *>(kq + g);
-#pragma unroll
-    for (int e = 0; e < (1 << R) / 8; e++) {
-      const uint4 s = __ldg(&pm[e]);                                       // eight 16-bit source positions
-      const uint4 m0 = __ldg(&w4[2 * e]), m1 = __ldg(&w4[2 * e + 1]), c0 = __ldg(&q4[2 * e]), c1 = __ldg(&q4[2 * e + 1]);
-      x[8 * e + 0] = shoup32(smA[pidx32(s.x & 0xffff)], m0.x, c0.x, p);
-      x[8 * e + 1] = shoup32(smA[pidx32(s.x >> 16)], m0.y, c0.y, p);
-      x[8 * e + 2] = shoup32(smA[pidx32(s.y & 0xffff)], m0.z, c0.z, p);
-      x[8 * e + 3] = shoup32(smA[pidx32(s.y >> 16)], m0.w, c0.w, p);
-      x[8 * e + 4] = shoup32(smA[pidx32(s.z & 0xffff)], m1.x, c1.x, p);
-      x[8 * e + 5] = shoup32(smA[pidx32(s.z >> 16)], m1.y, c1.y, p);
-      x[8 * e + 6] = shoup32(smA[pidx32(s.w & 0xffff)], m1.z, c1.z, p);
-      x[8 * e + 7] = shoup32(smA[pidx32(s.w >> 16)], m1.w, c1.w, p);
-    }
-  }
-};
-// tile -> two accumulators: acc_h (+)= x o key_h for 2^R consecutive indices (last forward pass of a giant step)
-struct AccSt32 {
-  uint32_t *acc0, *acc1;
-  const uint32_t *kw0, *kq0, *kw1, *kq1;
-  uint32_t p, p2;
-  bool first;
-  template <int R, int STR, int RI>
-  __device__ __forceinline__ void operator()(const uint32_t (&x)[1 << R], int g) const {
-    static_assert(STR == 1 && R >= 2, "accumulation belongs to the stride-1 pass");
-#pragma unroll
-    for (int hh = 0; hh < 2; hh++) {
-      uint32_t *acc = hh ? acc1 : acc0;
-      const uint4 *w4 = reinterpret_cast<const uint4 *>((hh ? kw1 : kw0) + g), *q4 = reinterpret_cast<const uint4 *>((hh ? kq1 : kq0) + g);
-#pragma unroll
-      for (int e = 0; e < (1 << R) / 4; e++) {
-        const uint4 m = __ldg(&w4[e]), c = __ldg(&q4[e]);
-        uint32_t v[4] = {shoup32(x[4 * e], m.x, c.x, p), shoup32(x[4 * e + 1], m.y, c.y, p), shoup32(x[4 * e + 2], m.z, c.z, p),
-                         shoup32(x[4 * e + 3], m.w, c.w, p)};
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-          const int idx = pidx32(g + 4 * e + u);
-          acc[idx] = first ? v[u] : csub32(v[u] + acc[idx], p2);             // below 2q
-        }
-      }
-    }
-  }
-};
-
-// Baby rotations of he_gemv (he-algo.c:66-68) on the 30-bit limbs: ONE decomposition and forward transform of ct.c1 per limb,
-// then per rotation j and half h the permuted product with rk[j] and an inverse transform (same identity as k_ks_baby).
-//   chat32[j][b][h][i][N] = y-weighted invntt( perm_j( ntt(c1 mod q_i) ) o rk[j].p_h[i] ),  lazily reduced (below 2q)
-// The coefficients are decomposed inside the first forward pass and every product is formed inside the first inverse pass.
 template <int LOGN>
 __global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_KSB_MINB)
 k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const __grid_constant__ Baby32 S, unsigned m, unsigned mkey,
@@ -768,21 +565,29 @@ k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const _
   typedef Cfg32<LOGN> G;
   extern __shared__ __align__(16) uint32_t sm32[];
   uint32_t *smA = sm32, *smB = sm32 + G::SMEM_WORDS;
+  // (limb-major CTA order -- CTAs resident together share a prime, its twiddles and keys -- measured slower: 4.36 vs 4.28 ms)
   const unsigned b = blockIdx.x / m, i = blockIdx.x % m;
   const uint32_t p = T.primes[i].p, p2 = 2 * p;
   const uint2 *pw = dec32 + (size_t)i * decstride;
   const uint32_t negW = p - __ldg(&pw[2 * W]).x;
   const uint64_t *poly = src + (size_t)b * src_bstride;
-  fwd32x<LOGN, 0>(smA, T.tw + (size_t)i * G::N, p, WordsLd32{poly, pw, W, (unsigned)G::N, p, p2, negW}, SmSt32{smA});
-  __syncthreads();
+  for (int c = threadIdx.x; c < G::N; c += G::THREADS) smA[pidx32(c)] = decompose32(poly, c, W, G::N, pw, p, p2, negW);
+  ntt32_forward<LOGN>(smA, T.tw + (size_t)i * G::N, p);
   const uint2 *itw = T.itw + (size_t)i * G::N;
 #pragma unroll 1
   for (unsigned j = 0; j < S.nj; j++) {
+    const uint16_t *perm = S.perm[j];
 #pragma unroll 1
     for (int h = 0; h < 2; h++) {
-      const uint32_t *kw = S.key[j] + ((size_t)h * mkey + i) * 2 * G::N;
-      inv32x<LOGN, 0>(smB, itw, p, PermKeyLd32{smA, S.perm[j], kw, kw + G::N, p},
-                      StrideSt32{chat + (size_t)j * chat_jstride + (((size_t)b * 2 + h) * m + i) * G::N});
+      const uint32_t *kw = S.key[j] + ((size_t)h * mkey + i) * 2 * G::N, *kq = kw + G::N;
+#pragma unroll 4
+      for (int c = threadIdx.x; c < G::N; c += G::THREADS) {
+        const unsigned s = __ldg(&perm[c]);
+        smB[pidx32(c)] = shoup32(smA[pidx32(s)], __ldg(&kw[c]), __ldg(&kq[c]), p);      // below 2q
+      }
+      ntt32_inverse<LOGN>(smB, itw, p);
+      uint32_t *dst = chat + (size_t)j * chat_jstride + (((size_t)b * 2 + h) * m + i) * G::N;
+      for (int c = threadIdx.x; c < G::N; c += G::THREADS) __stcs(&dst[c], smB[pidx32(c)]);
       __syncthreads();                                       // smB is refilled
     }
   }
@@ -791,15 +596,14 @@ k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const _
 // Giant steps of he_gemv (he-algo.c:80-84) on the 30-bit limbs, summed over the giant steps in the transform domain (the
 // 30-bit twin of k_ks_limb_sum):
 //   chatX[b][h][i][N] = y-weighted invntt( sum_g ntt( sigma_g(inner_g[b].c1) mod q_i ) o rk[g n1].p_h[i] )
-// sigma_g is a scatter through shared memory (coalesced reads); the key products are accumulated inside the last forward pass.
 template <int LOGN>
 __global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_KSS_MINB)
 k32_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src_gstride, int W, const __grid_constant__ Groups32 S,
                 unsigned ng, unsigned m, unsigned mkey, const uint2 *__restrict__ dec32, unsigned decstride, uint32_t *__restrict__ chatX, Tables32 T) {
   typedef Cfg32<LOGN> G;
   extern __shared__ __align__(16) uint32_t sm32[];
-  uint32_t *smA = sm32, *acc0 = sm32 + G::SMEM_WORDS, *acc1 = sm32 + 2 * G::SMEM_WORDS;
-  const unsigned b = blockIdx.x / m, i = blockIdx.x % m;
+  uint32_t *smA = sm32;
+  const unsigned b = blockIdx.x / m, i = blockIdx.x % m;      // (limb-major order measured slower: 4.92 vs 4.33 ms)
   const uint32_t p = T.primes[i].p, p2 = 2 * p;
   const uint2 *pw = dec32 + (size_t)i * decstride;
   const uint32_t negW = p - __ldg(&pw[2 * W]).x;
@@ -814,16 +618,27 @@ k32_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src
       const unsigned k = ((unsigned)c * ge) & (2 * G::N - 1);
       smA[pidx32(k & (G::N - 1))] = (k >= (unsigned)G::N) ? 3 * p - v : v;
     }
-    __syncthreads();
-    const uint32_t *k0 = S.key[g] + ((size_t)0 * mkey + i) * 2 * G::N, *k1 = S.key[g] + ((size_t)1 * mkey + i) * 2 * G::N;
-    fwd32x<LOGN, 0>(smA, tw, p, SmLd32{smA}, AccSt32{acc0, acc1, k0, k0 + G::N, k1, k1 + G::N, p, p2, g == 0});
-    __syncthreads();                                         // smA is refilled; each accumulator word belongs to one thread
+    ntt32_forward<LOGN>(smA, tw, p);
+#pragma unroll 1
+    for (int h = 0; h < 2; h++) {
+      uint32_t *acc = sm32 + (size_t)(1 + h) * G::SMEM_WORDS;
+      const uint32_t *kw = S.key[g] + ((size_t)h * mkey + i) * 2 * G::N, *kq = kw + G::N;
+#pragma unroll 4
+      for (int c = threadIdx.x; c < G::N; c += G::THREADS) {
+        uint32_t v = shoup32(smA[pidx32(c)], __ldg(&kw[c]), __ldg(&kq[c]), p);          // below 2q
+        if (g) v = csub32(v + acc[pidx32(c)], p2);
+        acc[pidx32(c)] = v;
+      }
+    }
+    __syncthreads();                                         // smA is refilled; the accumulators are thread-private
   }
   const uint2 *itw = T.itw + (size_t)i * G::N;
 #pragma unroll 1
   for (int h = 0; h < 2; h++) {
-    uint32_t *acc = h ? acc1 : acc0;
-    inv32x<LOGN, 0>(acc, itw, p, SmLd32{acc}, StrideSt32{chatX + (((size_t)b * 2 + h) * m + i) * G::N});
+    uint32_t *acc = sm32 + (size_t)(1 + h) * G::SMEM_WORDS;
+    ntt32_inverse<LOGN>(acc, itw, p);
+    uint32_t *dst = chatX + (((size_t)b * 2 + h) * m + i) * G::N;
+    for (int c = threadIdx.x; c < G::N; c += G::THREADS) __stcs(&dst[c], acc[pidx32(c)]);
   }
 }
 
