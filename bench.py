@@ -279,6 +279,14 @@ def run_ours(args):
     if world != args.gpus and world > 1:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     torch.cuda.set_device(local)
+    affinity = "unchanged"
+    try:                                   # run (and first-touch the pinned staging buffers) on the CPUs next to this rank's GPU: with one
+        import pynvml                      # process per GPU the host copies of 8 ranks otherwise cross the socket interconnect
+        pynvml.nvmlInit()
+        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local))
+        affinity = f"nvmlDeviceSetCpuAffinity: {len(os.sched_getaffinity(0))} CPUs"
+    except Exception as ex:  # pragma: no cover
+        affinity = f"unchanged ({type(ex).__name__})"
     if world > 1:
         os.environ.setdefault("NCCL_DEBUG", "WARN")      # keeps NCCL's version banner off stdout (one JSON line only)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -444,7 +452,7 @@ def run_ours(args):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "api": "hb_ctr_hempc_submit_host / hb_ctr_hempc_wait (pinned host buffers in and out; step k+1 is submitted before step k "
                        "is waited for, so its upload overlaps the evaluation of step k; every launch keeps the full per-GPU batch)",
-                "result_equals_device_resident_run": e2e_same,
+                "result_equals_device_resident_run": e2e_same, "host_affinity": affinity,
                 "results_end_in": "each rank's own pinned host buffer (one process per GPU, no gather on this path)" if world > 1 else "the caller's pinned host buffer",
                 "single_blocking_call": {"api": "hb_ctr_hempc_eval_host (chunks pipelined inside one call)",
                                          "value": total / e2e_call_s, "unit": UNIT}},
