@@ -107,6 +107,7 @@ struct hb_ctx {
   struct HybBasis { unsigned m = 0, Mbits = 0; ulonglong2 *dec59 = nullptr; uint2 *dec32 = nullptr; hbdev::KsHyb F; };
   std::map<unsigned, HybBasis> hyb; // constants of M = P * Q_m, by m
   bool no_hyb = false;              // HB_GEMV_NOHYB=1: every key-switch limb on the reference's 59-bit primes
+  bool no_pair = false;             // HB_HEMPC_NOPAIR=1: ctr_hempc's two matrix-vector products as two passes
   bool no_sum = false;              // HB_GEMV_NOSUM=1: one tail per giant step (A/B timing, tests)
   bool no_skip = false;             // HB_GEMV_NOSKIP=1: evaluate identically zero giant steps too
   std::vector<uint64_t> enc_host;   // [WC][N] scratch for hb_he_ecd / gemv plans
@@ -207,16 +208,16 @@ struct Launch32 {
     if (canon) launch(c, "k32_poly_ntt", hb32::k32_poly_ntt<LOGN, true>, (unsigned)(npoly * D), G::THREADS, G::SMEM_BYTES, 1, src, stride, W, out, c->dt32, D);
     else launch(c, "k32_poly_ntt", hb32::k32_poly_ntt<LOGN, false>, (unsigned)(npoly * D), G::THREADS, G::SMEM_BYTES, 1, src, stride, W, out, c->dt32, D);
   }
-  static void mulacc_intt(hb_ctx *c, const uint32_t *hat, size_t jstride, const uint32_t *pthat, size_t gstride, const hbdev::GroupMap &GM,
-                          unsigned n1, unsigned ngroups, uint32_t *chat, unsigned D, unsigned batch) {
+  static void mulacc_intt(hb_ctx *c, const uint32_t *hat, size_t jstride, const uint32_t *pthat, const uint32_t *pthat_b, unsigned q_split,
+                          size_t gstride, const hbdev::GroupMap &GM, unsigned n1, unsigned ngroups, uint32_t *chat, unsigned D, unsigned batch) {
     if (gstride == (size_t)n1 * D && (n1 == 2 || n1 == 4) && G::N >= 1024) {      // rotated transforms read once, in registers
       const unsigned grid = (unsigned)((size_t)batch * 2 * D);
-      if (n1 == 4) launch(c, "k32_mulacc_intt_all", hb32::k32_mulacc_intt_all<LOGN, 4>, grid, G::THREADS, G::SMEM_BYTES, 1, hat, jstride, pthat, gstride, GM, ngroups, batch * 2, chat, c->dt32, D);
-      else launch(c, "k32_mulacc_intt_all", hb32::k32_mulacc_intt_all<LOGN, 2>, grid, G::THREADS, G::SMEM_BYTES, 1, hat, jstride, pthat, gstride, GM, ngroups, batch * 2, chat, c->dt32, D);
+      if (n1 == 4) launch(c, "k32_mulacc_intt_all", hb32::k32_mulacc_intt_all<LOGN, 4>, grid, G::THREADS, G::SMEM_BYTES, 1, hat, jstride, pthat, pthat_b, q_split, gstride, GM, ngroups, batch * 2, chat, c->dt32, D);
+      else launch(c, "k32_mulacc_intt_all", hb32::k32_mulacc_intt_all<LOGN, 2>, grid, G::THREADS, G::SMEM_BYTES, 1, hat, jstride, pthat, pthat_b, q_split, gstride, GM, ngroups, batch * 2, chat, c->dt32, D);
       return;
     }
     launch(c, "k32_mulacc_intt", hb32::k32_mulacc_intt<LOGN>, (unsigned)((size_t)ngroups * batch * 2 * D), G::THREADS, G::SMEM_BYTES, 1, hat, jstride,
-           pthat, gstride, GM, n1, batch * 2, chat, c->dt32, D);
+           pthat, pthat_b, q_split, gstride, GM, n1, batch * 2, chat, c->dt32, D);
   }
 };
 template <int LOGN>
@@ -261,9 +262,12 @@ static void do32_poly_ntt(hb_ctx *c, const uint64_t *src, size_t stride, int W, 
   switch (c->ht.logn) { HB_LOGN32_CASES(X) default: hb_die("logn=%u has no 30-bit path", c->ht.logn); }
 #undef X
 }
-static void do32_mulacc_intt(hb_ctx *c, const uint32_t *hat, size_t jstride, const uint32_t *pthat, size_t gstride, const hbdev::GroupMap &GM,
-                             unsigned n1, unsigned ngroups, uint32_t *chat, unsigned D, unsigned batch) {
-#define X(L) case L: Launch32<L>::mulacc_intt(c, hat, jstride, pthat, gstride, GM, n1, ngroups, chat, D, batch); break;
+// pthat_b != nullptr: the second half of the batch (instances >= batch / 2) multiplies the diagonals pthat_b
+static void do32_mulacc_intt(hb_ctx *c, const uint32_t *hat, size_t jstride, const uint32_t *pthat, const uint32_t *pthat_b, size_t gstride,
+                             const hbdev::GroupMap &GM, unsigned n1, unsigned ngroups, uint32_t *chat, unsigned D, unsigned batch) {
+  const unsigned q_split = pthat_b ? batch : 2 * batch;        // in polynomials (two per instance)
+  if (!pthat_b) pthat_b = pthat;
+#define X(L) case L: Launch32<L>::mulacc_intt(c, hat, jstride, pthat, pthat_b, q_split, gstride, GM, n1, ngroups, chat, D, batch); break;
   switch (c->ht.logn) { HB_LOGN32_CASES(X) default: hb_die("logn=%u has no 30-bit path", c->ht.logn); }
 #undef X
 }
@@ -647,6 +651,8 @@ extern "C" hb_ctx *hb_ctx_create(unsigned logn, unsigned logq, unsigned slots, u
     ctx->exact_tail = e && *e && *e != '0';
     e = getenv("HB_GEMV_NOHOIST");
     ctx->no_hoist = e && *e && *e != '0';
+    e = getenv("HB_HEMPC_NOPAIR");
+    ctx->no_pair = e && *e && *e != '0';
     e = getenv("HB_GEMV_NOHYB");
     ctx->no_hyb = e && *e && *e != '0';
     e = getenv("HB_GEMV_NOSUM");
@@ -1426,6 +1432,26 @@ static const GemvPlan &gemv_plan(hb_ctx *ctx, const double *A, unsigned l) {
   return ctx->plans.back();
 }
 
+// bookkeeping fields of he_gemv's result (level l -> l - 1) exactly as the reference's calls update them, for an input with (nu, B):
+// he_mulpt, he_add over the n1 baby steps, he_rot, he_add over the n2 giant steps, he_rs (he-algo.c:57-90, precomp.c:417)
+static void gemv_meta(const hb_ctx *ctx, double nu_in, double B_in, unsigned n1, unsigned n2, double *nu_out, double *B_out) {
+  const hb::HostTables &h = ctx->ht;
+  const double Delta = std::ldexp(1.0, (int)h.logDelta);
+  double inu = 0, iB = 0, onu = 0, oB = 0;
+  for (unsigned i = 0; i < n2; i++) {
+    for (unsigned j = 0; j < n1; j++) {
+      const double nu = nu_in * Delta, B = B_in * Delta;
+      if (!j) { inu = nu; iB = B; }
+      else { inu = inu >= nu ? inu : nu; iB = iB + B; }
+    }
+    if (!i) { onu = inu; oB = iB; }
+    else { onu = onu >= inu ? onu : inu; oB = oB + iB; }
+  }
+  const double nn = h.N, Brs = std::sqrt(nn / 3.) * (3 + 8 * std::sqrt(64.0));
+  *nu_out = onu / Delta;
+  *B_out = oB / Delta + Brs;
+}
+
 // The reference schedule, one he_* call after the other (he-algo.c:57-87).
 static void gemv_stepwise(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_ct *ct, const hb_evk *rk, unsigned n1, unsigned n2) {
   const hb::HostTables &h = ctx->ht;
@@ -1477,8 +1503,15 @@ static const uint16_t *perm_table(hb_ctx *ctx, unsigned g) {
 // transform of ct.c1 (k_ks_baby) --, transformed once (hat_j = ntt(decompose(rot_j))), and each giant step sums its n1
 // diagonal products in the NTT domain before one inverse transform and one reconstruction (k_mulacc_intt).  Every
 // he_swk rounding of the reference is still performed on the same integers, so the result is bit-identical.
-static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_ct *ct, const hb_evk *rk, unsigned n1, unsigned n2) {
+// planB != nullptr: TWO matrix-vector products in one pass -- the first half of the batch (instances < batch / 2) is multiplied by
+// plan's matrix, the second half by planB's (ctr_hempc's Ka (xhat - xr) and Kb (uhat - ur), src/hempc.c:257-259).  Only the
+// diagonal products know which matrix an instance belongs to; rotations, key switches and the rescale are the same launches
+// over twice the batch.  The caller sets the bookkeeping fields of the two halves (gemv_meta); dst->nu / dst->B are plan's.
+static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_ct *ct, const hb_evk *rk, unsigned n1, unsigned n2,
+                       const GemvPlan *planB = nullptr) {
   const hb::HostTables &h = ctx->ht;
+  if (planB && !(plan.use32 && planB->use32 && plan.D == planB->D && plan.D32 == planB->D32 && ct->batch % 2 == 0))
+    hb_die("internal: paired matvec needs two plans on the 30-bit basis with equal limb counts");
   const double Delta = std::ldexp(1.0, (int)h.logDelta);
   const unsigned batch = ct->batch, D = plan.D, l = ct->l;
   const int W = hb::words_of_level(h, l), k = h.logq_l[l];
@@ -1493,6 +1526,7 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
   const size_t jstride32 = plan.use32 ? (size_t)batch * 2 * plan.D32 * N : 0;
   const size_t hat_bytes = std::max((size_t)n1 * jstride * 8, (size_t)n1 * jstride32 * 4);
   uint64_t *hat = ws_get(ctx, ctx->wsC, ctx->wsC_bytes, hat_bytes);
+  if (planB && !grouped) hb_die("internal: paired matvec outside the grouped schedule");
   if (!grouped) {
     // one launch per rotation and per giant step (A/B timing, very large rings)
     hb_ct inner, outer, rot;
@@ -1588,17 +1622,21 @@ static void gemv_fused(hb_ctx *ctx, hb_ct *dst, const GemvPlan &plan, const hb_c
   hbdev::GroupMap GM;
   memset(&GM, 0, sizeof GM);
   unsigned ngs = 0;
-  if (!ctx->no_skip && !plan.giant_nz.empty())
-    for (unsigned i : plan.giant_nz) GM.idx[ngs++] = i;
-  else
-    for (unsigned i = 0; i < n2; i++) GM.idx[ngs++] = i;
+  {
+    std::vector<bool> need(n2, false);                       // a giant step is skipped only if it is zero for every matrix involved
+    for (unsigned i : plan.giant_nz) need[i] = true;
+    if (planB) for (unsigned i : planB->giant_nz) need[i] = true;
+    const bool any = std::find(need.begin(), need.end(), true) != need.end();
+    for (unsigned i = 0; i < n2; i++)
+      if (ctx->no_skip || !any || need[i]) GM.idx[ngs++] = i;
+  }
   uint64_t *inner = cts;                                           // [ngs][batch][2][W][N]
   if (plan.use32) {
     // 2-3 on the internal 30-bit basis (twice the butterfly throughput per modulus bit; same integers, hb_tables32.hpp)
     const unsigned D32 = plan.D32;
     uint32_t *hat32 = (uint32_t *)hat, *mchat32 = (uint32_t *)chat;       // sized above for either layout
     do32_poly_ntt(ctx, cts, polyw, W, hat32, D32, (size_t)n1 * batch * 2, false);
-    do32_mulacc_intt(ctx, hat32, jstride32, plan.pthat32, (size_t)n1 * D32, GM, n1, ngs, mchat32, D32, batch);
+    do32_mulacc_intt(ctx, hat32, jstride32, plan.pthat32, planB ? planB->pthat32 : nullptr, (size_t)n1 * D32, GM, n1, ngs, mchat32, D32, batch);
     do32_recon_smod(ctx, mchat32, D32, inner, W, k, (size_t)ngs * batch * 2);
   } else {
     // 2. transform the rotated ciphertexts once
@@ -1720,31 +1758,63 @@ extern "C" void hb_ctr_hempc_eval(hb_ctx *ctx, hb_ct *up, const double *Ka, cons
                                   const hb_ct *xr, const hb_ct *uhat, const hb_ct *ur, const hb_evk *rk) { use_device(ctx);
   same_shape(xhat, xr, "hb_ctr_hempc_eval"); same_shape(uhat, ur, "hb_ctr_hempc_eval");
   same_shape(xhat, uhat, "hb_ctr_hempc_eval"); same_shape(up, xhat, "hb_ctr_hempc_eval");
-  const unsigned batch = xhat->batch;
-  hb_ct xdiff, udiff, KaX, KbU;
-  ct_alloc_tmp(ctx, &xdiff, batch); ct_alloc_tmp(ctx, &udiff, batch); ct_alloc_tmp(ctx, &KaX, batch);
-  ct_alloc_tmp(ctx, &KbU, batch);
+  const hb::HostTables &h = ctx->ht;
+  const unsigned batch = xhat->batch, S = h.slots;
+  if (xhat->l != uhat->l || xhat->l == 0) hb_die("hb_ctr_hempc_eval: operands are at different levels");
+  const unsigned l = xhat->l;
+  const int W = hb::words_of_level(h, l), Wout = hb::words_of_level(h, l - 1), kout = h.logq_l[l - 1];
+  const size_t N = h.N;
+  // Both differences and both matrix-vector products live in ONE batch of 2 x batch instances: first half x, second half u.
+  hb_ct diff2, out2;
+  ct_alloc_tmp(ctx, &diff2, 2 * batch);
+  ct_alloc_tmp(ctx, &out2, 2 * batch);
+  hb_ct xdiff = diff2, udiff = diff2, KaX = out2, KbU = out2;
+  xdiff.batch = udiff.batch = KaX.batch = KbU.batch = batch;
+  udiff.words = diff2.words + (size_t)batch * 2 * W * N;
+  KbU.words = out2.words + (size_t)batch * 2 * Wout * N;
   hb_he_sub(ctx, &xdiff, xhat, xr);              // hempc.c:253
   hb_he_sub(ctx, &udiff, uhat, ur);              // hempc.c:255
-  hb_he_gemv(ctx, &KaX, Ka, &xdiff, rk);         // hempc.c:257
-  hb_he_gemv(ctx, &KbU, Kb, &udiff, rk);         // hempc.c:259
+  unsigned n1 = (unsigned)std::sqrt((double)S);
+  if (S != n1 * n1) n1 = (unsigned)std::sqrt((double)(2 * S));
+  const unsigned n2 = S / n1;
+  gemv_plan(ctx, Ka, l);
+  gemv_plan(ctx, Kb, l);
+  const GemvPlan *pa = &gemv_plan(ctx, Ka, l);    // Ka's plan may have been evicted by Kb's: this lookup settles the cache ...
+  const GemvPlan *pb = &gemv_plan(ctx, Kb, l);    // ... and this one is a hit that moves nothing
+  hb_ct sepA, sepB;
+  sepA.words = sepB.words = nullptr;
+  const bool pair = !ctx->no_pair && !ctx->stepwise && !ctx->no_hoist && pa->fused && pb->fused && pa->use32 && pb->use32 && pa->D == pb->D &&
+                    pa->D32 == pb->D32 && n1 <= HB_MAX_GROUPS && n2 <= HB_MAX_GROUPS;
+  if (pair) {
+    diff2.l = l; diff2.nu = xdiff.nu; diff2.B = xdiff.B;
+    gemv_fused(ctx, &out2, *pa, &diff2, rk, n1, n2, pb);      // hempc.c:257 and :259 in one pass
+    KaX.l = KbU.l = out2.l;
+    gemv_meta(ctx, xdiff.nu, xdiff.B, n1, n2, &KaX.nu, &KaX.B);
+    gemv_meta(ctx, udiff.nu, udiff.B, n1, n2, &KbU.nu, &KbU.B);
+  } else {
+    // two passes into buffers of their own: he_rs inside the call-by-call schedule swaps its handle's buffer
+    ct_alloc_tmp(ctx, &sepA, batch);
+    ct_alloc_tmp(ctx, &sepB, batch);
+    hb_he_gemv(ctx, &sepA, Ka, &xdiff, rk);      // hempc.c:257
+    hb_he_gemv(ctx, &sepB, Kb, &udiff, rk);      // hempc.c:259
+    KaX = sepA; KbU = sepB;
+  }
   // hempc.c:261-266: he_add(du, KaX, KbU); he_neg(du); he_copy_ct(ucopy, uhat); he_moddown(ucopy); he_add(up, ucopy, du) -- all
   // of it arithmetic mod q_{l-1} followed by centring, so one pass computes smod(uhat - KaX - KbU, q_{l-1}); the bookkeeping
   // fields follow the five calls
-  if (KaX.l != KbU.l || uhat->l == 0 || KaX.l != uhat->l - 1) hb_die("hb_ctr_hempc_eval: operands are at different levels");
+  if (KaX.l != KbU.l || KaX.l != l - 1) hb_die("hb_ctr_hempc_eval: operands are at different levels");
   {
-    const hb::HostTables &h = ctx->ht;
     const double du_nu = KaX.nu >= KbU.nu ? KaX.nu : KbU.nu, du_B = KaX.B + KbU.B;
     up->l = KaX.l;
     up->nu = uhat->nu >= du_nu ? uhat->nu : du_nu;
     up->B = uhat->B + du_B;
-    const int Wu = hb::words_of_level(h, uhat->l), Wout = hb::words_of_level(h, up->l), kout = h.logq_l[up->l];
     const size_t npoly = (size_t)batch * 2, total = npoly * h.N;
-    launch(ctx, "k_ct_combine", hbdev::k_ct_combine, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint64_t *)uhat->words, Wu,
+    launch(ctx, "k_ct_combine", hbdev::k_ct_combine, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint64_t *)uhat->words, W,
            (const uint64_t *)KaX.words, (const uint64_t *)KbU.words, up->words, Wout, kout, h.N, npoly);
   }
-  hb_ct_free(ctx, &xdiff); hb_ct_free(ctx, &udiff); hb_ct_free(ctx, &KaX);
-  hb_ct_free(ctx, &KbU);
+  hb_ct_free(ctx, &diff2);
+  hb_ct_free(ctx, &out2);
+  if (sepA.words) { hb_ct_free(ctx, &sepA); hb_ct_free(ctx, &sepB); }
 }
 
 // End to end from host buffers.  The batch is cut into chunks that flow through three streams -- upload (copy stream),

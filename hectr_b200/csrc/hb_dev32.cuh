@@ -227,11 +227,13 @@ __global__ void k32_shoup_prep(const uint32_t *__restrict__ in, uint32_t *__rest
 // ---------------------------------------------------------------------------------------------------------------
 template <int LOGN>
 __global__ void __launch_bounds__(Cfg32<LOGN>::THREADS)
-k32_mulacc_intt(const uint32_t *__restrict__ hat, size_t hat_jstride, const uint32_t *__restrict__ pthat_all, size_t pthat_gstride,
-                const __grid_constant__ hbdev::GroupMap GM, unsigned n1, unsigned nq, uint32_t *__restrict__ chat, Tables32 T, unsigned D) {
+k32_mulacc_intt(const uint32_t *__restrict__ hat, size_t hat_jstride, const uint32_t *__restrict__ pthat_a, const uint32_t *__restrict__ pthat_b,
+                unsigned q_split, size_t pthat_gstride, const __grid_constant__ hbdev::GroupMap GM, unsigned n1, unsigned nq,
+                uint32_t *__restrict__ chat, Tables32 T, unsigned D) {
   typedef Cfg32<LOGN> G;
   extern __shared__ __align__(16) uint32_t sm32[];
   const unsigned qq = blockIdx.x / D, d = blockIdx.x % D, q = qq % nq;
+  const uint32_t *pthat_all = q < q_split ? pthat_a : pthat_b;
   const uint32_t p = T.primes[d].p, p2 = 2 * p;
   const uint32_t *a = hat + ((size_t)q * D + d) * G::N;
   const uint32_t *w = pthat_all + ((size_t)GM.idx[qq / nq] * pthat_gstride + d) * 2 * G::N;       // strides in limbs
@@ -369,12 +371,16 @@ k32_poly_ntt_all(const uint64_t *__restrict__ src, size_t poly_stride, uint32_t 
 // giant step g < ngroups:  chat[g][q][d] = y-weighted invntt( sum_j hat[j][q][d] o pthat[g*NJ + j][d] ).
 template <int LOGN, int NJ>
 __global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_MA_MINB)
-k32_mulacc_intt_all(const uint32_t *__restrict__ hat, size_t hat_jstride, const uint32_t *__restrict__ pthat_all, size_t pthat_gstride,
-                    const __grid_constant__ hbdev::GroupMap GM, unsigned ngroups, unsigned nq, uint32_t *__restrict__ chat, Tables32 T, unsigned D) {
+k32_mulacc_intt_all(const uint32_t *__restrict__ hat, size_t hat_jstride, const uint32_t *__restrict__ pthat_a, const uint32_t *__restrict__ pthat_b,
+                    unsigned q_split, size_t pthat_gstride, const __grid_constant__ hbdev::GroupMap GM, unsigned ngroups, unsigned nq,
+                    uint32_t *__restrict__ chat, Tables32 T, unsigned D) {
+  // polynomials q < q_split multiply the diagonals pthat_a, the others pthat_b: the two matrix-vector products of ctr_hempc
+  // (src/hempc.c:257-259) share every launch (q_split = nq: one matrix)
   typedef Cfg32<LOGN> G;
   constexpr int V = G::N / 4 / G::THREADS;                    // uint4 per thread
   extern __shared__ __align__(16) uint32_t sm32[];
   const unsigned q = blockIdx.x / D, d = blockIdx.x % D;
+  const uint32_t *pthat_all = q < q_split ? pthat_a : pthat_b;
   const uint32_t p = T.primes[d].p, p2 = 2 * p;
   uint4 h[NJ][V];
 #pragma unroll

@@ -2,15 +2,15 @@
 # GPU call: full test suite, bench line, A/B without the hybrid basis, per-kernel times
 set -u
 mkdir -p gpurun_out
-timeout 2400 python -m pytest tests -m gpu -q -x --durations=8 > gpurun_out/pytest5.log 2>&1
-echo "pytest rc=$?" >> gpurun_out/pytest5.log
-grep -vE "^\s*$" gpurun_out/pytest5.log | tail -25 | cut -c1-300
+timeout 2400 python -m pytest tests -m gpu -q -x --durations=8 > gpurun_out/pytest6.log 2>&1
+echo "pytest rc=$?" >> gpurun_out/pytest6.log
+grep -vE "^\s*$" gpurun_out/pytest6.log | tail -25 | cut -c1-300
 FAST="--steps 8 --warmup 3 --no-ntt --no-cpu-baseline --no-closed-loop"
-timeout 600 python bench.py $FAST > gpurun_out/bench5.json 2> gpurun_out/bench5.err; echo "bench rc=$?"; tail -c 300 gpurun_out/bench5.err
-HB_GEMV_NOHYB=1 timeout 600 python bench.py $FAST --no-parity-spot > gpurun_out/bench5_nohyb.json 2>> gpurun_out/bench5.err
+timeout 600 python bench.py $FAST > gpurun_out/bench6.json 2> gpurun_out/bench6.err; echo "bench rc=$?"; tail -c 300 gpurun_out/bench6.err
+HB_HEMPC_NOPAIR=1 timeout 600 python bench.py $FAST --no-parity-spot > gpurun_out/bench6_nopair.json 2>> gpurun_out/bench6.err
 python - <<'PY'
 import json
-for f in ("bench5", "bench5_nohyb"):
+for f in ("bench6", "bench6_nopair"):
     try:
         d = [json.loads(l) for l in open(f"gpurun_out/{f}.json") if l.startswith("{")][-1]
         print(f, round(d["value"]), "it/s  e2e", round(d["e2e"]["value"]), "ms/step", round(d["ms_per_step"], 2), "parity", d.get("parity_spot"))

@@ -164,6 +164,33 @@ def test_gemv_shortcuts_equal_the_plain_schedule(cfgA, monkeypatch):
         plain.close()
 
 
+def test_paired_matvecs_equal_two_passes(cfgA, monkeypatch):
+    """hb_ctr_hempc_eval runs Ka (xhat - xr) and Kb (uhat - ur) as ONE pass over a batch of 2 x B instances (only the diagonal
+    products know which matrix an instance belongs to); HB_HEMPC_NOPAIR=1 keeps two passes.  Same words on 96 random
+    controller states, with the hempc block matrices and with dense ones (different sets of non-zero giant steps)."""
+    from hectr_b200 import Engine
+    eng, ref = cfgA["eng"], cfgA["ref"]
+    rk_arr = np.stack([ref.evk_to_array(cfgA["rk"][i]) for i in range(16)])
+    rng = np.random.default_rng(911)
+    monkeypatch.setenv("HB_HEMPC_NOPAIR", "1")
+    two = Engine(*A_PARAMS)
+    monkeypatch.delenv("HB_HEMPC_NOPAIR")
+    try:
+        keys2 = two.keys(rk_arr)
+        l = 2
+        w = [random_ct_words(rng, 96, eng.words(l), eng.n, eng.logq(l)) for _ in range(4)]
+        Ka, Kb = hempc_gains(rng)
+        dense = rng.standard_normal((16, 16)) + 1j * rng.standard_normal((16, 16))
+        for A, B in ((Ka, Kb), (dense, Kb), (Ka, dense)):
+            got = eng.ctr_hempc_eval(A, B, *[eng.ct(x, l) for x in w], cfgA["keys"])
+            want = two.ctr_hempc_eval(A, B, *[two.ct(x, l) for x in w], keys2)
+            assert got.l == want.l and got.nu == want.nu and got.B == want.B
+            assert np.array_equal(got.download(), want.download())
+        keys2.free()
+    finally:
+        two.close()
+
+
 def test_synthetic_keys_keep_the_per_step_tails(cfgA):
     """Uniform residues are not a switching key: their lift reaches P_D, the products wrap, and the sum of the wrapped
     reconstructions is not the reconstruction of the sum.  hb_evk_upload records the bound of every key (k_lift_bits) and
