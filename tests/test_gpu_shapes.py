@@ -191,6 +191,27 @@ def test_paired_matvecs_equal_two_passes(cfgA, monkeypatch):
         two.close()
 
 
+def test_streaming_host_interface(cfgA):
+    """hb_ctr_hempc_submit_host / hb_ctr_hempc_wait: four batches of different sizes and contents submitted back to back (two in
+    flight, the third submission waits for the first), waited for out of order; every result must equal the device-resident
+    evaluation of the same batch, and a larger batch after smaller ones regrows the persistent buffer sets."""
+    eng, keys = cfgA["eng"], cfgA["keys"]
+    rng = np.random.default_rng(1201)
+    l = 2
+    Ka, Kb = hempc_gains(rng)
+    sizes = (5, 9, 3, 17)
+    ins, outs, want = [], [], []
+    for nb in sizes:
+        w = [random_ct_words(rng, nb, eng.words(l), eng.n, eng.logq(l)) for _ in range(4)]
+        ins.append(w)
+        outs.append(np.zeros((nb, 2, eng.words(l - 1), eng.n), dtype=np.uint64))
+        want.append(eng.ctr_hempc_eval(Ka, Kb, *[eng.ct(x, l) for x in w], keys).download())
+    tickets = [eng.ctr_hempc_submit_host(Ka, Kb, *ins[i], keys, l, outs[i]) for i in range(len(sizes))]
+    for i in (1, 0, 3, 2):
+        eng.ctr_hempc_wait(tickets[i])
+        assert np.array_equal(outs[i], want[i]), i
+
+
 def test_synthetic_keys_keep_the_per_step_tails(cfgA):
     """Uniform residues are not a switching key: their lift reaches P_D, the products wrap, and the sum of the wrapped
     reconstructions is not the reconstruction of the sum.  hb_evk_upload records the bound of every key (k_lift_bits) and
