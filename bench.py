@@ -544,6 +544,10 @@ def finish_line(args, eng, keys, key_arr, secret, Ka, Kb, host, dev_out, prof, p
         cpus = cpu_baselines(args.cpu_evals)
         out["cpu_baseline"] = cpus.get("Og")
         out["cpu_baseline_O2"] = cpus.get("O2")
+        try:
+            out["cpu_baseline_all_cores"] = cpu_baseline_all_cores()
+        except Exception as ex:  # pragma: no cover
+            out["cpu_baseline_all_cores"] = {"error": repr(ex)}
     else:
         out["cpu_baseline"] = None
     if not args.no_ntt:
@@ -849,6 +853,39 @@ def cpu_baselines(n_eval=3):
                     "sample": f"{n_eval} single-instance ctr_hempc ciphertext evaluations (src/hempc.c:253-266) through "
                               f"oracle/_ref/libgpqhe{'_O2' if opt == 'O2' else ''}.so (unmodified reference), {dt:.1f} s"}
     return out
+
+
+def cpu_baseline_all_cores(per_proc=1):
+    """The unmodified reference (-Og) on ALL host cores: P = os.cpu_count() processes (threads are impossible: process-global
+    context), each evaluating `per_proc` instances after one warm-up evaluation; aggregate iterations/s, P stated."""
+    from oracle import ref as R
+    if not R.available():
+        return None
+    import multiprocessing as mp
+    mpctx = mp.get_context("spawn")
+    P = os.cpu_count() or 1
+    qs = [(mpctx.Queue(), mpctx.Queue()) for _ in range(P)]
+    procs = [mpctx.Process(target=_ref_worker, args=(qi, qo, "Og"), daemon=True) for qi, qo in qs]
+    for pr in procs:
+        pr.start()
+    for _, qo in qs:
+        qo.get()
+    for qi, _ in qs:
+        qi.put(1)
+    for _, qo in qs:
+        qo.get()
+    t0 = time.perf_counter()
+    for qi, _ in qs:
+        qi.put(per_proc)
+    for _, qo in qs:
+        qo.get()
+    dt = time.perf_counter() - t0
+    for qi, _ in qs:
+        qi.put(None)
+    for pr in procs:
+        pr.join(timeout=10)
+    return {"value": P * per_proc / dt, "unit": UNIT, "cores": P, "kind": "reference", "flags": "-Og -fomit-frame-pointer -DSUPERCOP",
+            "sample": f"{P} processes x {per_proc} ctr_hempc ciphertext evaluation(s), one process per host core, {dt:.1f} s"}
 
 
 def _ref_worker(q_in, q_out, opt):
