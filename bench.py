@@ -520,8 +520,10 @@ def finish_line(args, eng, keys, key_arr, secret, Ka, Kb, host, dev_out, prof, p
     roofline = {"bound": "hbm", "kernel": dom, "unit": "GB/s", "peak": peak, "peak_source": peak_src,
                 "achieved": du["achieved_gbs"], "frac": du["frac_of_hbm"], "traffic": traffic, "traffic_note": traffic_note,
                 "unit_of_work": dom_unit, "unit_kernels": du["kernels"],
-                "algorithmic_bytes_per_launch": du["algorithmic_bytes_per_gemv"],
-                "avg_launch_ms": sum(prof[kn]["ms"] for kn in du["kernels"]) / (2 * steps),
+                # one launch of the dominant kernel covers 2 / lps matrix-vector products (both of ctr_hempc's when they are paired)
+                "algorithmic_bytes_per_launch": du["algorithmic_bytes_per_gemv"] * 2 * steps / prof[dom]["launches"],
+                "avg_launch_ms": sum(prof[kn]["ms"] for kn in du["kernels"]) / prof[dom]["launches"],
+                "matvecs_per_launch": 2 * steps / prof[dom]["launches"],
                 "dominant_kernel_avg_launch_ms": prof[dom]["ms"] / prof[dom]["launches"],
                 "share_of_step": prof[dom]["ms"] / tot_ms,
                 "units": units,

@@ -12,7 +12,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-fil
     $DRV --case hempc --batch 4096 --reps 1 > "$O/ncu_launches.log" 2>&1
 echo "ncu launches rc=$?"
 ncu --set full --clock-control none --import-source on \
-    -k regex:'k_ks_limb|k_ks_baby|k32_ks|k_ks_finish|k32_mulacc_intt_all|k32_recon_smod4|k32_poly_ntt_all' -s 11 -c 11 \
+    -k regex:'k_ks_limb|k_ks_baby|k32_ks|k_ks_finish|k32_mulacc_intt_all|k32_recon_smod4|k32_poly_ntt_all' -s 9 -c 9 \
     -o "$O/prof_hempc" -f $DRV --case hempc --batch 4096 --reps 1 > "$O/ncu_full_hempc.log" 2>&1
 echo "ncu full hempc rc=$?"
 ncu --set full --clock-control none --import-source on -k regex:'k_ntt' -s 2 -c 2 \
