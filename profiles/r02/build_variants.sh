@@ -4,6 +4,8 @@ set -u
 cd "$(dirname "${BASH_SOURCE[0]}")/../.."
 mkdir -p build_variants
 build() { tag="$1"; shift; OUT="$PWD/build_variants/lib_$tag.so" bash hectr_b200/csrc/build.sh -DHB_DEV_FAST "$@" > "build_variants/$tag.log" 2>&1 && echo "ok $tag" || echo "FAILED $tag"; }
-build v_base &
-build v_limbmajor -DHB32_LIMB_MAJOR &
+build w_base &
+build w_tile1024 -DHB32_TILE_ORDER=1024 &
+build w_tile512_madmajor -DHB32_TILE_ORDER=512 -DHB32_MA_DMAJOR &
+build w_madmajor -DHB32_MA_DMAJOR &
 wait

@@ -1,0 +1,6 @@
+#!/usr/bin/env bash
+mkdir -p gpurun_out
+for v in build_variants/lib_*.so; do
+  [ -f "$v" ] || continue
+  echo "== $v"; HB_LIB="$PWD/$v" python profiles/prof_driver.py --case hempc --batch 4096 --reps 3 2>&1 | head -13
+done | tee gpurun_out/variants_run.log
