@@ -1056,6 +1056,7 @@ static const hb_ctx::HybBasis &hyb_basis(hb_ctx *ctx, unsigned m) {
     const hb::BigU Mhat = M.divmod_u64(pe, nullptr);
     const uint64_t mh = Mhat.mod_u64(pe), inv = hb::powmod(mh, pe - 2, pe);
     F.p[e] = pe; F.mu[e] = h.primes[e].mu;
+    F.rp[e] = (float)(4294967296.0 / (double)pe);
     fold2(Mhat, F.phat[e]);
     for (unsigned w = 0; w <= h.WC; w++) {
       const uint64_t c = hb::mulmod(h.pow64[(size_t)e * (h.WC + 1) + w], inv, pe);
@@ -1080,6 +1081,7 @@ static const hb_ctx::HybBasis &hyb_basis(hb_ctx *ctx, unsigned m) {
     const hb::BigU Qhat = M.divmod_u64(qi, nullptr);
     const uint64_t inv = hb::powmod(Qhat.mod_u64(qi), qi - 2, qi);
     F.q[i] = (uint32_t)qi; F.mu32[i] = g.primes[i].mu;
+    F.rq[i] = (float)(1.0 / (double)qi);
     fold2(Qhat, F.qhat[i]);
     for (unsigned w = 0; w < nd; w++) {
       const uint64_t c = hb::mulmod(g.pow32[((size_t)i * (g.ndig + 1) + w) * 2], inv, qi);

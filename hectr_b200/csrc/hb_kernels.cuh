@@ -933,6 +933,9 @@ k_ks_finish_sum(const uint64_t *__restrict__ chatP, size_t chatP_gstride, const 
 struct KsHyb {
   uint64_t p[4], mu[4], phat[4][2];                       // limbs of P: modulus, floor(2^120/p), M/p_e mod 2^128 (times P^-1)
   uint32_t q[HB_HYB_MAX32], mu32[HB_HYB_MAX32];           // 30-bit limbs: modulus, floor(2^61/q)
+  float rq[HB_HYB_MAX32], rp[4];                          // 1/q_i and 2^32/p_e: the rounding v = round(sum y/prime) is decided in
+                                                          // FP32 (|x| < M/8 keeps it 3/8 from a boundary; eleven terms err by < 1e-5),
+                                                          // on the FP32 pipe instead of eleven wide integer multiplies
   uint64_t qhat[HB_HYB_MAX32][2];                         // M/q_i mod 2^128 (times P^-1)
   uint64_t M[2];                                          // M mod 2^128 (times P^-1)
   uint64_t kinv[4], kinvq[4], kphat[4][2], kP[2];         // y_e -> z_e re-weighting, P/p_e and P mod 2^128 (times P^-1)
@@ -949,16 +952,27 @@ __device__ __forceinline__ void mac_low32(uint64_t (&acc)[2], uint32_t y, const 
   acc[1] += hi + (acc[0] < lo);
 }
 
-// x part of the hybrid tail for one coefficient: acc = sum y phat (mod 2^128), Fx = sum y / prime in units of 2^-56
+// 128-bit accumulators (the compiler's carry chains: IADD3.X, no compare / select pairs)
+typedef unsigned __int128 hb_u128;
+__device__ __forceinline__ hb_u128 u128_of(const uint64_t (&w)[2]) { return (((hb_u128)w[1]) << 64) | w[0]; }
+__device__ __forceinline__ void mac128(hb_u128 &acc, uint64_t y, const uint64_t (&w)[2]) {        // acc += y * w (mod 2^128)
+  acc += (hb_u128)y * w[0] + (((hb_u128)(y * w[1])) << 64);
+}
+__device__ __forceinline__ void mac128_32(hb_u128 &acc, uint32_t y, const uint64_t (&w)[2]) {     // the same for a 32-bit y
+  const uint64_t a = (uint64_t)y * lo32(w[0]), b = (uint64_t)y * hi32(w[0]);
+  acc += (hb_u128)a + (((hb_u128)b) << 32) + (((hb_u128)((uint64_t)y * lo32(w[1]) + (((uint64_t)(y * hi32(w[1]))) << 32))) << 64);
+}
+
+// x part of the hybrid tail for one coefficient: acc += sum y_i (M/q_i) (mod 2^128), fx += sum y_i / q_i (FP32)
 template <int DIM, int M32>
-__device__ __forceinline__ void hyb_x32(const uint32_t *__restrict__ limbs32, unsigned N, const KsHyb &F, uint64_t (&acc)[2], uint64_t &Fx) {
+__device__ __forceinline__ void hyb_x32(const uint32_t *__restrict__ limbs32, unsigned N, const KsHyb &F, hb_u128 &acc, float &fx) {
   uint32_t y[M32];
 #pragma unroll
   for (int i = 0; i < M32; i++) y[i] = __ldcs(&limbs32[(size_t)i * N]);
 #pragma unroll
   for (int i = 0; i < M32; i++) {
-    Fx += ((uint64_t)y[i] * F.mu32[i]) >> 5;
-    mac_low32(acc, y[i], F.qhat[i]);
+    fx = fmaf(__uint2float_rn(y[i]), F.rq[i], fx);
+    mac128_32(acc, y[i], F.qhat[i]);
   }
 }
 
@@ -985,34 +999,32 @@ k_ks_finish_hyb(const uint64_t *__restrict__ chat59, const uint32_t *__restrict_
   const uint64_t *limbs59 = chat59 + ((size_t)b * 2 + h) * DIM * N + i;
   const uint32_t *limbs32 = chat32 + ((size_t)b * 2 + h) * M32 * N + i;
   const uint64_t ONE = 1ULL << 56, HALF = 1ULL << 55, MASK = ONE - 1, MARGIN = 1ULL << 38;
-  uint64_t acc[2] = {0, 0}, Rl[2] = {0, 0}, Fx = 0, Fr = 0;
-  hyb_x32<DIM, M32>(limbs32, N, F, acc, Fx);
+  u128 acc = 0, Rl = 0;
+  uint64_t Fr = 0;
+  float fx = 0.5f;
+  hyb_x32<DIM, M32>(limbs32, N, F, acc, fx);
 #pragma unroll
   for (int e = 0; e < DIM; e++) {
     const uint64_t y = HB_LD(&limbs59[(size_t)e * N]);                   // below 2p
-    Fx += (uint64_t)hi32(y) * hi32(F.mu[e]);
-    mac_low<2>(acc, y, F.phat[e]);
+    fx = fmaf(__uint2float_rn(hi32(y)), F.rp[e], fx);
+    mac128(acc, y, F.phat[e]);
     const Mod m = make_mod(F.p[e]);
     const uint64_t z = shoup_lazy(y, F.kinv[e], F.kinvq[e], m);
     Fr += (uint64_t)hi32(z) * hi32(F.mu[e]);
-    mac_low<2>(Rl, z, F.kphat[e]);
+    mac128(Rl, z, F.kphat[e]);
   }
-  const uint64_t v = (Fx + HALF) >> 56;
-  uint64_t dlt[2] = {0, 0};
-  mac_low<2>(dlt, v, F.M);
-  u128 tt = ((((u128)acc[1]) << 64) | acc[0]) - ((((u128)dlt[1]) << 64) | dlt[0]);
+  const uint32_t v = (uint32_t)fx;                                       // round(sum y/prime): at most 2 (dim + m)
+  u128 tt = acc - u128_of(F.M) * v;
   const uint64_t fr = Fr & MASK;
   bool roundup;
   if (fr < MARGIN || fr > ONE - MARGIN || (fr > HALF - MARGIN && fr < HALF + MARGIN)) {
     uint64_t RP[2];
     hyb_R_slow<WPK>(limbs59, N, T, F.ztab, RP, roundup);
-    tt -= (((u128)RP[1]) << 64) | RP[0];
+    tt -= u128_of(RP);
   } else {
-    const uint64_t v2 = Fr >> 56;
+    const uint32_t v2 = (uint32_t)(Fr >> 56);
     roundup = fr > HALF;
-    uint64_t sub[2] = {0, 0};
-    mac_low<2>(sub, v2, F.kP);
-    tt -= ((((u128)Rl[1]) << 64) | Rl[0]) - ((((u128)sub[1]) << 64) | sub[0]);
+    tt -= Rl - u128_of(F.kP) * v2;
   }
   uint64_t t[2] = {(uint64_t)tt, (uint64_t)(tt >> 64)};
   ks_tail<2>(t, roundup, h ? add1 : add0, add_bstride, Wadd, ginv, N, b, badd, h, i, out, Wout, k);
@@ -1033,8 +1045,9 @@ k_ks_finish_sum_hyb(const uint64_t *__restrict__ chatP, size_t chatP_gstride, co
   const uint64_t *limbsP = chatP + ((size_t)b * 2 + h) * DIM * N + i;
   const uint32_t *limbs32 = chatX32 + ((size_t)b * 2 + h) * M32 * N + i;
   const uint64_t ONE = 1ULL << 56, HALF = 1ULL << 55, MASK = ONE - 1, MARGIN = 1ULL << 38;
-  uint64_t acc[2] = {0, 0}, Fx = 0;
-  hyb_x32<DIM, M32>(limbs32, N, F, acc, Fx);
+  u128 acc = 0;
+  float fx = 0.5f;
+  hyb_x32<DIM, M32>(limbs32, N, F, acc, fx);
   uint64_t ysum[DIM];
 #pragma unroll
   for (int e = 0; e < DIM; e++) ysum[e] = 0;
@@ -1042,7 +1055,8 @@ k_ks_finish_sum_hyb(const uint64_t *__restrict__ chatP, size_t chatP_gstride, co
   unsigned nround = 0;
 #pragma unroll 1
   for (unsigned g = 0; g < ng; g++) {
-    uint64_t Rl[2] = {0, 0}, Fr = 0;
+    u128 Rl = 0;
+    uint64_t Fr = 0;
     const uint64_t *lg = limbsP + (size_t)g * chatP_gstride;
 #pragma unroll
     for (int e = 0; e < DIM; e++) {
@@ -1051,32 +1065,28 @@ k_ks_finish_sum_hyb(const uint64_t *__restrict__ chatP, size_t chatP_gstride, co
       const Mod m = make_mod(F.p[e]);
       const uint64_t z = shoup_lazy(a, F.kinv[e], F.kinvq[e], m);
       Fr += (uint64_t)hi32(z) * hi32(F.mu[e]);
-      mac_low<2>(Rl, z, F.kphat[e]);
+      mac128(Rl, z, F.kphat[e]);
     }
     const uint64_t fr = Fr & MASK;
     if (fr < MARGIN || fr > ONE - MARGIN || (fr > HALF - MARGIN && fr < HALF + MARGIN)) {
       uint64_t RP[2];
       bool up;
       hyb_R_slow<WPK>(lg, N, T, F.ztab, RP, up);
-      Rsum += (((u128)RP[1]) << 64) | RP[0];
+      Rsum += u128_of(RP);
       nround += up ? 1u : 0u;
     } else {
-      const uint64_t v2 = Fr >> 56;
+      const uint32_t v2 = (uint32_t)(Fr >> 56);
       nround += fr > HALF ? 1u : 0u;
-      uint64_t sub[2] = {0, 0};
-      mac_low<2>(sub, v2, F.kP);
-      Rsum += ((((u128)Rl[1]) << 64) | Rl[0]) - ((((u128)sub[1]) << 64) | sub[0]);
+      Rsum += Rl - u128_of(F.kP) * v2;
     }
   }
 #pragma unroll
   for (int e = 0; e < DIM; e++) {
-    Fx += (uint64_t)hi32(ysum[e]) * hi32(F.mu[e]);
-    mac_low<2>(acc, ysum[e], F.phat[e]);
+    fx = fmaf(__uint2float_rn(hi32(ysum[e])), F.rp[e], fx);
+    mac128(acc, ysum[e], F.phat[e]);
   }
-  const uint64_t v = (Fx + HALF) >> 56;
-  uint64_t dlt[2] = {0, 0};
-  mac_low<2>(dlt, v, F.M);
-  u128 tt = ((((u128)acc[1]) << 64) | acc[0]) - ((((u128)dlt[1]) << 64) | dlt[0]) - Rsum + nround;
+  const uint32_t v = (uint32_t)fx;
+  u128 tt = acc - u128_of(F.M) * v - Rsum + nround;
   if (h == 0 && add0) {                                                  // sum_g sigma_g(inner_g.c0)
 #pragma unroll 1
     for (unsigned g = 0; g < ng; g++) {
