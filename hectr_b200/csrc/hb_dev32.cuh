@@ -41,6 +41,9 @@ struct Cfg32 {
 // one pad word per 32: a warp's 32 consecutive words, its 16-strided tiles and (with the lane swap in pass32) its two
 // 256-blocks of the middle pass all fall on 32 different banks
 __device__ __forceinline__ int pidx32(int i) { return i + (i >> 5); }
+// Thread tid's coefficients c = tid + k THREADS (THREADS a multiple of 32) sit at padded offsets pidx32(tid) + k PSTEP32: the loops
+// below index shared memory as base + k * constant instead of recomputing the padding per access.
+#define HB32_PSTEP(THREADS) ((THREADS) + ((THREADS) >> 5))
 
 // the 2^a consecutive twiddles of one stage of a tile, fetched 16 bytes at a time (the run starts at an even index)
 template <int CNT>
@@ -121,12 +124,32 @@ __device__ __forceinline__ void pass32(uint32_t *sm, const uint2 *__restrict__ t
     const int tile = (LOGST == 4 && TILES >= 64) ? ((t0 & ~0x30) | ((t0 & 0x10) << 1) | ((t0 & 0x20) >> 1)) : t0;
     const int b = tile >> LOGST, o = tile & (ST - 1), g = (b << LOGBLK) + o;
     uint32_t x[1 << R];
+    // Padded offsets of the tile's elements as base + compile-time constant, so that every access is one LDS / STS with an
+    // immediate: pidx32(g + t ST) = pidx32(g) + t (ST + ST/32) when 32 | ST; two interleaved bases when ST = 16; pidx32(g) + t
+    // for the 2^R <= 16 consecutive elements of the stride-1 pass (g is a multiple of 2^R: no carry into bit 5).
+    int off[1 << R];
+    if constexpr (LOGST >= 5) {
+      const int base = pidx32(g);
 #pragma unroll
-    for (int t = 0; t < (1 << R); t++) x[t] = sm[pidx32(g + t * ST)];
+      for (int t = 0; t < (1 << R); t++) off[t] = base + t * (ST + (ST >> 5));
+    } else if constexpr (LOGST == 4) {
+      const int b0 = pidx32(g), b1 = pidx32(g + 16);
+#pragma unroll
+      for (int t = 0; t < (1 << R); t++) off[t] = ((t & 1) ? b1 : b0) + (t >> 1) * 33;
+    } else if constexpr (LOGST == 0 && R <= 4) {
+      const int base = pidx32(g);
+#pragma unroll
+      for (int t = 0; t < (1 << R); t++) off[t] = base + t;
+    } else {
+#pragma unroll
+      for (int t = 0; t < (1 << R); t++) off[t] = pidx32(g + t * ST);
+    }
+#pragma unroll
+    for (int t = 0; t < (1 << R); t++) x[t] = sm[off[t]];
     if (INV) tile_inv32<R>(x, tw, (1u << S) + b, p);
     else tile_fwd32<R>(x, tw, (1u << S) + b, p);
 #pragma unroll
-    for (int t = 0; t < (1 << R); t++) sm[pidx32(g + t * ST)] = x[t];
+    for (int t = 0; t < (1 << R); t++) sm[off[t]] = x[t];
   }
 }
 
@@ -352,7 +375,7 @@ k32_poly_ntt_all(const uint64_t *__restrict__ src, size_t poly_stride, uint32_t 
       uint32_t acc = shoup32(dig[k][0], c[0].x, c[0].y, p);
 #pragma unroll
       for (int w = 1; w < 2 * WT; w++) acc = csub32(acc + shoup32(dig[k][w], c[w].x, c[w].y, p), p2);
-      sm32[pidx32(threadIdx.x + k * G::THREADS)] = acc + (negW & sign[k]);      // below 3p
+      sm32[pidx32(threadIdx.x) + k * HB32_PSTEP(G::THREADS)] = acc + (negW & sign[k]);      // below 3p
     }
     ntt32_forward<LOGN>(sm32, T.tw + (size_t)d * G::N, p);
     uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)q * D + d) * G::N);
@@ -360,7 +383,8 @@ k32_poly_ntt_all(const uint64_t *__restrict__ src, size_t poly_stride, uint32_t 
     for (int k = 0; k < PER / 4; k++) {
       const int i4 = threadIdx.x + k * G::THREADS;
       uint4 v;
-      v.x = sm32[pidx32(4 * i4)]; v.y = sm32[pidx32(4 * i4 + 1)]; v.z = sm32[pidx32(4 * i4 + 2)]; v.w = sm32[pidx32(4 * i4 + 3)];
+      const int b4 = pidx32(4 * i4);                          // four consecutive words never straddle a pad word
+      v.x = sm32[b4]; v.y = sm32[b4 + 1]; v.z = sm32[b4 + 2]; v.w = sm32[b4 + 3];
       __stcs(&dst[i4], v);
     }
     __syncthreads();                                          // the buffer is refilled for the next limb
@@ -407,7 +431,7 @@ k32_mulacc_intt_all(const uint32_t *__restrict__ hat, size_t hat_jstride, const 
         acc[3] = csub32(acc[3] + shoup32(h[j][k].w, kw.w, kq.w, p), p2);
       }
 #pragma unroll
-      for (int e = 0; e < 4; e++) sm32[pidx32(4 * i4 + e)] = acc[e];
+      for (int e = 0; e < 4; e++) sm32[pidx32(4 * i4) + e] = acc[e];
     }
     ntt32_inverse<LOGN>(sm32, itw, p);
     uint4 *dst = reinterpret_cast<uint4 *>(chat + (((size_t)g * nq + q) * D + d) * G::N);
@@ -415,7 +439,8 @@ k32_mulacc_intt_all(const uint32_t *__restrict__ hat, size_t hat_jstride, const 
     for (int k = 0; k < V; k++) {
       const int i4 = threadIdx.x + k * G::THREADS;
       uint4 v;
-      v.x = sm32[pidx32(4 * i4)]; v.y = sm32[pidx32(4 * i4 + 1)]; v.z = sm32[pidx32(4 * i4 + 2)]; v.w = sm32[pidx32(4 * i4 + 3)];
+      const int b4 = pidx32(4 * i4);                          // four consecutive words never straddle a pad word
+      v.x = sm32[b4]; v.y = sm32[b4 + 1]; v.z = sm32[b4 + 2]; v.w = sm32[b4 + 3];
       __stcs(&dst[i4], v);
     }
     __syncthreads();
@@ -577,7 +602,10 @@ k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const _
   const uint2 *pw = dec32 + (size_t)i * decstride;
   const uint32_t negW = p - __ldg(&pw[2 * W]).x;
   const uint64_t *poly = src + (size_t)b * src_bstride;
-  for (int c = threadIdx.x; c < G::N; c += G::THREADS) smA[pidx32(c)] = decompose32(poly, c, W, G::N, pw, p, p2, negW);
+  constexpr int PER = G::N / G::THREADS, PST = HB32_PSTEP(G::THREADS);
+  const int pb = pidx32(threadIdx.x);
+#pragma unroll 4
+  for (int k = 0; k < PER; k++) smA[pb + k * PST] = decompose32(poly, threadIdx.x + k * G::THREADS, W, G::N, pw, p, p2, negW);
   ntt32_forward<LOGN>(smA, T.tw + (size_t)i * G::N, p);
   const uint2 *itw = T.itw + (size_t)i * G::N;
 #pragma unroll 1
@@ -587,13 +615,15 @@ k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const _
     for (int h = 0; h < 2; h++) {
       const uint32_t *kw = S.key[j] + ((size_t)h * mkey + i) * 2 * G::N, *kq = kw + G::N;
 #pragma unroll 4
-      for (int c = threadIdx.x; c < G::N; c += G::THREADS) {
+      for (int k = 0; k < PER; k++) {
+        const int c = threadIdx.x + k * G::THREADS;
         const unsigned s = __ldg(&perm[c]);
-        smB[pidx32(c)] = shoup32(smA[pidx32(s)], __ldg(&kw[c]), __ldg(&kq[c]), p);      // below 2q
+        smB[pb + k * PST] = shoup32(smA[pidx32(s)], __ldg(&kw[c]), __ldg(&kq[c]), p);      // below 2q
       }
       ntt32_inverse<LOGN>(smB, itw, p);
       uint32_t *dst = chat + (size_t)j * chat_jstride + (((size_t)b * 2 + h) * m + i) * G::N;
-      for (int c = threadIdx.x; c < G::N; c += G::THREADS) __stcs(&dst[c], smB[pidx32(c)]);
+#pragma unroll 4
+      for (int k = 0; k < PER; k++) __stcs(&dst[threadIdx.x + k * G::THREADS], smB[pb + k * PST]);
       __syncthreads();                                       // smB is refilled
     }
   }
@@ -614,6 +644,8 @@ k32_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src
   const uint2 *pw = dec32 + (size_t)i * decstride;
   const uint32_t negW = p - __ldg(&pw[2 * W]).x;
   const uint2 *tw = T.tw + (size_t)i * G::N;
+  constexpr int PER = G::N / G::THREADS, PST = HB32_PSTEP(G::THREADS);
+  const int pb = pidx32(threadIdx.x);
 #pragma unroll 1
   for (unsigned g = 0; g < ng; g++) {
     const uint64_t *poly = src + (size_t)g * src_gstride + (size_t)b * src_bstride;
@@ -630,10 +662,11 @@ k32_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src
       uint32_t *acc = sm32 + (size_t)(1 + h) * G::SMEM_WORDS;
       const uint32_t *kw = S.key[g] + ((size_t)h * mkey + i) * 2 * G::N, *kq = kw + G::N;
 #pragma unroll 4
-      for (int c = threadIdx.x; c < G::N; c += G::THREADS) {
-        uint32_t v = shoup32(smA[pidx32(c)], __ldg(&kw[c]), __ldg(&kq[c]), p);          // below 2q
-        if (g) v = csub32(v + acc[pidx32(c)], p2);
-        acc[pidx32(c)] = v;
+      for (int k = 0; k < PER; k++) {
+        const int c = threadIdx.x + k * G::THREADS, o = pb + k * PST;
+        uint32_t v = shoup32(smA[o], __ldg(&kw[c]), __ldg(&kq[c]), p);                  // below 2q
+        if (g) v = csub32(v + acc[o], p2);
+        acc[o] = v;
       }
     }
     __syncthreads();                                         // smA is refilled; the accumulators are thread-private
@@ -644,7 +677,8 @@ k32_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src
     uint32_t *acc = sm32 + (size_t)(1 + h) * G::SMEM_WORDS;
     ntt32_inverse<LOGN>(acc, itw, p);
     uint32_t *dst = chatX + (((size_t)b * 2 + h) * m + i) * G::N;
-    for (int c = threadIdx.x; c < G::N; c += G::THREADS) __stcs(&dst[c], acc[pidx32(c)]);
+#pragma unroll 4
+    for (int k = 0; k < PER; k++) __stcs(&dst[threadIdx.x + k * G::THREADS], acc[pb + k * PST]);
   }
 }
 
