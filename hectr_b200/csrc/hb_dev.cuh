@@ -303,12 +303,18 @@ __device__ __forceinline__ void local_pass(uint64_t *sm, const Tw &tw, const Mod
     const int b = tile >> LOGST, o = tile & (ST - 1);
     const int g = (b << LOGBLK) + o;
     uint64_t x[1 << R];
+    // padded offsets as one base plus compile-time constants: pidx(g + t ST) = pidx(g) + t (ST + ST/8) when
+    // 16 | ST, and pidx(g + t) = pidx(g) + t inside one group of 16 (g is a multiple of 2^R, R <= 4)
+    const int pg = pidx(g);
     if (ST == 1) {
 #pragma unroll
       for (int t = 0; t < (1 << R); t += 2) {
-        ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(&sm[pidx(g + t)]);
+        ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(&sm[pg + t]);
         x[t] = v.x; x[t + 1] = v.y;
       }
+    } else if (ST % 16 == 0) {
+#pragma unroll
+      for (int t = 0; t < (1 << R); t++) x[t] = sm[pg + t * (ST + ST / 8)];
     } else {
 #pragma unroll
       for (int t = 0; t < (1 << R); t++) x[t] = sm[pidx(g + t * ST)];
@@ -323,7 +329,10 @@ __device__ __forceinline__ void local_pass(uint64_t *sm, const Tw &tw, const Mod
     if (ST == 1) {
 #pragma unroll
       for (int t = 0; t < (1 << R); t += 2)
-        *reinterpret_cast<ulonglong2 *>(&sm[pidx(g + t)]) = make_ulonglong2(x[t], x[t + 1]);
+        *reinterpret_cast<ulonglong2 *>(&sm[pg + t]) = make_ulonglong2(x[t], x[t + 1]);
+    } else if (ST % 16 == 0) {
+#pragma unroll
+      for (int t = 0; t < (1 << R); t++) sm[pg + t * (ST + ST / 8)] = x[t];
     } else {
 #pragma unroll
       for (int t = 0; t < (1 << R); t++) sm[pidx(g + t * ST)] = x[t];
@@ -404,7 +413,8 @@ __device__ __forceinline__ void ntt_forward(uint64_t *sm, Load load, const Tw &t
         }
       } else {
 #pragma unroll
-        for (int t = 0; t < 16; t++) sm[pidx(tau + t * ST0)] = x[t];
+        for (int t = 0; t < 16; t++)
+          sm[(ST0 % 16 == 0) ? pidx(tau) + t * (ST0 + ST0 / 8) : pidx(tau + t * ST0)] = x[t];
       }
     }
     if constexpr (G::C > 1) cg::this_cluster().sync();
@@ -450,7 +460,8 @@ __device__ __forceinline__ void ntt_inverse(uint64_t *sm, Store store, const Tw 
       }
     } else {
 #pragma unroll
-      for (int t = 0; t < 16; t++) x[t] = sm[pidx(tau + t * ST0)];
+      for (int t = 0; t < 16; t++)
+        x[t] = sm[(ST0 % 16 == 0) ? pidx(tau) + t * (ST0 + ST0 / 8) : pidx(tau + t * ST0)];
     }
     tile_inv<4, MODE == INV_RAW>(x, TileTw<4, false>(itw, 1u, 0u), m);
 #pragma unroll

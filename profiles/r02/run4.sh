@@ -1,20 +1,23 @@
 #!/usr/bin/env bash
+# GPU call: the allocation-free entry point alone in a fresh process, then the whole suite (it is collected last),
+# then the bench line and the NTT table
 set -u
 mkdir -p gpurun_out
-FAST="--steps 8 --warmup 3 --no-ntt --no-cpu-baseline --no-closed-loop"
-timeout 600 python bench.py $FAST > gpurun_out/bench4.json 2> gpurun_out/bench4.err; echo "bench rc=$?"; tail -c 300 gpurun_out/bench4.err
+timeout 900 python -m pytest tests/test_zz_no_alloc.py -m gpu -q -x > gpurun_out/pytest_zz_alone.log 2>&1
+echo "zz alone rc=$?" | tee -a gpurun_out/pytest_zz_alone.log
+tail -5 gpurun_out/pytest_zz_alone.log | cut -c1-300
+timeout 2400 python -m pytest tests -m gpu -q -x --durations=8 > gpurun_out/pytest10.log 2>&1
+echo "pytest rc=$?" >> gpurun_out/pytest10.log
+grep -vE "^\s*$" gpurun_out/pytest10.log | tail -22 | cut -c1-300
+timeout 900 python bench.py --steps 10 --warmup 3 --no-closed-loop > gpurun_out/bench10.json 2> gpurun_out/bench10.err; echo "bench rc=$?"; tail -c 300 gpurun_out/bench10.err
 python - <<'PY'
 import json
-for f in ("bench4",):
-    try:
-        d = [json.loads(l) for l in open(f"gpurun_out/{f}.json") if l.startswith("{")][-1]
-        print(f, round(d["value"]), "it/s  e2e", round(d["e2e"]["value"]), "ms/step", round(d["ms_per_step"], 2), "parity", d.get("parity_spot"))
-        for k, v in list(d["roofline"]["kernels"].items())[:14]:
-            print("   ", k, v["launches"], round(v["ms"] / d["steps"], 3), "ms/step")
-    except Exception as ex:
-        print(f, "unreadable", ex)
+try:
+    d = [json.loads(l) for l in open("gpurun_out/bench10.json") if l.startswith("{")][-1]
+    print("bench10", round(d["value"]), "it/s  e2e", round(d["e2e"]["value"]), "ms/step", round(d["ms_per_step"], 2), "parity", d.get("parity_spot"))
+    for k, v in list(d["roofline"]["kernels"].items())[:12]:
+        print("   ", k, v["launches"], round(v["ms"] / d["steps"], 3), "ms/step")
+    print(json.dumps(d.get("ntt_table", d.get("ntt")))[:1500])
+except Exception as ex:
+    print("unreadable", ex)
 PY
-for v in build_variants/lib_h*.so; do
-  [ -f "$v" ] || continue
-  echo "== $v"; HB_LIB="$PWD/$v" python profiles/prof_driver.py --case hempc --batch 4096 --reps 2 2>&1 | head -14
-done
