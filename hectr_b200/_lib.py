@@ -109,6 +109,7 @@ PROTOTYPES = {
     "hb_he_rs": (None, [ctx_p, ct_p]),
     "hb_he_moddown": (None, [ctx_p, ct_p]),
     "hb_he_mulpt": (None, [ctx_p, ct_p, ct_p, pt_p]),
+    "hb_he_mulpt_static": (None, [ctx_p, ct_p, ct_p, pt_p]),
     "hb_he_mul": (None, [ctx_p, ct_p, ct_p, ct_p, evk_p]),
     "hb_he_rot": (None, [ctx_p, ct_p, C.c_int, evk_p]),
     "hb_he_conj": (None, [ctx_p, ct_p, evk_p]),

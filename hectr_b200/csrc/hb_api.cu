@@ -2171,3 +2171,68 @@ extern "C" void hb_poly_rot(hb_ctx *ctx, const uint64_t *polys, unsigned W, size
   if (out == polys) hb_die("hb_poly_rot: the permutation is not in place (out must not alias polys)");
   if (total) launch(ctx, "k_poly_automorph", hbdev::k_poly_automorph, (unsigned)((total + 255) / 256), 256, 0, 1, polys, out, (int)W, ginv, ctx->ht.N, npoly);
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// hb_he_mulpt_static: he_mulpt for callers that may not allocate (CUDA graph capture, serving loops, harnesses
+// that forbid cudaMalloc).  No counterpart in the reference.
+//
+// Same kernels as hb_he_mulpt (k_poly_ntt, k_shoup_prep, k_mulpt_limb, k_recon_smod); the three work buffers of
+// the product live in ONE file-scope device array of HB_STATIC_SCRATCH_BYTES instead of the context's growing
+// workspaces.  Every GPU that loads the library holds the array until the process exits.
+//   words [0, hw)        raw   transform of the plaintext, D limbs          (written by k_poly_ntt)
+//   words [hw, 3 hw)     pthat Shoup pairs of raw times N^-1 (P_D/p_d)^-1  (written by k_shoup_prep)
+//   words [3 hw, ...)    chat  limbs of the 2 batch product polynomials     (written by k_mulpt_limb)
+// hw = D N rounded up to 32 words, so every part keeps the 256-byte alignment of the array.  Each word that a
+// kernel reads was written earlier in the same call, so nothing has to start at zero and the contents left by
+// the previous call are never observed.  All calls on one GPU share the array: calls that overlap on the GPU
+// (two streams, two contexts on the same device, two host threads) race.  Calls on one context's stream are
+// ordered and safe.
+//
+// In host code `g_static_scratch` is only a handle for the runtime, not a device address: the address comes
+// from cudaGetSymbolAddress, once per device, with that device current.
+// ---------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned long long g_static_scratch[HB_STATIC_SCRATCH_BYTES / 8];
+
+static uint64_t *static_scratch(const hb_ctx *ctx) {
+  enum { MAXDEV = 64 };
+  static uint64_t *addr[MAXDEV];          // per device; filled on the first call with that device current
+  const int dev = ctx->device;
+  if (dev < 0 || dev >= MAXDEV) hb_die("hb_he_mulpt_static: device index %d outside [0,%d)", dev, (int)MAXDEV);
+  if (!addr[dev]) {
+    int cur = -1;
+    CUDA_OK(cudaGetDevice(&cur));
+    if (cur != dev) hb_die("hb_he_mulpt_static: device %d is current, the context lives on device %d", cur, dev);
+    void *p = nullptr;
+    CUDA_OK(cudaGetSymbolAddress(&p, g_static_scratch));
+    if (!p || ((uintptr_t)p & 255)) hb_die("hb_he_mulpt_static: scratch array resolved to %p", p);
+    addr[dev] = (uint64_t *)p;
+  }
+  return addr[dev];
+}
+
+extern "C" void hb_he_mulpt_static(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt) { use_device(ctx);
+  same_shape(dst, src, "hb_he_mulpt_static");
+  if (!pt || !pt->words) hb_die("hb_he_mulpt_static: plaintext handle is not allocated");
+  if (ctx->prof) hb_die("hb_he_mulpt_static: per-kernel profiling creates events; switch it off (hb_prof_enable(ctx, 0))");
+  const unsigned D = hb::dim_mulpt(ctx->ht, src->l, pt->nu);
+  if (D == 0 || D > ctx->ht.dimub) hb_die("hb_he_mulpt_static: limb count %u outside the prime chain (%u)", D, ctx->ht.dimub);
+  const size_t N = ctx->ht.N;
+  const size_t hw = ((size_t)D * N + 31) & ~(size_t)31;
+  const size_t chat_words = (size_t)src->batch * 2 * D * N;
+  const size_t need = (3 * hw + chat_words) * 8;
+  if (need > (size_t)HB_STATIC_SCRATCH_BYTES)
+    hb_die("hb_he_mulpt_static: batch %u at level %u (N = %zu, %u limbs) needs %zu bytes of scratch, the static array holds %zu; "
+           "use hb_he_mulpt or a smaller batch", src->batch, src->l, N, D, need, (size_t)HB_STATIC_SCRATCH_BYTES);
+  uint64_t *raw = static_scratch(ctx);
+  ulonglong2 *pthat = (ulonglong2 *)(raw + hw);
+  uint64_t *chat = raw + 3 * hw;
+  const int W = hb::words_of_level(ctx->ht, src->l), k = ctx->ht.logq_l[src->l];
+  do_poly_ntt(ctx, pt->words, (size_t)ctx->ht.WC * N, ctx->ht.WC, raw, D, 1);
+  do_shoup_prep(ctx, raw, pthat, D, D, 2, D);
+  do_mulpt_limb(ctx, src->words, (size_t)W * N, W, pthat, chat, D, (size_t)src->batch * 2);
+  const double nu = src->nu, B = src->B;
+  dst->l = src->l;
+  dst->nu = nu * pt->nu;
+  dst->B = B * pt->nu;
+  do_recon_smod(ctx, chat, D, dst->words, W, k, (size_t)src->batch * 2, true);
+}

@@ -208,6 +208,12 @@ class Engine:
         self.lib.hb_he_mulpt(self.ctx, C.byref(r.h), C.byref(a.h), C.byref(pt))
         return r
 
+    def he_mulpt_static(self, a, pt: HbPt, out):
+        """hb_he_mulpt_static: he_mulpt without any allocation (scratch in the library's static device array);
+        the caller supplies the output ciphertext."""
+        self.lib.hb_he_mulpt_static(self.ctx, C.byref(out.h), C.byref(a.h), C.byref(pt))
+        return out
+
     def he_mul(self, a, b, rlk: EvalKeys, out=None):
         r = out or self._new_like(a)
         self.lib.hb_he_mul(self.ctx, C.byref(r.h), C.byref(a.h), C.byref(b.h), rlk.arr)

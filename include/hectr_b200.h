@@ -221,6 +221,18 @@ void hb_rns2words(hb_ctx *ctx, const uint64_t *limbs, size_t npoly, unsigned D, 
 /* poly_rot / poly_conj (poly.c:263-283) on DEVICE polynomials; rot < 0 means conjugation */
 void hb_poly_rot(hb_ctx *ctx, const uint64_t *polys, unsigned W, size_t npoly, int rot, uint64_t *out);
 
+/* ---- allocation-free variant --------------------------------------------------------------------------- */
+/* No counterpart in the reference.
+ * hb_he_mulpt for callers that may not allocate (CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc): same inputs, outputs, kernels and results as hb_he_mulpt, but the work buffers of the product sit in
+ * one static device array of HB_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.  The call
+ * makes no cudaMalloc / cudaFree.  It aborts with a message when (3 hw + 2 batch D N) * 8 bytes (D = hb_dim_mulpt,
+ * hw = D N rounded up to 32 words) exceed the array, and when per-kernel profiling is on.  The array is shared by
+ * every call on a GPU and keeps the last call's contents (each word read is written first in the same call): calls
+ * that overlap on the GPU (other streams, other contexts on the device) race; calls on one stream do not. */
+#define HB_STATIC_SCRATCH_BYTES (32u << 20)
+void hb_he_mulpt_static(hb_ctx *ctx, hb_ct *dst, const hb_ct *src, const hb_pt *pt);
+
 #ifdef __cplusplus
 }
 #endif
