@@ -225,15 +225,21 @@ struct LaunchHyb {
   typedef hb32::Cfg32<LOGN> G;
   static void ks_baby(hb_ctx *c, const uint64_t *src, size_t bstride, int W, const hb32::Baby32 &S, unsigned m, const uint2 *dec32, uint32_t *chat,
                       size_t jstride, unsigned batch) {
-    want_smem(hb32::k32_ks_baby<LOGN>, 2 * G::SMEM_BYTES);
-    launch(c, "k32_ks_baby", hb32::k32_ks_baby<LOGN>, batch * m, G::THREADS, 2 * G::SMEM_BYTES, 1, src, bstride, W, S, m, c->hyb_mmax, dec32, 2 * c->ht.WC + 1, chat,
-           jstride, c->dt32);
+#define X(WT)                                                                                                                      \
+    want_smem(hb32::k32_ks_baby<LOGN, WT>, 2 * G::SMEM_BYTES);                                                                     \
+    launch(c, "k32_ks_baby", hb32::k32_ks_baby<LOGN, WT>, batch * m, G::THREADS, 2 * G::SMEM_BYTES, 1, src, bstride, W, S, m, c->hyb_mmax, dec32, \
+           2 * c->ht.WC + 1, chat, jstride, c->dt32);
+    if (W == 1) { X(1) } else if (W == 2) { X(2) } else { X(0) }
+#undef X
   }
   static void ks_limb_sum(hb_ctx *c, const uint64_t *src, size_t bstride, size_t gstride, int W, const hb32::Groups32 &S, unsigned ng, unsigned m,
                           const uint2 *dec32, uint32_t *chatX, unsigned batch) {
-    want_smem(hb32::k32_ks_limb_sum<LOGN>, 3 * G::SMEM_BYTES);
-    launch(c, "k32_ks_limb_sum", hb32::k32_ks_limb_sum<LOGN>, batch * m, G::THREADS, 3 * G::SMEM_BYTES, 1, src, bstride, gstride, W, S, ng, m, c->hyb_mmax, dec32,
-           2 * c->ht.WC + 1, chatX, c->dt32);
+#define X(WT)                                                                                                                      \
+    want_smem(hb32::k32_ks_limb_sum<LOGN, WT>, 3 * G::SMEM_BYTES);                                                                 \
+    launch(c, "k32_ks_limb_sum", hb32::k32_ks_limb_sum<LOGN, WT>, batch * m, G::THREADS, 3 * G::SMEM_BYTES, 1, src, bstride, gstride, W, S, ng, m, \
+           c->hyb_mmax, dec32, 2 * c->ht.WC + 1, chatX, c->dt32);
+    if (W == 1) { X(1) } else if (W == 2) { X(2) } else { X(0) }
+#undef X
   }
   static void ntt_fwd_plain(hb_ctx *c, const uint32_t *in, uint32_t *out, size_t nlimbs, unsigned D) {
     launch(c, "k32_ntt_fwd_plain", hb32::k32_ntt_fwd_plain<LOGN>, (unsigned)nlimbs, G::THREADS, G::SMEM_BYTES, 1, in, out, c->dt32, D);
@@ -537,12 +543,24 @@ static bool do_ks_finish_sum_hyb(hb_ctx *c, const uint64_t *chatP, size_t chatP_
   const unsigned grid = (unsigned)(((size_t)batch * 2 * c->ht.N + threads - 1) / threads);
 #define X(DD, MM)                                                                                                                \
   if (dim == DD && m == MM) {                                                                                                    \
-    if (F) launch(c, "k_ks_finish_sum_hyb", hbdev::k_ks_finish_sum_hyb<4, DD, MM>, grid, threads, 0, 1, chatP, chatP_gstride, chatX32, *F, add0, \
-                  add_gstride, add_bstride, Wadd, SG, out, Wout, k, shift, kout, c->dt, batch);                                  \
+    if (F) {                                                                                                                     \
+      switch (SG.ng) {      /* giant steps actually evaluated: 3 for the CSTR gains, 4 for a full 16-slot matrix */              \
+        Y(DD, MM, 2) Y(DD, MM, 3) Y(DD, MM, 4)                                                                                   \
+        default: Y0(DD, MM)                                                                                                      \
+      }                                                                                                                          \
+    }                                                                                                                            \
     return true;                                                                                                                 \
   }
+#define Y(DD, MM, NG)                                                                                                            \
+  case NG: launch(c, "k_ks_finish_sum_hyb", hbdev::k_ks_finish_sum_hyb<4, DD, MM, NG>, grid, threads, 0, 1, chatP, chatP_gstride, chatX32, *F, \
+                  add0, add_gstride, add_bstride, Wadd, SG, out, Wout, k, shift, kout, c->dt, batch); break;
+#define Y0(DD, MM)                                                                                                               \
+  launch(c, "k_ks_finish_sum_hyb", hbdev::k_ks_finish_sum_hyb<4, DD, MM, 0>, grid, threads, 0, 1, chatP, chatP_gstride, chatX32, *F, add0, \
+         add_gstride, add_bstride, Wadd, SG, out, Wout, k, shift, kout, c->dt, batch);
   HB_HYB_PAIRS(X)
 #undef X
+#undef Y
+#undef Y0
   return false;
 }
 

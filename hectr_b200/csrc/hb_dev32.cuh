@@ -559,10 +559,15 @@ struct Groups32 {
 };
 
 // residue (below 3q) of the signed W-word coefficient, times the weight folded into `pw`
-__device__ __forceinline__ uint32_t decompose32(const uint64_t *__restrict__ poly, int i, int W, unsigned N, const uint2 *__restrict__ pw,
+// WT > 0: the word count as a compile-time constant (the loads of all words, and of the coefficients an unrolled caller
+// handles together, are issued before the first product)
+template <int WT = 0>
+__device__ __forceinline__ uint32_t decompose32(const uint64_t *__restrict__ poly, int i, int Wdyn, unsigned N, const uint2 *__restrict__ pw,
                                                 uint32_t p, uint32_t p2, uint32_t negW) {
   uint32_t acc = 0;
   uint64_t top = 0;
+  const int W = WT > 0 ? WT : Wdyn;
+#pragma unroll
   for (int w = 0; w < W; w++) {
     top = HB_LD(&poly[(size_t)w * N + i]);
     const uint2 c0 = __ldg(&pw[2 * w]), c1 = __ldg(&pw[2 * w + 1]);
@@ -588,7 +593,16 @@ __device__ __forceinline__ uint32_t decompose32(const uint64_t *__restrict__ pol
 #ifndef HB32_KSS_MINB
 #define HB32_KSS_MINB 4
 #endif
-template <int LOGN>
+#ifndef HB32_KSS_UNROLL
+#define HB32_KSS_UNROLL 4
+#endif
+#ifndef HB32_KSS_PUNROLL
+#define HB32_KSS_PUNROLL 8
+#endif
+#ifndef HB32_KSB_PUNROLL
+#define HB32_KSB_PUNROLL 8
+#endif
+template <int LOGN, int WT>
 __global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_KSB_MINB)
 k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const __grid_constant__ Baby32 S, unsigned m, unsigned mkey,
             const uint2 *__restrict__ dec32, unsigned decstride, uint32_t *__restrict__ chat, size_t chat_jstride, Tables32 T) {
@@ -602,10 +616,10 @@ k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const _
   const uint2 *pw = dec32 + (size_t)i * decstride;
   const uint32_t negW = p - __ldg(&pw[2 * W]).x;
   const uint64_t *poly = src + (size_t)b * src_bstride;
-  constexpr int PER = G::N / G::THREADS, PST = HB32_PSTEP(G::THREADS);
+  constexpr int PER = G::N / G::THREADS, PST = HB32_PSTEP(G::THREADS), KSB_PUNROLL = HB32_KSB_PUNROLL;
   const int pb = pidx32(threadIdx.x);
 #pragma unroll 4
-  for (int k = 0; k < PER; k++) smA[pb + k * PST] = decompose32(poly, threadIdx.x + k * G::THREADS, W, G::N, pw, p, p2, negW);
+  for (int k = 0; k < PER; k++) smA[pb + k * PST] = decompose32<WT>(poly, threadIdx.x + k * G::THREADS, W, G::N, pw, p, p2, negW);
   ntt32_forward<LOGN>(smA, T.tw + (size_t)i * G::N, p);
   const uint2 *itw = T.itw + (size_t)i * G::N;
 #pragma unroll 1
@@ -614,7 +628,7 @@ k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const _
 #pragma unroll 1
     for (int h = 0; h < 2; h++) {
       const uint32_t *kw = S.key[j] + ((size_t)h * mkey + i) * 2 * G::N, *kq = kw + G::N;
-#pragma unroll 4
+#pragma unroll KSB_PUNROLL
       for (int k = 0; k < PER; k++) {
         const int c = threadIdx.x + k * G::THREADS;
         const unsigned s = __ldg(&perm[c]);
@@ -632,7 +646,7 @@ k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const _
 // Giant steps of he_gemv (he-algo.c:80-84) on the 30-bit limbs, summed over the giant steps in the transform domain (the
 // 30-bit twin of k_ks_limb_sum):
 //   chatX[b][h][i][N] = y-weighted invntt( sum_g ntt( sigma_g(inner_g[b].c1) mod q_i ) o rk[g n1].p_h[i] )
-template <int LOGN>
+template <int LOGN, int WT>
 __global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_KSS_MINB)
 k32_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src_gstride, int W, const __grid_constant__ Groups32 S,
                 unsigned ng, unsigned m, unsigned mkey, const uint2 *__restrict__ dec32, unsigned decstride, uint32_t *__restrict__ chatX, Tables32 T) {
@@ -644,15 +658,16 @@ k32_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src
   const uint2 *pw = dec32 + (size_t)i * decstride;
   const uint32_t negW = p - __ldg(&pw[2 * W]).x;
   const uint2 *tw = T.tw + (size_t)i * G::N;
-  constexpr int PER = G::N / G::THREADS, PST = HB32_PSTEP(G::THREADS);
+  constexpr int PER = G::N / G::THREADS, PST = HB32_PSTEP(G::THREADS), KSS_UNROLL = HB32_KSS_UNROLL, KSS_PUNROLL = HB32_KSS_PUNROLL;
   const int pb = pidx32(threadIdx.x);
 #pragma unroll 1
   for (unsigned g = 0; g < ng; g++) {
     const uint64_t *poly = src + (size_t)g * src_gstride + (size_t)b * src_bstride;
     const unsigned ge = S.g[g];
     // sigma_g scatters coefficient c to c g mod 2N, negated past N (poly_rot, poly.c:263-283)
+#pragma unroll KSS_UNROLL
     for (int c = threadIdx.x; c < G::N; c += G::THREADS) {
-      const uint32_t v = decompose32(poly, c, W, G::N, pw, p, p2, negW);            // below 3q
+      const uint32_t v = decompose32<WT>(poly, c, W, G::N, pw, p, p2, negW);        // below 3q
       const unsigned k = ((unsigned)c * ge) & (2 * G::N - 1);
       smA[pidx32(k & (G::N - 1))] = (k >= (unsigned)G::N) ? 3 * p - v : v;
     }
@@ -661,7 +676,7 @@ k32_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src
     for (int h = 0; h < 2; h++) {
       uint32_t *acc = sm32 + (size_t)(1 + h) * G::SMEM_WORDS;
       const uint32_t *kw = S.key[g] + ((size_t)h * mkey + i) * 2 * G::N, *kq = kw + G::N;
-#pragma unroll 4
+#pragma unroll KSS_PUNROLL
       for (int k = 0; k < PER; k++) {
         const int c = threadIdx.x + k * G::THREADS, o = pb + k * PST;
         uint32_t v = shoup32(smA[o], __ldg(&kw[c]), __ldg(&kq[c]), p);                  // below 2q

@@ -640,15 +640,14 @@ __device__ __forceinline__ void ks_exact(const uint64_t *__restrict__ limbs, uns
   mul_Pinv<WK>(diff, T, t);
 }
 
-// t + roundup + sigma(add_h)[i], centred mod 2^k, stored as Wout words
+// sigma(add_h)[i] as WK sign-extended words (zero without an addend) and its sign under the automorphism.  Separate from
+// ks_tail_apply so that a kernel can issue these gathered loads before its arithmetic instead of waiting for them at the end.
 template <int WK>
-__device__ __forceinline__ void ks_tail(uint64_t (&t)[WK], bool roundup, const uint64_t *__restrict__ add, size_t add_bstride,
-                                        int Wadd, unsigned ginv, unsigned N, unsigned b, unsigned badd, unsigned h, unsigned i,
-                                        uint64_t *__restrict__ out, int Wout, int k) {
-  uint64_t addw[WK];
+__device__ __forceinline__ void ks_tail_load(const uint64_t *__restrict__ add, size_t add_bstride, int Wadd, unsigned ginv, unsigned N,
+                                             unsigned badd, unsigned i, uint64_t (&addw)[WK], bool &negate) {
 #pragma unroll
   for (int w = 0; w < WK; w++) addw[w] = 0;
-  bool negate = false;
+  negate = false;
   if (add) {
     unsigned ip = (i * ginv) & (2 * N - 1);
     negate = ip >= N;
@@ -660,6 +659,12 @@ __device__ __forceinline__ void ks_tail(uint64_t (&t)[WK], bool roundup, const u
       else addw[w] = fill;
     }
   }
+}
+
+// t + roundup + (negate ? -addw : addw), centred mod 2^k, stored as Wout words
+template <int WK>
+__device__ __forceinline__ void ks_tail_apply(uint64_t (&t)[WK], bool roundup, const uint64_t (&addw)[WK], bool negate, unsigned N,
+                                              unsigned b, unsigned h, unsigned i, uint64_t *__restrict__ out, int Wout, int k) {
   {
     // t += roundup + (negate ? -addw : addw)  ==  t + roundup + (addw ^ m) + (negate ? 1 : 0)
     const uint64_t m = negate ? ~0ULL : 0ULL;
@@ -684,6 +689,17 @@ __device__ __forceinline__ void ks_tail(uint64_t (&t)[WK], bool roundup, const u
 #pragma unroll
   for (int w = 0; w < WK; w++)
     if (w < Wout) HB_ST(&o[(size_t)w * N], t[w]);
+}
+
+// t + roundup + sigma(add_h)[i], centred mod 2^k, stored as Wout words
+template <int WK>
+__device__ __forceinline__ void ks_tail(uint64_t (&t)[WK], bool roundup, const uint64_t *__restrict__ add, size_t add_bstride,
+                                        int Wadd, unsigned ginv, unsigned N, unsigned b, unsigned badd, unsigned h, unsigned i,
+                                        uint64_t *__restrict__ out, int Wout, int k) {
+  uint64_t addw[WK];
+  bool negate;
+  ks_tail_load<WK>(add, add_bstride, Wadd, ginv, N, badd, i, addw, negate);
+  ks_tail_apply<WK>(t, roundup, addw, negate, N, b, h, i, out, Wout, k);
 }
 
 // ---- fast path ------------------------------------------------------------------------------------------------
@@ -985,8 +1001,12 @@ __device__ __noinline__ void hyb_R_slow(const uint64_t *__restrict__ limbs59, un
   mul_Pinv<2>(r2, T, RP);                                   // R P^-1 mod 2^128
 }
 
+// nine CTAs of 128 threads per SM (56 registers, nothing spilled): 6.61 -> 6.49 ms per step [variants_tails.log]
+#ifndef HB_FH_MINB
+#define HB_FH_MINB 9
+#endif
 template <int WPK, int DIM, int M32>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, HB_FH_MINB)
 k_ks_finish_hyb(const uint64_t *__restrict__ chat59, const uint32_t *__restrict__ chat32, const __grid_constant__ KsHyb F,
                 const uint64_t *__restrict__ add0, const uint64_t *__restrict__ add1, size_t add_bstride, int Wadd,
                 const __grid_constant__ TailGroups TG, uint64_t *__restrict__ out, int Wout, int k, const __grid_constant__ Tables T, unsigned batch) {
@@ -1002,10 +1022,17 @@ k_ks_finish_hyb(const uint64_t *__restrict__ chat59, const uint32_t *__restrict_
   u128 acc = 0, Rl = 0;
   uint64_t Fr = 0;
   float fx = 0.5f;
+  // every load of the coefficient is issued here: the gathered addend (needed last), the 59-bit limbs, then the 30-bit limbs
+  uint64_t addw[2];
+  bool negate;
+  ks_tail_load<2>(h ? add1 : add0, add_bstride, Wadd, ginv, N, badd, i, addw, negate);
+  uint64_t y59[DIM];
+#pragma unroll
+  for (int e = 0; e < DIM; e++) y59[e] = HB_LD(&limbs59[(size_t)e * N]);
   hyb_x32<DIM, M32>(limbs32, N, F, acc, fx);
 #pragma unroll
   for (int e = 0; e < DIM; e++) {
-    const uint64_t y = HB_LD(&limbs59[(size_t)e * N]);                   // below 2p
+    const uint64_t y = y59[e];                                           // below 2p
     fx = fmaf(__uint2float_rn(hi32(y)), F.rp[e], fx);
     mac128(acc, y, F.phat[e]);
     const Mod m = make_mod(F.p[e]);
@@ -1027,12 +1054,19 @@ k_ks_finish_hyb(const uint64_t *__restrict__ chat59, const uint32_t *__restrict_
     tt -= Rl - u128_of(F.kP) * v2;
   }
   uint64_t t[2] = {(uint64_t)tt, (uint64_t)(tt >> 64)};
-  ks_tail<2>(t, roundup, h ? add1 : add0, add_bstride, Wadd, ginv, N, b, badd, h, i, out, Wout, k);
+  ks_tail_apply<2>(t, roundup, addw, negate, N, b, h, i, out, Wout, k);
 }
 
 // summed giant steps on the hybrid basis: chatP[g][b][h][DIM][N] (u64, limbs of P per giant step), chatX32[b][h][M32][N] (u32, summed)
-template <int WPK, int DIM, int M32>
-__global__ void __launch_bounds__(128)
+// NGT > 0: the number of giant steps as a compile-time constant; the limbs of P of every giant step and the gathered addends
+// are then read before the first product (with a run-time count each giant step waits for its own loads in turn).
+// six CTAs of 128 threads per SM (80 registers, a few spilled): 3.10 -> 2.91 ms per step against the compiler's own choice
+// of 102 [B200, 4096 instances, profiles/r02/variants_tails.log]
+#ifndef HB_FSH_MINB
+#define HB_FSH_MINB 6
+#endif
+template <int WPK, int DIM, int M32, int NGT>
+__global__ void __launch_bounds__(128, HB_FSH_MINB)
 k_ks_finish_sum_hyb(const uint64_t *__restrict__ chatP, size_t chatP_gstride, const uint32_t *__restrict__ chatX32, const __grid_constant__ KsHyb F,
                     const uint64_t *__restrict__ add0, size_t add_gstride, size_t add_bstride, int Wadd, const __grid_constant__ SumGroups SG,
                     uint64_t *__restrict__ out, int Wout, int k, int shift, int kout, const __grid_constant__ Tables T, unsigned batch) {
@@ -1041,26 +1075,48 @@ k_ks_finish_sum_hyb(const uint64_t *__restrict__ chatP, size_t chatP_gstride, co
   const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= (size_t)batch * 2 * N) return;
   const unsigned i = gid % N, h = (gid / N) & 1, b = gid / (2 * (size_t)N);
-  const unsigned ng = SG.ng;
+  const unsigned ng = NGT > 0 ? (unsigned)NGT : SG.ng;
+  constexpr int NB = NGT > 0 ? NGT : 1, UNR = NGT > 0 ? NGT : 1;
   const uint64_t *limbsP = chatP + ((size_t)b * 2 + h) * DIM * N + i;
   const uint32_t *limbs32 = chatX32 + ((size_t)b * 2 + h) * M32 * N + i;
   const uint64_t ONE = 1ULL << 56, HALF = 1ULL << 55, MASK = ONE - 1, MARGIN = 1ULL << 38;
   u128 acc = 0;
   float fx = 0.5f;
+  const bool with_add = h == 0 && add0;
+  uint64_t pre[NB][DIM], addlo[NB], addhi[NB];
+  bool addneg[NB];
+  if constexpr (NGT > 0) {
+#pragma unroll
+    for (int g = 0; g < NGT; g++) {
+      addlo[g] = addhi[g] = 0;
+      addneg[g] = false;
+      if (with_add) {
+        const unsigned ip = (i * SG.ginv[g]) & (2 * N - 1);
+        const uint64_t *ap = add0 + (size_t)g * add_gstride + (size_t)b * add_bstride + (ip & (N - 1));
+        addlo[g] = HB_LD(&ap[0]);
+        addhi[g] = Wadd > 1 ? HB_LD(&ap[N]) : 0;
+        addneg[g] = ip >= N;
+      }
+    }
+#pragma unroll
+    for (int g = 0; g < NGT; g++)
+#pragma unroll
+      for (int e = 0; e < DIM; e++) pre[g][e] = HB_LD(&limbsP[(size_t)g * chatP_gstride + (size_t)e * N]);
+  }
   hyb_x32<DIM, M32>(limbs32, N, F, acc, fx);
   uint64_t ysum[DIM];
 #pragma unroll
   for (int e = 0; e < DIM; e++) ysum[e] = 0;
   u128 Rsum = 0;
   unsigned nround = 0;
-#pragma unroll 1
+#pragma unroll UNR
   for (unsigned g = 0; g < ng; g++) {
     u128 Rl = 0;
     uint64_t Fr = 0;
     const uint64_t *lg = limbsP + (size_t)g * chatP_gstride;
 #pragma unroll
     for (int e = 0; e < DIM; e++) {
-      const uint64_t a = HB_LD(&lg[(size_t)e * N]);                       // below 2p
+      const uint64_t a = NGT > 0 ? pre[NGT > 0 ? g : 0][e] : HB_LD(&lg[(size_t)e * N]);       // below 2p
       ysum[e] += a;                                                      // at most 8 giant steps: below 16p < 2^64
       const Mod m = make_mod(F.p[e]);
       const uint64_t z = shoup_lazy(a, F.kinv[e], F.kinvq[e], m);
@@ -1087,15 +1143,24 @@ k_ks_finish_sum_hyb(const uint64_t *__restrict__ chatP, size_t chatP_gstride, co
   }
   const uint32_t v = (uint32_t)fx;
   u128 tt = acc - u128_of(F.M) * v - Rsum + nround;
-  if (h == 0 && add0) {                                                  // sum_g sigma_g(inner_g.c0)
+  if (with_add) {                                                        // sum_g sigma_g(inner_g.c0)
+    if constexpr (NGT > 0) {
+#pragma unroll
+      for (int g = 0; g < NGT; g++) {
+        const uint64_t hi = Wadd > 1 ? addhi[g] : (uint64_t)((int64_t)addlo[g] >> 63);
+        const u128 a = ((u128)hi << 64) | addlo[g];
+        tt = addneg[g] ? tt - a : tt + a;
+      }
+    } else {
 #pragma unroll 1
-    for (unsigned g = 0; g < ng; g++) {
-      const unsigned ip = (i * SG.ginv[g]) & (2 * N - 1);
-      const uint64_t *ap = add0 + (size_t)g * add_gstride + (size_t)b * add_bstride + (ip & (N - 1));
-      const uint64_t lo = HB_LD(&ap[0]);
-      const uint64_t hi = Wadd > 1 ? HB_LD(&ap[N]) : (uint64_t)((int64_t)lo >> 63);
-      const u128 a = ((u128)hi << 64) | lo;
-      tt = (ip >= N) ? tt - a : tt + a;
+      for (unsigned g = 0; g < ng; g++) {
+        const unsigned ip = (i * SG.ginv[g]) & (2 * N - 1);
+        const uint64_t *ap = add0 + (size_t)g * add_gstride + (size_t)b * add_bstride + (ip & (N - 1));
+        const uint64_t lo = HB_LD(&ap[0]);
+        const uint64_t hi = Wadd > 1 ? HB_LD(&ap[N]) : (uint64_t)((int64_t)lo >> 63);
+        const u128 a = ((u128)hi << 64) | lo;
+        tt = (ip >= N) ? tt - a : tt + a;
+      }
     }
   }
   uint64_t x[2] = {(uint64_t)tt, (uint64_t)(tt >> 64)};
