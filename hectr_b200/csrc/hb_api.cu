@@ -695,6 +695,9 @@ extern "C" hb_ctx *hb_ctx_create(unsigned logn, unsigned logq, unsigned slots, u
       d.primes = (const hb32::Prime32 *)upload_vec(ctx, g.primes);
       d.tw = (const uint2 *)upload_vec(ctx, g.tw);
       d.itw = (const uint2 *)upload_vec(ctx, g.itw);
+      d.tw_tr = (const uint2 *)upload_vec(ctx, g.tw_tr);
+      d.itw_tr = (const uint2 *)upload_vec(ctx, g.itw_tr);
+      d.tr_stride = g.tr_stride;
       d.pow32 = (const uint2 *)upload_vec(ctx, g.pow32);
       d.crt_inv = (const uint2 *)upload_vec(ctx, g.crt_inv);
       d.crt_qhat = upload_vec(ctx, g.crt_qhat);

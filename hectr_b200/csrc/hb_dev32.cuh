@@ -18,6 +18,8 @@ struct Prime32 { uint32_t p, ninv, ninv_q, mu; };   // must match hb::Prime32
 struct Tables32 {                 // device pointers, by value
   const Prime32 *primes;          // [nprimes]
   const uint2 *tw, *itw;          // [nprimes][N] (w, floor(w 2^32 / p))
+  const uint2 *tw_tr, *itw_tr;    // [nprimes][tr_stride] lane-transposed copy for the stride-1 pass (see Tw32)
+  unsigned tr_stride;
   const uint2 *pow32;             // [nprimes][ndig + 1]
   const uint2 *crt_inv;           // [nprimes + 1][nprimes]
   const uint64_t *crt_qhat;       // [nprimes + 1][nprimes][WC]
@@ -61,12 +63,36 @@ __device__ __forceinline__ void load_tw32(uint2 (&w)[CNT], const uint2 *__restri
   }
 }
 
-template <int R, int A>
+// Twiddles of one prime and one direction.  nat: index = bit-reversed exponent (entry k of stage s at 2^s + k).  In the
+// stride-1 pass every thread has its own 2^R - 1 twiddles; read from `nat` a warp's 16-byte loads of stage A >= 2 are 32 / 64
+// bytes apart (8 / 16 cache lines per instruction, 86 L1 wavefronts per tile), so a lane-transposed copy holds them as
+//   slot (2^A - 1) + u of tile K  at  ((K >> 5) (2^R - 1) + slot) 32 + (K & 31)  =  nat[((2^S + K) << A) + u],  S = log2 N - R
+// and every load is 256 contiguous bytes per warp (30 wavefronts per tile).  Built by hb::build_tables32.
+struct Tw32 {
+  const uint2 *nat, *tr;
+};
+__device__ __forceinline__ Tw32 tw32_of(const Tables32 &T, unsigned i, bool inverse) {
+  Tw32 t;
+  t.nat = (inverse ? T.itw : T.tw) + (size_t)i * T.N;
+  t.tr = (inverse ? T.itw_tr : T.tw_tr) + (size_t)i * T.tr_stride;
+  return t;
+}
+template <int R, int A, bool TR>
+__device__ __forceinline__ void load_stage_tw32(uint2 (&w)[1 << A], const uint2 *__restrict__ tw, unsigned K0) {
+  if constexpr (TR) {                         // tw: the tile's lane of the transposed copy
+#pragma unroll
+    for (int u = 0; u < (1 << A); u++) w[u] = __ldg(&tw[(((1 << A) - 1) + u) * 32]);
+  } else {
+    load_tw32<(1 << A)>(w, tw + ((size_t)K0 << A));
+  }
+}
+
+template <int R, int A, bool TR = false>
 __device__ __forceinline__ void stage_fwd32(uint32_t (&x)[1 << R], const uint2 *__restrict__ tw, unsigned K0, uint32_t p) {
   constexpr int beta = R - 1 - A, half = 1 << beta;
   const uint32_t p2 = 2 * p;
   uint2 w[1 << A];
-  load_tw32<(1 << A)>(w, tw + ((size_t)K0 << A));
+  load_stage_tw32<R, A, TR>(w, tw, K0);
 #pragma unroll
   for (int t = 0; t < (1 << R); t++) {
     if ((t & half) == 0) {
@@ -79,20 +105,20 @@ __device__ __forceinline__ void stage_fwd32(uint32_t (&x)[1 << R], const uint2 *
   }
 }
 // forward tile: X' = X + wY, Y' = X - wY + 2p, X first brought below 2p; all values stay in [0, 4p)
-template <int R>
+template <int R, bool TR = false>
 __device__ __forceinline__ void tile_fwd32(uint32_t (&x)[1 << R], const uint2 *__restrict__ tw, unsigned K0, uint32_t p) {
-  stage_fwd32<R, 0>(x, tw, K0, p);
-  if constexpr (R > 1) stage_fwd32<R, 1>(x, tw, K0, p);
-  if constexpr (R > 2) stage_fwd32<R, 2>(x, tw, K0, p);
-  if constexpr (R > 3) stage_fwd32<R, 3>(x, tw, K0, p);
+  stage_fwd32<R, 0, TR>(x, tw, K0, p);
+  if constexpr (R > 1) stage_fwd32<R, 1, TR>(x, tw, K0, p);
+  if constexpr (R > 2) stage_fwd32<R, 2, TR>(x, tw, K0, p);
+  if constexpr (R > 3) stage_fwd32<R, 3, TR>(x, tw, K0, p);
 }
 
-template <int R, int BETA>
+template <int R, int BETA, bool TR = false>
 __device__ __forceinline__ void stage_inv32(uint32_t (&x)[1 << R], const uint2 *__restrict__ tw, unsigned K0, uint32_t p) {
   constexpr int A = R - 1 - BETA, half = 1 << BETA;
   const uint32_t p2 = 2 * p;
   uint2 w[1 << A];
-  load_tw32<(1 << A)>(w, tw + ((size_t)K0 << A));
+  load_stage_tw32<R, A, TR>(w, tw, K0);
 #pragma unroll
   for (int t = 0; t < (1 << R); t++) {
     if ((t & half) == 0) {
@@ -105,17 +131,20 @@ __device__ __forceinline__ void stage_inv32(uint32_t (&x)[1 << R], const uint2 *
   }
 }
 // inverse tile (Gentleman-Sande): inputs and outputs in [0, 2p)
-template <int R>
+template <int R, bool TR = false>
 __device__ __forceinline__ void tile_inv32(uint32_t (&x)[1 << R], const uint2 *__restrict__ tw, unsigned K0, uint32_t p) {
-  stage_inv32<R, 0>(x, tw, K0, p);
-  if constexpr (R > 1) stage_inv32<R, 1>(x, tw, K0, p);
-  if constexpr (R > 2) stage_inv32<R, 2>(x, tw, K0, p);
-  if constexpr (R > 3) stage_inv32<R, 3>(x, tw, K0, p);
+  stage_inv32<R, 0, TR>(x, tw, K0, p);
+  if constexpr (R > 1) stage_inv32<R, 1, TR>(x, tw, K0, p);
+  if constexpr (R > 2) stage_inv32<R, 2, TR>(x, tw, K0, p);
+  if constexpr (R > 3) stage_inv32<R, 3, TR>(x, tw, K0, p);
 }
 
 // one pass over the limb in shared memory: stages [S, S+R) in forward numbering
+#ifndef HB32_TW_TR
+#define HB32_TW_TR 1
+#endif
 template <int LOGN, int S, int R, bool INV>
-__device__ __forceinline__ void pass32(uint32_t *sm, const uint2 *__restrict__ tw, uint32_t p) {
+__device__ __forceinline__ void pass32(uint32_t *sm, const Tw32 &tw, uint32_t p) {
   typedef Cfg32<LOGN> G;
   constexpr int LOGST = LOGN - S - R, ST = 1 << LOGST, TILES = G::N >> R, LOGBLK = LOGN - S;
   for (int t0 = threadIdx.x; t0 < TILES; t0 += G::THREADS) {
@@ -146,15 +175,21 @@ __device__ __forceinline__ void pass32(uint32_t *sm, const uint2 *__restrict__ t
     }
 #pragma unroll
     for (int t = 0; t < (1 << R); t++) x[t] = sm[off[t]];
-    if (INV) tile_inv32<R>(x, tw, (1u << S) + b, p);
-    else tile_fwd32<R>(x, tw, (1u << S) + b, p);
+    if constexpr (LOGST == 0 && HB32_TW_TR && (TILES % 32 == 0)) {      // stride-1 pass: b == tile, one set of twiddles per thread
+      const uint2 *lane_tw = tw.tr + (size_t)(tile >> 5) * (((1 << R) - 1) * 32) + (tile & 31);
+      if (INV) tile_inv32<R, true>(x, lane_tw, 0u, p);
+      else tile_fwd32<R, true>(x, lane_tw, 0u, p);
+    } else {
+      if (INV) tile_inv32<R>(x, tw.nat, (1u << S) + b, p);
+      else tile_fwd32<R>(x, tw.nat, (1u << S) + b, p);
+    }
 #pragma unroll
     for (int t = 0; t < (1 << R); t++) sm[off[t]] = x[t];
   }
 }
 
 template <int LOGN, int S>
-__device__ __forceinline__ void fwd32(uint32_t *sm, const uint2 *__restrict__ tw, uint32_t p) {
+__device__ __forceinline__ void fwd32(uint32_t *sm, const Tw32 &tw, uint32_t p) {
   if constexpr (S < LOGN) {
     constexpr int R = hbdev::PassSize<LOGN - S>::R;
     pass32<LOGN, S, R, false>(sm, tw, p);
@@ -163,7 +198,7 @@ __device__ __forceinline__ void fwd32(uint32_t *sm, const uint2 *__restrict__ tw
   }
 }
 template <int LOGN, int S>
-__device__ __forceinline__ void inv32(uint32_t *sm, const uint2 *__restrict__ itw, uint32_t p) {
+__device__ __forceinline__ void inv32(uint32_t *sm, const Tw32 &itw, uint32_t p) {
   if constexpr (S < LOGN) {
     constexpr int R = hbdev::PassSize<LOGN - S>::R;
     inv32<LOGN, S + R>(sm, itw, p);
@@ -173,13 +208,13 @@ __device__ __forceinline__ void inv32(uint32_t *sm, const uint2 *__restrict__ it
 }
 // natural order, values below 4p, visible after the barrier this starts with -> bit-reversed order, values below 4p
 template <int LOGN>
-__device__ __forceinline__ void ntt32_forward(uint32_t *sm, const uint2 *__restrict__ tw, uint32_t p) {
+__device__ __forceinline__ void ntt32_forward(uint32_t *sm, const Tw32 &tw, uint32_t p) {
   __syncthreads();
   fwd32<LOGN, 0>(sm, tw, p);
 }
 // bit-reversed order, values below 2p -> natural order, NOT scaled by N^-1 (folded into the fixed multiplicand), below 2p
 template <int LOGN>
-__device__ __forceinline__ void ntt32_inverse(uint32_t *sm, const uint2 *__restrict__ itw, uint32_t p) {
+__device__ __forceinline__ void ntt32_inverse(uint32_t *sm, const Tw32 &itw, uint32_t p) {
   __syncthreads();
   inv32<LOGN, 0>(sm, itw, p);
 }
@@ -215,7 +250,7 @@ k32_poly_ntt(const uint64_t *__restrict__ src, size_t poly_stride, int W, uint32
     acc += (negW & (uint32_t)((int64_t)top >> 63));                            // below 3p
     sm32[pidx32(i)] = acc;
   }
-  ntt32_forward<LOGN>(sm32, T.tw + (size_t)d * G::N, p);
+  ntt32_forward<LOGN>(sm32, tw32_of(T, d, false), p);
   uint32_t *dst = out + ((size_t)q * D + d) * G::N;
   for (int i = threadIdx.x; i < G::N; i += G::THREADS) {
     uint32_t v = sm32[pidx32(i)];
@@ -269,7 +304,7 @@ k32_mulacc_intt(const uint32_t *__restrict__ hat, size_t hat_jstride, const uint
     }
     sm32[pidx32(i)] = acc;                                                       // below 2p
   }
-  ntt32_inverse<LOGN>(sm32, T.itw + (size_t)d * G::N, p);
+  ntt32_inverse<LOGN>(sm32, tw32_of(T, d, true), p);
   uint32_t *dst = chat + ((size_t)qq * D + d) * G::N;
   for (int i = threadIdx.x; i < G::N; i += G::THREADS) dst[i] = sm32[pidx32(i)];
 }
@@ -377,7 +412,7 @@ k32_poly_ntt_all(const uint64_t *__restrict__ src, size_t poly_stride, uint32_t 
       for (int w = 1; w < 2 * WT; w++) acc = csub32(acc + shoup32(dig[k][w], c[w].x, c[w].y, p), p2);
       sm32[pidx32(threadIdx.x) + k * HB32_PSTEP(G::THREADS)] = acc + (negW & sign[k]);      // below 3p
     }
-    ntt32_forward<LOGN>(sm32, T.tw + (size_t)d * G::N, p);
+    ntt32_forward<LOGN>(sm32, tw32_of(T, d, false), p);
     uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)q * D + d) * G::N);
 #pragma unroll
     for (int k = 0; k < PER / 4; k++) {
@@ -413,7 +448,7 @@ k32_mulacc_intt_all(const uint32_t *__restrict__ hat, size_t hat_jstride, const 
 #pragma unroll
     for (int k = 0; k < V; k++) h[j][k] = __ldcs(&a[threadIdx.x + k * G::THREADS]);
   }
-  const uint2 *itw = T.itw + (size_t)d * G::N;
+  const Tw32 itw = tw32_of(T, d, true);
 #pragma unroll 1
   for (unsigned g = 0; g < ngroups; g++) {
     const uint32_t *w = pthat_all + ((size_t)GM.idx[g] * pthat_gstride + d) * 2 * G::N;       // strides in limbs
@@ -620,8 +655,8 @@ k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const _
   const int pb = pidx32(threadIdx.x);
 #pragma unroll 4
   for (int k = 0; k < PER; k++) smA[pb + k * PST] = decompose32<WT>(poly, threadIdx.x + k * G::THREADS, W, G::N, pw, p, p2, negW);
-  ntt32_forward<LOGN>(smA, T.tw + (size_t)i * G::N, p);
-  const uint2 *itw = T.itw + (size_t)i * G::N;
+  ntt32_forward<LOGN>(smA, tw32_of(T, i, false), p);
+  const Tw32 itw = tw32_of(T, i, true);
 #pragma unroll 1
   for (unsigned j = 0; j < S.nj; j++) {
     const uint16_t *perm = S.perm[j];
@@ -657,7 +692,7 @@ k32_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src
   const uint32_t p = T.primes[i].p, p2 = 2 * p;
   const uint2 *pw = dec32 + (size_t)i * decstride;
   const uint32_t negW = p - __ldg(&pw[2 * W]).x;
-  const uint2 *tw = T.tw + (size_t)i * G::N;
+  const Tw32 tw = tw32_of(T, i, false);
   constexpr int PER = G::N / G::THREADS, PST = HB32_PSTEP(G::THREADS), KSS_UNROLL = HB32_KSS_UNROLL, KSS_PUNROLL = HB32_KSS_PUNROLL;
   const int pb = pidx32(threadIdx.x);
 #pragma unroll 1
@@ -686,7 +721,7 @@ k32_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src
     }
     __syncthreads();                                         // smA is refilled; the accumulators are thread-private
   }
-  const uint2 *itw = T.itw + (size_t)i * G::N;
+  const Tw32 itw = tw32_of(T, i, true);
 #pragma unroll 1
   for (int h = 0; h < 2; h++) {
     uint32_t *acc = sm32 + (size_t)(1 + h) * G::SMEM_WORDS;
@@ -707,7 +742,7 @@ k32_ntt_fwd_plain(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, T
   const uint32_t p = T.primes[i].p, p2 = 2 * p;
   const uint32_t *src = in + (size_t)blockIdx.x * G::N;
   for (int c = threadIdx.x; c < G::N; c += G::THREADS) sm32[pidx32(c)] = src[c];
-  ntt32_forward<LOGN>(sm32, T.tw + (size_t)i * G::N, p);
+  ntt32_forward<LOGN>(sm32, tw32_of(T, i, false), p);
   uint32_t *dst = out + (size_t)blockIdx.x * G::N;
   for (int c = threadIdx.x; c < G::N; c += G::THREADS) {
     uint32_t v = sm32[pidx32(c)];

@@ -28,6 +28,8 @@ struct HostTables32 {
   unsigned logn = 0, N = 0, nprimes = 0, WC = 0, ndig = 0;
   std::vector<Prime32> primes;                 // [nprimes]
   std::vector<uint32_t> tw, itw;               // [nprimes][N][2]
+  std::vector<uint32_t> tw_tr, itw_tr;         // [nprimes][tr_stride][2]: lane-transposed twiddles of the stride-1 pass (hb_dev32.cuh Tw32)
+  unsigned tr_R = 0, tr_stride = 0;            // stages of that pass; entries per prime
   std::vector<uint32_t> pow32;                 // [nprimes][ndig + 1][2]   ndig = 2 WC digits, + the sign digit weight
   std::vector<uint32_t> crt_inv;               // [nprimes + 1][nprimes][2]  (value, quotient)
   std::vector<uint64_t> crt_qhat;              // [nprimes + 1][nprimes][WC]
@@ -72,6 +74,32 @@ inline std::string build_tables32(HostTables32 &t, unsigned logn, unsigned WC, u
       itw[2 * j] = (uint32_t)pwi; itw[2 * j + 1] = shoup_quotient32((uint32_t)pwi, c.p);
       pw = mulmod(pw, root, p);
       pwi = mulmod(pwi, rootinv, p);
+    }
+    {
+      // the stride-1 pass of the device transform (hb_dev32.cuh fwd32 / inv32: passes of PassSize<remaining>::R stages)
+      unsigned S = 0, R = 0;
+      for (;;) {
+        const unsigned rem = logn - S, np = (rem + 3) / 4;
+        R = (rem + np - 1) / np;
+        if (S + R == logn) break;
+        S += R;
+      }
+      const unsigned tiles = N >> R, slots = (1u << R) - 1;
+      t.tr_R = R;
+      t.tr_stride = ((tiles + 31) / 32) * slots * 32;
+      if (d == 0) {
+        t.tw_tr.assign((size_t)t.nprimes * t.tr_stride * 2, 0);
+        t.itw_tr.assign((size_t)t.nprimes * t.tr_stride * 2, 0);
+      }
+      uint32_t *ttr = &t.tw_tr[(size_t)d * t.tr_stride * 2], *itr = &t.itw_tr[(size_t)d * t.tr_stride * 2];
+      for (unsigned K = 0; K < tiles; K++)
+        for (unsigned A = 0; A < R; A++)
+          for (unsigned u = 0; u < (1u << A); u++) {
+            const size_t src = ((size_t)((1u << S) + K) << A) + u;
+            const size_t dst = ((size_t)(K >> 5) * slots + ((1u << A) - 1) + u) * 32 + (K & 31);
+            ttr[2 * dst] = tw[2 * src]; ttr[2 * dst + 1] = tw[2 * src + 1];
+            itr[2 * dst] = itw[2 * src]; itr[2 * dst + 1] = itw[2 * src + 1];
+          }
     }
     uint64_t r = 1;
     const uint64_t r32 = (1ULL << 32) % p;
