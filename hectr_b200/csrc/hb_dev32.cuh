@@ -373,7 +373,7 @@ namespace hb32 {
 #define HB32_PN_MINB 2
 #endif
 #ifndef HB32_MA_MINB
-#define HB32_MA_MINB 2
+#define HB32_MA_MINB 3      /* 79 registers, 112 bytes of stack: 5.38 -> 5.23 ms per step against 2 CTAs of 128 (variants_occ.log) */
 #endif
 template <int LOGN, int WT>
 __global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_PN_MINB)
@@ -623,7 +623,7 @@ __device__ __forceinline__ uint32_t decompose32(const uint64_t *__restrict__ pol
 // 6.05 -> 8.01 ms per step (its 64-byte-per-thread runs halve the coalescing): the 30-bit kernels are not bound by their
 // shared-memory traffic (profiles/r02/fused_passes.txt).
 #ifndef HB32_KSB_MINB
-#define HB32_KSB_MINB 5
+#define HB32_KSB_MINB 6      /* after the transposed twiddles and the static word count: 7.11 ms at 5, 6.99 at 6, 7.34 at 4 (variants_occ.log) */
 #endif
 #ifndef HB32_KSS_MINB
 #define HB32_KSS_MINB 4
