@@ -1036,7 +1036,7 @@ static unsigned key_lift_bits(hb_ctx *ctx, const uint64_t *raw, uint32_t **key32
     uint32_t *key32 = (uint32_t *)hb_dev_alloc(ctx, (size_t)2 * m * 2 * N * 4);
     do32_ntt_fwd_plain(ctx, res32, hat32, (size_t)2 * m, m);
     const size_t total = (size_t)2 * m * N;
-    launch(ctx, "k32_shoup_prep", hb32::k32_shoup_prep, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint32_t *)hat32, key32, ctx->dt32, m, (size_t)2 * m, 0u);
+    launch(ctx, "k32_shoup_prep", hb32::k32_shoup_prep, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint32_t *)hat32, key32, ctx->dt32, m, (size_t)2 * m, 0u, 2u);
     *key32_out = key32;
   }
   unsigned bits = 0;
@@ -1439,11 +1439,11 @@ static const GemvPlan &gemv_plan(hb_ctx *ctx, const double *A, unsigned l) {
     plan.D32 = hb::limbs32_for_bits(ctx->ht32, h.Pfull[plan.D].bits());
     if (plan.D32) {
       raw32 = (uint32_t *)hb_dev_alloc(ctx, (size_t)S * plan.D32 * h.N * 4);
-      plan.pthat32 = (uint32_t *)hb_dev_alloc(ctx, (size_t)S * plan.D32 * h.N * 8);
+      plan.pthat32 = (uint32_t *)hb_dev_alloc(ctx, (size_t)S * plan.D32 * h.N * 4 * HB32_PT_PLANES);
       do32_poly_ntt(ctx, dpt, ptw, (int)h.WC, raw32, plan.D32, S, true);
       const size_t total = (size_t)S * plan.D32 * h.N;
       launch(ctx, "k32_shoup_prep", hb32::k32_shoup_prep, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint32_t *)raw32, plan.pthat32, ctx->dt32,
-             plan.D32, (size_t)S * plan.D32, plan.D32);
+             plan.D32, (size_t)S * plan.D32, plan.D32, (unsigned)HB32_PT_PLANES);
       plan.use32 = true;
     }
   }

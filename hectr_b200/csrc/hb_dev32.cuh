@@ -31,6 +31,18 @@ __device__ __forceinline__ uint32_t shoup32(uint32_t a, uint32_t w, uint32_t wq,
   return a * w - __umulhi(a, wq) * p;
 }
 __device__ __forceinline__ uint32_t csub32(uint32_t x, uint32_t m) { return min(x, x - m); }    // x < 2m -> x mod-ish m
+// a w mod p in (0, 2p) for any 32-bit a, from wR = w 2^32 mod p and pinv = p^-1 mod 2^32:  t = a wR, m = lo(t) pinv, so that
+// m p = t (mod 2^32) and (t - m p) / 2^32 = hi(t) - hi(m p) exactly, in (-p, p)
+__device__ __forceinline__ uint32_t mont32(uint32_t a, uint32_t wR, uint32_t p, uint32_t pinv) {
+  const uint64_t t = (uint64_t)a * wR;
+  const uint32_t m = (uint32_t)t * pinv;
+  return (uint32_t)(t >> 32) - __umulhi(m, p) + p;
+}
+__device__ __forceinline__ uint32_t inv32_mod_2_32(uint32_t p) {      // p odd: Newton, 5 -> 10 -> 20 -> 40 correct bits
+  uint32_t x = p * 3u ^ 2u;                                           // 5 correct bits
+  x *= 2u - p * x; x *= 2u - p * x; x *= 2u - p * x;
+  return x;
+}
 
 template <int LOGN>
 struct Cfg32 {
@@ -263,7 +275,11 @@ k32_poly_ntt(const uint64_t *__restrict__ src, size_t poly_stride, int W, uint32
 // reconstruction its per-limb multiply).  limbs[j][N] uses prime j % D.
 // Output is PLANAR per limb: out[limb][0][N] the multiplicands, out[limb][1][N] their quotients, so that a warp's 16-byte
 // loads of either plane are contiguous.
-__global__ void k32_shoup_prep(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, Tables32 T, unsigned D, size_t nlimbs, unsigned Dw) {
+// planes = 3 adds out[limb][2][N] = w 2^32 mod p: a fixed multiplicand in Montgomery form needs ONE word per product where a
+// Shoup pair needs two (mont32 below); the diagonals of a gemv plan carry all three (HB32_PT_PLANES).
+#define HB32_PT_PLANES 3
+__global__ void k32_shoup_prep(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, Tables32 T, unsigned D, size_t nlimbs, unsigned Dw,
+                               unsigned planes) {
   const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= nlimbs * T.N) return;
   const unsigned d = (unsigned)((gid / T.N) % D);
@@ -275,8 +291,11 @@ __global__ void k32_shoup_prep(const uint32_t *__restrict__ in, uint32_t *__rest
     w = csub32(shoup32(w, inv.x, inv.y, pc.p), pc.p);
   }
   const size_t limb = gid / T.N, i = gid % T.N;
-  out[(2 * limb) * T.N + i] = w;
-  out[(2 * limb + 1) * T.N + i] = (uint32_t)((((uint64_t)w) << 32) / pc.p);
+  const uint64_t w32 = ((uint64_t)w) << 32;
+  const uint32_t wq = (uint32_t)(w32 / pc.p);
+  out[(planes * limb) * T.N + i] = w;
+  out[(planes * limb + 1) * T.N + i] = wq;
+  if (planes > 2) out[(planes * limb + 2) * T.N + i] = (uint32_t)(w32 - (uint64_t)wq * pc.p);      // w 2^32 mod p (Montgomery form)
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -294,12 +313,12 @@ k32_mulacc_intt(const uint32_t *__restrict__ hat, size_t hat_jstride, const uint
   const uint32_t *pthat_all = q < q_split ? pthat_a : pthat_b;
   const uint32_t p = T.primes[d].p, p2 = 2 * p;
   const uint32_t *a = hat + ((size_t)q * D + d) * G::N;
-  const uint32_t *w = pthat_all + ((size_t)GM.idx[qq / nq] * pthat_gstride + d) * 2 * G::N;       // strides in limbs
+  const uint32_t *w = pthat_all + ((size_t)GM.idx[qq / nq] * pthat_gstride + d) * HB32_PT_PLANES * G::N;       // strides in limbs
 #pragma unroll 2
   for (int i = threadIdx.x; i < G::N; i += G::THREADS) {
     uint32_t acc = 0;
     for (unsigned j = 0; j < n1; j++) {
-      const uint32_t *wj = w + (size_t)j * D * 2 * G::N;
+      const uint32_t *wj = w + (size_t)j * D * HB32_PT_PLANES * G::N;
       acc = csub32(acc + shoup32(HB_LD(&a[(size_t)j * hat_jstride + i]), __ldg(&wj[i]), __ldg(&wj[G::N + i]), p), p2);
     }
     sm32[pidx32(i)] = acc;                                                       // below 2p
@@ -372,6 +391,9 @@ namespace hb32 {
 #ifndef HB32_PN_MINB
 #define HB32_PN_MINB 2
 #endif
+#ifndef HB32_MA_MONT
+#define HB32_MA_MONT 1
+#endif
 #ifndef HB32_MA_MINB
 #define HB32_MA_MINB 3      /* 79 registers, 112 bytes of stack: 5.38 -> 5.23 ms per step against 2 CTAs of 128 (variants_occ.log) */
 #endif
@@ -441,6 +463,9 @@ k32_mulacc_intt_all(const uint32_t *__restrict__ hat, size_t hat_jstride, const 
   const unsigned q = blockIdx.x / D, d = blockIdx.x % D;
   const uint32_t *pthat_all = q < q_split ? pthat_a : pthat_b;
   const uint32_t p = T.primes[d].p, p2 = 2 * p;
+#if HB32_MA_MONT
+  const uint32_t pinv = inv32_mod_2_32(p);
+#endif
   uint4 h[NJ][V];
 #pragma unroll
   for (int j = 0; j < NJ; j++) {
@@ -451,19 +476,27 @@ k32_mulacc_intt_all(const uint32_t *__restrict__ hat, size_t hat_jstride, const 
   const Tw32 itw = tw32_of(T, d, true);
 #pragma unroll 1
   for (unsigned g = 0; g < ngroups; g++) {
-    const uint32_t *w = pthat_all + ((size_t)GM.idx[g] * pthat_gstride + d) * 2 * G::N;       // strides in limbs
+    const uint32_t *w = pthat_all + ((size_t)GM.idx[g] * pthat_gstride + d) * HB32_PT_PLANES * G::N;       // strides in limbs
 #pragma unroll
     for (int k = 0; k < V; k++) {
       const int i4 = threadIdx.x + k * G::THREADS;
       uint32_t acc[4] = {0, 0, 0, 0};
 #pragma unroll
       for (int j = 0; j < NJ; j++) {
-        const uint4 *wp = reinterpret_cast<const uint4 *>(w + (size_t)j * D * 2 * G::N);
+        const uint4 *wp = reinterpret_cast<const uint4 *>(w + (size_t)j * D * HB32_PT_PLANES * G::N);
+#if HB32_MA_MONT
+        const uint4 kr = __ldg(&wp[2 * (G::N / 4) + i4]);                   // Montgomery plane: one 16-byte load per four products
+        acc[0] = csub32(acc[0] + mont32(h[j][k].x, kr.x, p, pinv), p2);
+        acc[1] = csub32(acc[1] + mont32(h[j][k].y, kr.y, p, pinv), p2);
+        acc[2] = csub32(acc[2] + mont32(h[j][k].z, kr.z, p, pinv), p2);
+        acc[3] = csub32(acc[3] + mont32(h[j][k].w, kr.w, p, pinv), p2);
+#else
         const uint4 kw = __ldg(&wp[i4]), kq = __ldg(&wp[G::N / 4 + i4]);    // elements 4 i4 .. 4 i4 + 3 of both planes
         acc[0] = csub32(acc[0] + shoup32(h[j][k].x, kw.x, kq.x, p), p2);
         acc[1] = csub32(acc[1] + shoup32(h[j][k].y, kw.y, kq.y, p), p2);
         acc[2] = csub32(acc[2] + shoup32(h[j][k].z, kw.z, kq.z, p), p2);
         acc[3] = csub32(acc[3] + shoup32(h[j][k].w, kw.w, kq.w, p), p2);
+#endif
       }
 #pragma unroll
       for (int e = 0; e < 4; e++) sm32[pidx32(4 * i4) + e] = acc[e];
