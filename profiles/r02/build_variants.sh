@@ -13,3 +13,9 @@ build ksminb2 -DHB_KS_MINB=2 &            # 59-bit key-switch kernels: 2 CTAs pe
 build nostream -DHB_NOSTREAM &            # no evict-first cache hints
 build ksb4_kss3 -DHB32_KSB_MINB=4 -DHB32_KSS_MINB=3 &
 wait
+# knobs of the later A/B runs (variants_tails.log, variants_tw_tr.log, variants_occ.log, variants_mont.log):
+#   -DHB32_KSS_UNROLL=2|8|16  -DHB32_KSS_PUNROLL=4  -DHB32_KSB_PUNROLL=4     loop unrolling of the 30-bit key-switch kernels
+#   -DHB_FSH_MINB=1|5|7|8  -DHB_FH_MINB=1|10|12                                resident CTAs per SM of the hybrid tails
+#   -DHB32_TW_TR=0                                                             natural twiddle table in the stride-1 pass
+#   -DHB32_KSB_MINB=4|5  -DHB32_KSS_MINB=3  -DHB32_PN_MINB=3  -DHB32_MA_MINB=2  resident CTAs per SM of the 30-bit kernels
+#   -DHB32_MA_MONT=0                                                           Shoup pairs instead of Montgomery-form diagonals
