@@ -388,14 +388,26 @@ namespace hb32 {
 // ===============================================================================================================
 
 // One CTA per polynomial: the W words of 16 coefficients per thread are read once and decomposed onto every limb.
+// k32_poly_ntt_all keeps no digits in registers: the words are read again for every limb (from L2 after the first), four
+// coefficients at a time, and five CTAs of 48 registers fit an SM where two of 128 did: 6.13 -> 5.45 ms per step
+// [B200, 4096 instances; variants_misc.log, variants_reread.log].  HB32_PN_REREAD=0 restores the digits in registers.
 #ifndef HB32_PN_MINB
-#define HB32_PN_MINB 2
+#define HB32_PN_MINB 5
+#endif
+#ifndef HB32_PN_REREAD
+#define HB32_PN_REREAD 4
+#endif
+// k32_mulacc_intt_all reads the n1 rotated transforms again for every giant step (from L2 after the first) instead of holding
+// them in 64 registers: five CTAs of 48 registers per SM, 5.13 -> 4.75 ms per step [variants_reread_ma.log].
+// HB32_MA_REREAD=0 with HB32_MA_MINB=3 restores the register-resident version.
+#ifndef HB32_MA_REREAD
+#define HB32_MA_REREAD 1
 #endif
 #ifndef HB32_MA_MONT
 #define HB32_MA_MONT 1
 #endif
 #ifndef HB32_MA_MINB
-#define HB32_MA_MINB 3      /* 79 registers, 112 bytes of stack: 5.38 -> 5.23 ms per step against 2 CTAs of 128 (variants_occ.log) */
+#define HB32_MA_MINB 5
 #endif
 template <int LOGN, int WT>
 __global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_PN_MINB)
@@ -405,20 +417,19 @@ k32_poly_ntt_all(const uint64_t *__restrict__ src, size_t poly_stride, uint32_t 
   extern __shared__ __align__(16) uint32_t sm32[];
   const unsigned q = blockIdx.x;
   const uint64_t *poly = src + (size_t)q * poly_stride;
-  uint32_t dig[PER][2 * WT];
-  uint32_t sign[PER];
+#if !HB32_PN_REREAD
+  uint32_t dig[PER][2 * WT];                                  // the sign of a coefficient is the top bit of its last digit
 #pragma unroll
   for (int k = 0; k < PER; k++) {
     const int i = threadIdx.x + k * G::THREADS;
-    uint64_t top = 0;
 #pragma unroll
     for (int w = 0; w < WT; w++) {
-      top = HB_LD(&poly[(size_t)w * G::N + i]);
-      dig[k][2 * w] = (uint32_t)top;
-      dig[k][2 * w + 1] = (uint32_t)(top >> 32);
+      const uint64_t word = HB_LD(&poly[(size_t)w * G::N + i]);
+      dig[k][2 * w] = (uint32_t)word;
+      dig[k][2 * w + 1] = (uint32_t)(word >> 32);
     }
-    sign[k] = (uint32_t)((int64_t)top >> 63);
   }
+#endif
 #pragma unroll 1
   for (unsigned d = 0; d < D; d++) {
     const uint32_t p = T.primes[d].p, p2 = 2 * p;
@@ -427,13 +438,33 @@ k32_poly_ntt_all(const uint64_t *__restrict__ src, size_t poly_stride, uint32_t 
 #pragma unroll
     for (int w = 0; w < 2 * WT; w++) c[w] = __ldg(&pw[w]);
     const uint32_t negW = p - __ldg(&pw[2 * WT]).x;
+#if HB32_PN_REREAD
+    // the words are read again for every limb (from L2 after the first): 64 registers of digits less per thread
+    constexpr int RR = HB32_PN_REREAD;
+#pragma unroll RR
+    for (int k = 0; k < PER; k++) {
+      const int i = threadIdx.x + k * G::THREADS;
+      uint32_t dg[2 * WT];
+#pragma unroll
+      for (int w = 0; w < WT; w++) {
+        const uint64_t word = __ldg(&poly[(size_t)w * G::N + i]);
+        dg[2 * w] = (uint32_t)word;
+        dg[2 * w + 1] = (uint32_t)(word >> 32);
+      }
+      uint32_t acc = shoup32(dg[0], c[0].x, c[0].y, p);
+#pragma unroll
+      for (int w = 1; w < 2 * WT; w++) acc = csub32(acc + shoup32(dg[w], c[w].x, c[w].y, p), p2);
+      sm32[pidx32(threadIdx.x) + k * HB32_PSTEP(G::THREADS)] = acc + (negW & (uint32_t)((int32_t)dg[2 * WT - 1] >> 31));      // below 3p
+    }
+#else
 #pragma unroll
     for (int k = 0; k < PER; k++) {
       uint32_t acc = shoup32(dig[k][0], c[0].x, c[0].y, p);
 #pragma unroll
       for (int w = 1; w < 2 * WT; w++) acc = csub32(acc + shoup32(dig[k][w], c[w].x, c[w].y, p), p2);
-      sm32[pidx32(threadIdx.x) + k * HB32_PSTEP(G::THREADS)] = acc + (negW & sign[k]);      // below 3p
+      sm32[pidx32(threadIdx.x) + k * HB32_PSTEP(G::THREADS)] = acc + (negW & (uint32_t)((int32_t)dig[k][2 * WT - 1] >> 31));      // below 3p
     }
+#endif
     ntt32_forward<LOGN>(sm32, tw32_of(T, d, false), p);
     uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)q * D + d) * G::N);
 #pragma unroll
@@ -466,6 +497,7 @@ k32_mulacc_intt_all(const uint32_t *__restrict__ hat, size_t hat_jstride, const 
 #if HB32_MA_MONT
   const uint32_t pinv = inv32_mod_2_32(p);
 #endif
+#if !HB32_MA_REREAD
   uint4 h[NJ][V];
 #pragma unroll
   for (int j = 0; j < NJ; j++) {
@@ -473,29 +505,36 @@ k32_mulacc_intt_all(const uint32_t *__restrict__ hat, size_t hat_jstride, const 
 #pragma unroll
     for (int k = 0; k < V; k++) h[j][k] = __ldcs(&a[threadIdx.x + k * G::THREADS]);
   }
+#endif
   const Tw32 itw = tw32_of(T, d, true);
 #pragma unroll 1
   for (unsigned g = 0; g < ngroups; g++) {
     const uint32_t *w = pthat_all + ((size_t)GM.idx[g] * pthat_gstride + d) * HB32_PT_PLANES * G::N;       // strides in limbs
-#pragma unroll
+    constexpr int KU = HB32_MA_REREAD ? HB32_MA_REREAD : V;
+#pragma unroll KU
     for (int k = 0; k < V; k++) {
       const int i4 = threadIdx.x + k * G::THREADS;
       uint32_t acc[4] = {0, 0, 0, 0};
 #pragma unroll
       for (int j = 0; j < NJ; j++) {
         const uint4 *wp = reinterpret_cast<const uint4 *>(w + (size_t)j * D * HB32_PT_PLANES * G::N);
+#if HB32_MA_REREAD
+        const uint4 hv = __ldg(reinterpret_cast<const uint4 *>(hat + (size_t)j * hat_jstride + ((size_t)q * D + d) * G::N) + i4);
+#else
+        const uint4 hv = h[j][k];
+#endif
 #if HB32_MA_MONT
         const uint4 kr = __ldg(&wp[2 * (G::N / 4) + i4]);                   // Montgomery plane: one 16-byte load per four products
-        acc[0] = csub32(acc[0] + mont32(h[j][k].x, kr.x, p, pinv), p2);
-        acc[1] = csub32(acc[1] + mont32(h[j][k].y, kr.y, p, pinv), p2);
-        acc[2] = csub32(acc[2] + mont32(h[j][k].z, kr.z, p, pinv), p2);
-        acc[3] = csub32(acc[3] + mont32(h[j][k].w, kr.w, p, pinv), p2);
+        acc[0] = csub32(acc[0] + mont32(hv.x, kr.x, p, pinv), p2);
+        acc[1] = csub32(acc[1] + mont32(hv.y, kr.y, p, pinv), p2);
+        acc[2] = csub32(acc[2] + mont32(hv.z, kr.z, p, pinv), p2);
+        acc[3] = csub32(acc[3] + mont32(hv.w, kr.w, p, pinv), p2);
 #else
         const uint4 kw = __ldg(&wp[i4]), kq = __ldg(&wp[G::N / 4 + i4]);    // elements 4 i4 .. 4 i4 + 3 of both planes
-        acc[0] = csub32(acc[0] + shoup32(h[j][k].x, kw.x, kq.x, p), p2);
-        acc[1] = csub32(acc[1] + shoup32(h[j][k].y, kw.y, kq.y, p), p2);
-        acc[2] = csub32(acc[2] + shoup32(h[j][k].z, kw.z, kq.z, p), p2);
-        acc[3] = csub32(acc[3] + shoup32(h[j][k].w, kw.w, kq.w, p), p2);
+        acc[0] = csub32(acc[0] + shoup32(hv.x, kw.x, kq.x, p), p2);
+        acc[1] = csub32(acc[1] + shoup32(hv.y, kw.y, kq.y, p), p2);
+        acc[2] = csub32(acc[2] + shoup32(hv.z, kw.z, kq.z, p), p2);
+        acc[3] = csub32(acc[3] + shoup32(hv.w, kw.w, kq.w, p), p2);
 #endif
       }
 #pragma unroll
@@ -521,8 +560,11 @@ namespace hb32 {
 
 // k32_recon_smod with the limb count fixed at compile time and four consecutive coefficients per thread: one 16-byte
 // load per limb, 32-bit digit chains (one IMAD.WIDE per digit), 16-byte stores.  Same integers as k32_recon_smod.
+#ifndef HB32_RS4_MINB
+#define HB32_RS4_MINB 1
+#endif
 template <int WK, int DD>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, HB32_RS4_MINB)
 k32_recon_smod4(const uint32_t *__restrict__ chat, uint64_t *__restrict__ out, int Wout, int k, Tables32 T, unsigned npoly) {
   const unsigned N = T.N, N4 = N >> 2;
   const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
