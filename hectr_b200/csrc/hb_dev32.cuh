@@ -398,7 +398,7 @@ namespace hb32 {
 #define HB32_PN_REREAD 4
 #endif
 // k32_mulacc_intt_all reads the n1 rotated transforms again for every giant step (from L2 after the first) instead of holding
-// them in 64 registers: five CTAs of 48 registers per SM, 5.13 -> 4.75 ms per step [variants_reread_ma.log].
+// them in 64 registers: six CTAs of 40 registers per SM, 5.13 -> 4.65 ms per step [variants_reread_ma.log, variants_reread2.log].
 // HB32_MA_REREAD=0 with HB32_MA_MINB=3 restores the register-resident version.
 #ifndef HB32_MA_REREAD
 #define HB32_MA_REREAD 1
@@ -407,7 +407,7 @@ namespace hb32 {
 #define HB32_MA_MONT 1
 #endif
 #ifndef HB32_MA_MINB
-#define HB32_MA_MINB 5
+#define HB32_MA_MINB 6
 #endif
 template <int LOGN, int WT>
 __global__ void __launch_bounds__(Cfg32<LOGN>::THREADS, HB32_PN_MINB)
