@@ -119,6 +119,16 @@ def test_gemv_shortcuts_equal_the_plain_schedule(cfgA, monkeypatch):
     rng = np.random.default_rng(811)
     Ka, Kb = hempc_gains(rng)
     Ad = rng.standard_normal((16, 16)) + 1j * rng.standard_normal((16, 16))
+
+    def banded(diags):
+        """only the generalised diagonals `diags` are non-zero (zrotdiag, he-algo.c:29-43: entry r of diagonal d is A[r, r + d])"""
+        A = np.zeros((16, 16), dtype=np.complex128)
+        for d in diags:
+            for r in range(16):
+                A[r, (r + d) % 16] = rng.standard_normal() + 1j * rng.standard_normal()
+        return A
+
+    M1, M2 = banded(range(0, 4)), banded(list(range(0, 4)) + list(range(8, 12)))     # one / two giant steps of four evaluated
     monkeypatch.setenv("HB_GEMV_NOHYB", "1")
     sum59 = Engine(*A_PARAMS)
     monkeypatch.setenv("HB_GEMV_NOSUM", "1")
@@ -139,7 +149,7 @@ def test_gemv_shortcuts_equal_the_plain_schedule(cfgA, monkeypatch):
         for l in (2, 1):
             a = random_ct_words(rng, 192, eng.words(l), eng.n, eng.logq(l))
             a[0, 1] = 0                                     # c1 = 0: every R is exactly 0
-            for M in (Ad, Ka, Kb):
+            for M in (Ad, Ka, Kb, M1, M2):
                 outs, profs = [], []
                 for e, kk in engines:
                     e.lib.hb_prof_reset(e.ctx)
