@@ -103,7 +103,7 @@ struct hb_ctx {
   // hybrid-basis key switch (hb_dev32.cuh): every uploaded key also lives on the first hyb_mmax primes of the 30-bit basis
   unsigned hyb_mmax = 0;            // 0: the hybrid path is not available for this context
   uint32_t *hyb_q32 = nullptr;      // DEVICE [hyb_mmax] primes
-  std::map<const void *, uint32_t *> evk32;     // evk.p -> DEVICE key32[2][hyb_mmax][2][N] (multiplicand / quotient planes, times N^-1)
+  std::map<const void *, uint32_t *> evk32;     // evk.p -> DEVICE key32[2][hyb_mmax][HB32_KEY_PLANES][N], times N^-1 (Montgomery form, or multiplicand / quotient planes)
   struct HybBasis { unsigned m = 0, Mbits = 0; ulonglong2 *dec59 = nullptr; uint2 *dec32 = nullptr; hbdev::KsHyb F; };
   std::map<unsigned, HybBasis> hyb; // constants of M = P * Q_m, by m
   bool no_hyb = false;              // HB_GEMV_NOHYB=1: every key-switch limb on the reference's 59-bit primes
@@ -993,7 +993,7 @@ extern "C" void hb_pt_upload(hb_ctx *ctx, hb_pt *pt, const uint64_t *host, doubl
   CUDA_OK(cudaStreamSynchronize(ctx->stream));
 }
 // largest |coefficient| (bit length) of a key given as canonical-or-[0,p] transform limbs raw[2][dimevk][N] on the device.
-// key32_out (hybrid path available): the same key on the 30-bit primes, key32[2][hyb_mmax][2][N] planes, times N^-1.
+// key32_out (hybrid path available): the same key on the 30-bit primes, key32[2][hyb_mmax][HB32_KEY_PLANES][N], times N^-1.
 static unsigned key_lift_bits(hb_ctx *ctx, const uint64_t *raw, uint32_t **key32_out) {
   const hb::HostTables &h = ctx->ht;
   const unsigned D = h.dimevk;
@@ -1033,10 +1033,11 @@ static unsigned key_lift_bits(hb_ctx *ctx, const uint64_t *raw, uint32_t **key32
   launch(ctx, "k_lift_bits", hbkg::k_lift_bits, (unsigned)((2 * N + 127) / 128), 128, 0, 1, (const uint64_t *)coef, ctx->keycheck, 2u, dmax,
          (const uint32_t *)ctx->hyb_q32, m, res32);
   if (m) {
-    uint32_t *key32 = (uint32_t *)hb_dev_alloc(ctx, (size_t)2 * m * 2 * N * 4);
+    uint32_t *key32 = (uint32_t *)hb_dev_alloc(ctx, (size_t)2 * m * HB32_KEY_PLANES * N * 4);
     do32_ntt_fwd_plain(ctx, res32, hat32, (size_t)2 * m, m);
     const size_t total = (size_t)2 * m * N;
-    launch(ctx, "k32_shoup_prep", hb32::k32_shoup_prep, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint32_t *)hat32, key32, ctx->dt32, m, (size_t)2 * m, 0u, 2u);
+    launch(ctx, "k32_shoup_prep", hb32::k32_shoup_prep, (unsigned)((total + 255) / 256), 256, 0, 1, (const uint32_t *)hat32, key32, ctx->dt32, m, (size_t)2 * m, 0u,
+           (unsigned)HB32_KEY_PLANES);
     *key32_out = key32;
   }
   unsigned bits = 0;

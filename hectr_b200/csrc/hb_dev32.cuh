@@ -293,9 +293,11 @@ __global__ void k32_shoup_prep(const uint32_t *__restrict__ in, uint32_t *__rest
   const size_t limb = gid / T.N, i = gid % T.N;
   const uint64_t w32 = ((uint64_t)w) << 32;
   const uint32_t wq = (uint32_t)(w32 / pc.p);
+  const uint32_t wR = (uint32_t)(w32 - (uint64_t)wq * pc.p);         // w 2^32 mod p (Montgomery form)
+  if (planes == 1) { out[limb * T.N + i] = wR; return; }             // evaluation keys on the hybrid basis: mont32 only
   out[(planes * limb) * T.N + i] = w;
   out[(planes * limb + 1) * T.N + i] = wq;
-  if (planes > 2) out[(planes * limb + 2) * T.N + i] = (uint32_t)(w32 - (uint64_t)wq * pc.p);      // w 2^32 mod p (Montgomery form)
+  if (planes > 2) out[(planes * limb + 2) * T.N + i] = wR;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -697,6 +699,10 @@ __device__ __forceinline__ uint32_t decompose32(const uint64_t *__restrict__ pol
 // changed k32_ks_baby 8.55 -> 8.65, k32_ks_limb_sum 8.66 -> 8.48, k32_poly_ntt_all 6.76 -> 6.66 and k32_mulacc_intt_all
 // 6.05 -> 8.01 ms per step (its 64-byte-per-thread runs halve the coalescing): the 30-bit kernels are not bound by their
 // shared-memory traffic (profiles/r02/fused_passes.txt).
+// planes of an evaluation key on the 30-bit primes: 1 = Montgomery form only (mont32: one load per product), 2 = Shoup pairs
+#ifndef HB32_KEY_PLANES
+#define HB32_KEY_PLANES 1
+#endif
 #ifndef HB32_KSB_MINB
 #define HB32_KSB_MINB 6      /* after the transposed twiddles and the static word count: 7.11 ms at 5, 6.99 at 6, 7.34 at 4 (variants_occ.log) */
 #endif
@@ -723,6 +729,9 @@ k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const _
   // (limb-major CTA order -- CTAs resident together share a prime, its twiddles and keys -- measured slower: 4.36 vs 4.28 ms)
   const unsigned b = blockIdx.x / m, i = blockIdx.x % m;
   const uint32_t p = T.primes[i].p, p2 = 2 * p;
+#if HB32_KEY_PLANES == 1
+  const uint32_t pinv = inv32_mod_2_32(p);
+#endif
   const uint2 *pw = dec32 + (size_t)i * decstride;
   const uint32_t negW = p - __ldg(&pw[2 * W]).x;
   const uint64_t *poly = src + (size_t)b * src_bstride;
@@ -737,6 +746,15 @@ k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const _
     const uint16_t *perm = S.perm[j];
 #pragma unroll 1
     for (int h = 0; h < 2; h++) {
+#if HB32_KEY_PLANES == 1
+      const uint32_t *kr = S.key[j] + ((size_t)h * mkey + i) * G::N;
+#pragma unroll KSB_PUNROLL
+      for (int k = 0; k < PER; k++) {
+        const int c = threadIdx.x + k * G::THREADS;
+        const unsigned s = __ldg(&perm[c]);
+        smB[pb + k * PST] = mont32(smA[pidx32(s)], __ldg(&kr[c]), p, pinv);                 // below 2q
+      }
+#else
       const uint32_t *kw = S.key[j] + ((size_t)h * mkey + i) * 2 * G::N, *kq = kw + G::N;
 #pragma unroll KSB_PUNROLL
       for (int k = 0; k < PER; k++) {
@@ -744,6 +762,7 @@ k32_ks_baby(const uint64_t *__restrict__ src, size_t src_bstride, int W, const _
         const unsigned s = __ldg(&perm[c]);
         smB[pb + k * PST] = shoup32(smA[pidx32(s)], __ldg(&kw[c]), __ldg(&kq[c]), p);      // below 2q
       }
+#endif
       ntt32_inverse<LOGN>(smB, itw, p);
       uint32_t *dst = chat + (size_t)j * chat_jstride + (((size_t)b * 2 + h) * m + i) * G::N;
 #pragma unroll 4
@@ -765,6 +784,9 @@ k32_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src
   uint32_t *smA = sm32;
   const unsigned b = blockIdx.x / m, i = blockIdx.x % m;      // (limb-major order measured slower: 4.92 vs 4.33 ms)
   const uint32_t p = T.primes[i].p, p2 = 2 * p;
+#if HB32_KEY_PLANES == 1
+  const uint32_t pinv = inv32_mod_2_32(p);
+#endif
   const uint2 *pw = dec32 + (size_t)i * decstride;
   const uint32_t negW = p - __ldg(&pw[2 * W]).x;
   const Tw32 tw = tw32_of(T, i, false);
@@ -785,11 +807,19 @@ k32_ks_limb_sum(const uint64_t *__restrict__ src, size_t src_bstride, size_t src
 #pragma unroll 1
     for (int h = 0; h < 2; h++) {
       uint32_t *acc = sm32 + (size_t)(1 + h) * G::SMEM_WORDS;
+#if HB32_KEY_PLANES == 1
+      const uint32_t *kr = S.key[g] + ((size_t)h * mkey + i) * G::N;
+#else
       const uint32_t *kw = S.key[g] + ((size_t)h * mkey + i) * 2 * G::N, *kq = kw + G::N;
+#endif
 #pragma unroll KSS_PUNROLL
       for (int k = 0; k < PER; k++) {
         const int c = threadIdx.x + k * G::THREADS, o = pb + k * PST;
+#if HB32_KEY_PLANES == 1
+        uint32_t v = mont32(smA[o], __ldg(&kr[c]), p, pinv);                            // below 2q
+#else
         uint32_t v = shoup32(smA[o], __ldg(&kw[c]), __ldg(&kq[c]), p);                  // below 2q
+#endif
         if (g) v = csub32(v + acc[o], p2);
         acc[o] = v;
       }
